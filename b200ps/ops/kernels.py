@@ -1,0 +1,260 @@
+"""Torch-tensor front ends of the native sm_100a kernels (libb200ps.so).
+
+Each function validates shapes/dtypes/devices, then hands raw device pointers and the
+current CUDA stream to the C ABI (include/b200ps.h).  There is no PyTorch fallback: on a
+CUDA tensor the native kernel runs or an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import native
+from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI_SGD, EPI_STORE,
+                     GemmArgs, check, ptr, stream_ptr)
+
+__all__ = [
+    "gemm", "mlp_tail", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
+    "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
+    "cast_f32_bf16", "sparse_lr", "auc_hist", "push_sync_sgd", "push_async", "pull", "barrier",
+    "device_ptr_table", "signal_pad_words",
+]
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return DT_BF16
+    if t.dtype == torch.float32:
+        return DT_F32
+    raise TypeError(f"unsupported dtype {t.dtype} (bf16 or fp32 only)")
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("b200ps kernels need CUDA tensors")
+
+
+def _row_stride(t: torch.Tensor) -> int:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError("expected a 2-D tensor with unit inner stride")
+    return t.stride(0)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *,
+         a_mn_major: bool = False, b_mn_major: bool = False, alpha: float = 1.0,
+         bias: Optional[torch.Tensor] = None, act: int = ACT_NONE,
+         dsigmoid_of: Optional[torch.Tensor] = None, epilogue: int = EPI_STORE, split_k: int = 1,
+         sgd_master: Optional[torch.Tensor] = None, sgd_lowp: Optional[torch.Tensor] = None,
+         sgd_lr: float = 0.0, out_dtype: Optional[torch.dtype] = None, max_ctas: int = 0,
+         stream=None) -> Optional[torch.Tensor]:
+    """tcgen05/TMA GEMM  ``out[M,N] = epilogue(alpha * op(a) @ op(b))``.
+
+    ``a`` is ``[M,K]`` (K-major) or, with ``a_mn_major``, stored ``[K,M]``;
+    ``b`` is ``[N,K]`` (K-major) or, with ``b_mn_major``, stored ``[K,N]``.
+    fp32 operands run on the tensor cores as tf32.  Replaces tf.matmul and its gradients
+    (example.py:95,97,118).
+    """
+    _cuda(a, b, out, bias, dsigmoid_of, sgd_master, sgd_lowp)
+    if a.dtype != b.dtype:
+        raise TypeError("gemm: A and B dtypes differ")
+    M, K = (a.shape[1], a.shape[0]) if a_mn_major else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn_major else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise ValueError(f"gemm: reduction dims differ ({K} vs {Kb})")
+    args = GemmArgs()
+    args.M, args.N, args.K = M, N, K
+    args.ab_dtype = _dt(a)
+    args.a_mn_major, args.b_mn_major = int(a_mn_major), int(b_mn_major)
+    args.A, args.lda = ptr(a), _row_stride(a)
+    args.B, args.ldb = ptr(b), _row_stride(b)
+    if epilogue == EPI_SGD:
+        if sgd_master is None or tuple(sgd_master.shape) != (M, N) or sgd_master.dtype != torch.float32:
+            raise ValueError("gemm: EPI_SGD needs an fp32 sgd_master of shape [M,N]")
+        args.C, args.ldc, args.c_dtype = 0, _row_stride(sgd_master), DT_F32
+        if sgd_lowp is not None and (_row_stride(sgd_lowp) != args.ldc or sgd_lowp.dtype != torch.bfloat16):
+            raise ValueError("gemm: sgd_lowp must be bf16 with the master's row stride")
+    else:
+        if out is None:
+            out = torch.empty((M, N), device=a.device,
+                              dtype=out_dtype or (torch.float32 if epilogue == EPI_ATOMIC_ADD else a.dtype))
+        if tuple(out.shape) != (M, N):
+            raise ValueError(f"gemm: out has shape {tuple(out.shape)}, want {(M, N)}")
+        args.C, args.ldc, args.c_dtype = ptr(out), _row_stride(out), _dt(out)
+    args.epilogue = epilogue
+    args.alpha = alpha
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != N):
+        raise ValueError("gemm: bias must be fp32 [N]")
+    args.bias = ptr(bias)
+    args.act = act
+    if dsigmoid_of is not None:
+        if out is None or dsigmoid_of.dtype != out.dtype or tuple(dsigmoid_of.shape) != (M, N):
+            raise ValueError("gemm: dsigmoid_of must match out")
+        args.aux, args.ldaux = ptr(dsigmoid_of), _row_stride(dsigmoid_of)
+    else:
+        args.aux, args.ldaux = 0, 0
+    args.split_k = split_k
+    args.sgd_master, args.sgd_lowp, args.sgd_lr = ptr(sgd_master), ptr(sgd_lowp), sgd_lr
+    args.max_ctas = max_ctas
+    check(native.load().b200ps_gemm(C.byref(args), stream_ptr(stream)), "gemm")
+    return out
+
+
+def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=None, db2=None,
+             db1=None, a2_out=None, probs_out=None, train=True, grad_scale=None, loss_scale=None,
+             stream=None):
+    """Fused narrow MLP head (K6): see include/b200ps.h b200ps_mlp_tail."""
+    _cuda(z2, b1, w2, b2, labels)
+    B, H = z2.shape
+    Cn = w2.shape[1]
+    if labels.dtype != torch.int32:
+        raise TypeError("mlp_tail: labels must be int32 class ids")
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    check(native.load().b200ps_mlp_tail(ptr(z2), ptr(b1), ptr(w2), ptr(b2), ptr(labels), ptr(a2_out),
+                                        ptr(dz2), ptr(dw2), ptr(db2), ptr(db1), ptr(loss_sum),
+                                        ptr(correct), ptr(probs_out), B, H, Cn, int(train), gs, ls,
+                                        stream_ptr(stream)), "mlp_tail")
+
+
+def softmax_ce(logits, labels, *, dlogits=None, loss_sum=None, correct=None, grad_scale=None,
+               loss_scale=None, stream=None):
+    _cuda(logits, labels)
+    B, Cn = logits.shape
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    check(native.load().b200ps_softmax_ce(ptr(logits), ptr(labels), ptr(dlogits), ptr(loss_sum),
+                                          ptr(correct), B, Cn, _row_stride(logits), _dt(logits), gs, ls,
+                                          stream_ptr(stream)), "softmax_ce")
+
+
+def colsum(x, out, scale=1.0, stream=None):
+    _cuda(x, out)
+    M, N = x.shape
+    check(native.load().b200ps_colsum(ptr(x), ptr(out), M, N, _row_stride(x), _dt(x), scale,
+                                      stream_ptr(stream)), "colsum")
+
+
+def sgd_apply(params, grads, lr, *, lowp=None, grad_scale=1.0, stream=None):
+    _cuda(params, grads, lowp)
+    check(native.load().b200ps_sgd_apply(ptr(params), ptr(grads), _dt(grads), ptr(lowp), params.numel(),
+                                         lr, grad_scale, stream_ptr(stream)), "sgd_apply")
+
+
+def adam_apply(params, grads, m, v, beta_pow, lr, beta1=0.9, beta2=0.999, eps=1e-8, stream=None):
+    _cuda(params, grads, m, v, beta_pow)
+    check(native.load().b200ps_adam_apply(ptr(params), ptr(grads), ptr(m), ptr(v), params.numel(), lr,
+                                          beta1, beta2, eps, ptr(beta_pow), stream_ptr(stream)),
+          "adam_apply")
+
+
+def adam_advance(beta_pow, beta1=0.9, beta2=0.999, stream=None):
+    check(native.load().b200ps_adam_advance(ptr(beta_pow), beta1, beta2, stream_ptr(stream)), "adam_advance")
+
+
+def linreg_fwd_bwd(x, y, w, b, *, ypred=None, loss=None, gw=None, gb=None, inv_n=None, stream=None):
+    _cuda(x, y, w, b)
+    B, D = x.shape
+    check(native.load().b200ps_linreg_fwd_bwd(ptr(x), ptr(y), ptr(w), ptr(b), ptr(ypred), ptr(loss),
+                                              ptr(gw), ptr(gb), B, D,
+                                              (1.0 / B) if inv_n is None else inv_n,
+                                              stream_ptr(stream)), "linreg_fwd_bwd")
+
+
+def synth_mnist(x, labels, *, onehot=None, classes=10, seed=1, offset=0, stream=None):
+    _cuda(x, labels, onehot)
+    B, D = x.shape
+    check(native.load().b200ps_synth_mnist(ptr(x), ptr(onehot), ptr(labels), B, D, classes, seed, offset,
+                                           stream_ptr(stream)), "synth_mnist")
+
+
+def synth_dense_bf16(x, labels, *, classes, seed=1, offset=0, stream=None):
+    _cuda(x, labels)
+    B, D = x.shape
+    check(native.load().b200ps_synth_dense_bf16(ptr(x), ptr(labels), B, D, classes, seed, offset,
+                                                stream_ptr(stream)), "synth_dense_bf16")
+
+
+def synth_sparse(row_ptr, fid, fval, labels, *, nnz_mean, spread, features, skew=1.0, seed=1, offset=0,
+                 stream=None):
+    _cuda(row_ptr, fid, fval, labels)
+    B = labels.numel()
+    if fid.numel() < B * (nnz_mean + spread):
+        raise ValueError("synth_sparse: fid/fval too small for B*(nnz_mean+spread)")
+    check(native.load().b200ps_synth_sparse(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), B, nnz_mean,
+                                            spread, features, skew, seed, offset, stream_ptr(stream)),
+          "synth_sparse")
+
+
+def init_normal(out, *, mean=0.0, stddev=1.0, seed=1, stream_id=0, stream=None):
+    _cuda(out)
+    if out.dtype != torch.float32 or not out.is_contiguous():
+        raise TypeError("init_normal: contiguous fp32 only")
+    check(native.load().b200ps_init_normal(ptr(out), out.numel(), mean, stddev, seed, stream_id,
+                                           stream_ptr(stream)), "init_normal")
+
+
+def cast_f32_bf16(src, dst, stream=None):
+    _cuda(src, dst)
+    check(native.load().b200ps_cast_f32_bf16(ptr(src), ptr(dst), src.numel(), stream_ptr(stream)), "cast")
+
+
+def device_ptr_table(ptrs: Sequence[int], device) -> torch.Tensor:
+    """int64 device tensor holding raw addresses (the pointer tables the comm kernels take)."""
+    return torch.tensor([int(p) for p in ptrs], dtype=torch.int64, device=device)
+
+
+def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, pred=None, dz_out=None,
+              dz_in=None, loss_sum=None, global_step=None, forward=True, update=True, lr=0.0,
+              grad_scale=None, loss_scale=None, stream=None):
+    """Sparse LR step over a row-sharded weight (K4/K5).  ``w_table`` = device_ptr_table of shard bases."""
+    _cuda(row_ptr, fid, fval, labels, w_table, bias)
+    B = labels.numel()
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    check(native.load().b200ps_sparse_lr(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), ptr(w_table),
+                                         ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in), ptr(loss_sum),
+                                         ptr(global_step), B, rows_per_shard, int(forward), int(update),
+                                         lr, gs, ls, stream_ptr(stream)), "sparse_lr")
+
+
+def auc_hist(pred, labels, thresholds, hist_pos, hist_neg, stream=None):
+    _cuda(pred, labels, thresholds, hist_pos, hist_neg)
+    check(native.load().b200ps_auc_hist(ptr(pred), ptr(labels), pred.numel(), ptr(thresholds),
+                                        thresholds.numel(), ptr(hist_pos), ptr(hist_neg),
+                                        stream_ptr(stream)), "auc_hist")
+
+
+def signal_pad_words() -> int:
+    return int(native.load().b200ps_signal_pad_words())
+
+
+def push_sync_sgd(pads, masters, outs, grads, bounds, global_steps, *, world, rank_base, local_ranks=1,
+                  max_shard_elems, dtype, replicas_to_aggregate, lr, max_ctas=0, stream=None):
+    d = DT_BF16 if dtype == torch.bfloat16 else DT_F32
+    check(native.load().b200ps_push_sync_sgd(ptr(pads), ptr(masters), ptr(outs), ptr(grads), ptr(bounds),
+                                             ptr(global_steps), world, rank_base, local_ranks,
+                                             max_shard_elems, d, d, replicas_to_aggregate, lr, max_ctas,
+                                             stream_ptr(stream)), "push_sync_sgd")
+
+
+def push_async(masters, grads, bounds, global_steps, *, world, rank_base, local_ranks=1, total_elems, lr,
+               max_ctas=0, stream=None):
+    check(native.load().b200ps_push_async(ptr(masters), ptr(grads), ptr(bounds), ptr(global_steps), world,
+                                          rank_base, local_ranks, total_elems, lr, max_ctas,
+                                          stream_ptr(stream)), "push_async")
+
+
+def pull(masters, outs, bounds, *, world, rank_base, local_ranks=1, max_shard_elems, dtype,
+         include_self=False, max_ctas=0, stream=None):
+    d = DT_BF16 if dtype == torch.bfloat16 else DT_F32
+    check(native.load().b200ps_pull(ptr(masters), ptr(outs), ptr(bounds), world, rank_base, local_ranks,
+                                    max_shard_elems, d, int(include_self), max_ctas, stream_ptr(stream)),
+          "pull")
+
+
+def barrier(pads, *, world, rank_base, local_ranks=1, stream=None):
+    check(native.load().b200ps_barrier(ptr(pads), world, rank_base, local_ranks, stream_ptr(stream)),
+          "barrier")

@@ -1,0 +1,104 @@
+#!/usr/bin/env python
+"""Build libb200ps.so (sm_100a) in-tree with nvcc.  No GPU is needed to build.
+
+    python build.py            # incremental
+    python build.py --force    # rebuild everything
+    python build.py --verbose  # also print ptxas resource usage (-Xptxas -v)
+"""
+import argparse
+import concurrent.futures as cf
+import hashlib
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(ROOT, "csrc")
+OUT_DIR = os.path.join(ROOT, "b200ps", "_lib")
+OBJ_DIR = os.path.join(ROOT, "build", "obj")
+LIB = os.path.join(OUT_DIR, "libb200ps.so")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
+          "--expt-relaxed-constexpr", "-I", os.path.join(ROOT, "include")]
+
+
+def sources():
+    out = []
+    for d, _, files in os.walk(CSRC):
+        for f in sorted(files):
+            if f.endswith((".cu", ".cpp")):
+                out.append(os.path.join(d, f))
+    return sorted(out)
+
+
+def headers_digest():
+    h = hashlib.sha1()
+    for d, _, files in os.walk(CSRC):
+        for f in sorted(files):
+            if f.endswith((".h", ".cuh")):
+                h.update(open(os.path.join(d, f), "rb").read())
+    h.update(open(os.path.join(ROOT, "include", "b200ps.h"), "rb").read())
+    return h.hexdigest()
+
+
+def compile_one(src, obj, verbose):
+    cmd = [NVCC, *ARCH, *COMMON, "-c", src, "-o", obj]
+    if src.endswith(".cpp"):
+        cmd = [NVCC, *ARCH, *COMMON, "-x", "cu", "-c", src, "-o", obj]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    return src, r.returncode, r.stdout + r.stderr
+
+
+def build(force=False, verbose=False, quiet=False):
+    os.makedirs(OUT_DIR, exist_ok=True)
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    hdig = headers_digest()
+    jobs, objs = [], []
+    for src in sources():
+        rel = os.path.relpath(src, CSRC).replace(os.sep, "_")
+        obj = os.path.join(OBJ_DIR, rel + ".o")
+        stamp = obj + ".stamp"
+        key = hashlib.sha1(open(src, "rb").read() + hdig.encode()).hexdigest()
+        objs.append(obj)
+        fresh = (not force and os.path.exists(obj) and os.path.exists(stamp)
+                 and open(stamp).read() == key)
+        if not fresh:
+            jobs.append((src, obj, stamp, key))
+    failed = False
+    with cf.ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        futs = {ex.submit(compile_one, s, o, verbose): (s, o, st, k) for s, o, st, k in jobs}
+        for fut in cf.as_completed(futs):
+            src, rc, log = fut.result()
+            s, o, st, k = futs[fut]
+            if rc != 0:
+                failed = True
+                print(f"[build] FAILED {os.path.relpath(src, ROOT)}\n{log}", file=sys.stderr)
+            else:
+                open(st, "w").write(k)
+                if not quiet:
+                    print(f"[build] compiled {os.path.relpath(src, ROOT)}")
+                if verbose or "warning" in log:
+                    print(log)
+    if failed:
+        raise RuntimeError("nvcc failed")
+    if jobs or not os.path.exists(LIB):
+        cmd = [NVCC, *ARCH, "-shared", "-o", LIB, *objs, "-lpthread"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            print(r.stdout + r.stderr, file=sys.stderr)
+            raise RuntimeError("link failed")
+        if not quiet:
+            print(f"[build] linked {os.path.relpath(LIB, ROOT)}")
+    return LIB
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    a = ap.parse_args()
+    build(force=a.force, verbose=a.verbose)

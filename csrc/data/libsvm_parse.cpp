@@ -1,0 +1,77 @@
+// b200ps N6 — native libsvm text parser.  The reference parses every line in CPython
+// (Sample.parse_line_libsvm, lr2.py:57-67) and then rebuilds python lists per batch
+// (format_samples_sparse, lr2.py:69-84); that loop is its real CPU hot spot.  This parser
+// turns a whole text buffer into CSR arrays in one pass, multi-buffer safe (no globals).
+//
+// Grammar per line:  <int label> (SEP <int index> ':' <float value>)*   with SEP = ' ' | '\t'
+// Lines shorter than 2 characters are skipped, as in lr2.py:105.
+#include <cstddef>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+
+namespace {
+inline bool is_sep(char c) { return c == ' ' || c == '\t'; }
+}
+
+// Pass 1: count rows and non-zeros so the caller can size the arrays.
+extern "C" int b200ps_libsvm_count(const char* buf, uint64_t len, uint64_t* rows, uint64_t* nnz) {
+  uint64_t r = 0, z = 0;
+  const char* p = buf;
+  const char* end = buf + len;
+  while (p < end) {
+    const char* nl = static_cast<const char*>(memchr(p, '\n', end - p));
+    const char* le = nl ? nl : end;
+    if (le - p >= 2) {
+      ++r;
+      for (const char* q = p; q < le; ++q) z += (*q == ':');
+    }
+    p = nl ? nl + 1 : end;
+  }
+  *rows = r;
+  *nnz = z;
+  return 0;
+}
+
+// Pass 2: fill labels[rows], row_ptr[rows+1], fid[nnz], fval[nnz].
+// Returns 0, or -(line number) of the first malformed line.
+extern "C" int64_t b200ps_libsvm_parse(const char* buf, uint64_t len, float* labels, int32_t* row_ptr,
+                                       int64_t* fid, float* fval, uint64_t max_rows, uint64_t max_nnz) {
+  uint64_t r = 0, z = 0;
+  int64_t line_no = 0;
+  const char* p = buf;
+  const char* end = buf + len;
+  row_ptr[0] = 0;
+  while (p < end) {
+    const char* nl = static_cast<const char*>(memchr(p, '\n', end - p));
+    const char* le = nl ? nl : end;
+    ++line_no;
+    if (le - p >= 2) {
+      if (r >= max_rows) return -line_no;
+      const char* q = p;
+      char* e = nullptr;
+      const long lab = strtol(q, &e, 10);
+      if (e == q) return -line_no;
+      labels[r] = static_cast<float>(lab);
+      q = e;
+      while (q < le) {
+        while (q < le && (is_sep(*q) || *q == '\r')) ++q;
+        if (q >= le) break;
+        const long long idx = strtoll(q, &e, 10);
+        if (e == q || e >= le || *e != ':') return -line_no;
+        q = e + 1;
+        const float val = strtof(q, &e);
+        if (e == q) return -line_no;
+        q = e;
+        if (z >= max_nnz) return -line_no;
+        fid[z] = idx;
+        fval[z] = val;
+        ++z;
+      }
+      ++r;
+      row_ptr[r] = static_cast<int32_t>(z);
+    }
+    p = nl ? nl + 1 : end;
+  }
+  return 0;
+}

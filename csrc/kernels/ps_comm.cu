@@ -1,0 +1,266 @@
+// b200ps K1/K3/K12 + pull — the parameter-server "wire", as kernels over NVLink peer memory.
+//
+// In the reference every sess.run partitions the graph into a worker part and a ps part
+// joined by gRPC Send/Recv: variables are pulled (example.py:95,97), gradients pushed and
+// ApplyGradientDescent runs on the ps (example.py:108,118).  Here each GPU is worker k AND
+// parameter-server shard k.  All ranks hold peer-mapped pointers to each other's buffers
+// ("symmetric memory") and the kernels below issue the traffic themselves:
+//
+//   push_sync  (K1): reduce-scatter of the replicas' gradients (the shard owner loads its
+//                    slice from every replica in a fixed order), mean over the aggregated
+//                    replicas, SGD apply on the owner's fp32 master, and broadcast of the
+//                    fresh values into every replica's working copy (the next "pull" is
+//                    already done).  Two flag exchanges bracket it: "my gradients are
+//                    ready" and "my slice has landed everywhere" — together they are the
+//                    token barrier of SyncReplicasOptimizer (example.py:110-123,147-152).
+//   push_async (K3): Hogwild.  -lr*g is added straight into the owner's master with
+//                    red.global.add.v4.f32 at system scope; no flag, no barrier;
+//                    global_step += 1 on the chief's counter (example.py:118, README.md:3).
+//   pull            : copy every peer-owned slice into the local working copy (stale reads
+//                    are allowed in async mode, exactly like un-locked variable reads).
+//   barrier   (K12): stand-alone flag barrier (Supervisor ready barrier, done tokens).
+//
+// Several "virtual ranks" can be driven by one launch (blockIdx.y = local rank): that is
+// how the multi-rank protocol is exercised on a single GPU, where ranks that wait on each
+// other must not be separate launches.
+#include "../common.h"
+#include "ptx.cuh"
+
+namespace b200ps {
+
+// layout of one rank's signal pad (uint32 words)
+constexpr int kPadWords = 256;
+constexpr int kMaxWorld = 32;
+constexpr int kFlagGradsReady = 0;    // [0,32)   written by peer r at slot r
+constexpr int kFlagParamsDone = 32;   // [32,64)
+constexpr int kFlagBarrier = 64;      // [64,96)
+constexpr int kSlotEpoch = 96;        // push epoch (local)
+constexpr int kSlotBarrierEpoch = 97; // barrier epoch (local)
+constexpr int kSlotCtaDone = 98;      // CTA completion counter (local)
+
+struct CommArgs {
+  uint32_t* const* pads;      // [world] signal pads
+  float* const* masters;      // [world] fp32 master, indexable by GLOBAL element index on its owner
+  void* const* outs;          // [world] working copies (full size), dtype O
+  const void* const* grads;   // [world] gradient buffers (full size), dtype G
+  const long long* bounds;    // [world+1] owner ranges (multiples of 8 elements)
+  unsigned long long* const* global_steps;  // [world] per-rank int64 counters
+  int world, rank_base;
+  int replicas_to_aggregate;
+  float lr;
+};
+
+template <typename T> struct Vec4;
+template <> struct Vec4<float> {
+  static __device__ __forceinline__ float4 load(const float* p) {
+    return ld_relaxed_sys_v4(reinterpret_cast<const float4*>(p));
+  }
+  static __device__ __forceinline__ void store(float* p, float4 v) {
+    *reinterpret_cast<float4*>(p) = v;
+  }
+};
+template <> struct Vec4<__nv_bfloat16> {
+  static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
+    uint2 u;
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(u.x), "=r"(u.y) : "l"(p) : "memory");
+    const float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+  }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, float4 v) {
+    uint2 u;
+    *reinterpret_cast<__nv_bfloat162*>(&u.x) = __floats2bfloat162_rn(v.x, v.y);
+    *reinterpret_cast<__nv_bfloat162*>(&u.y) = __floats2bfloat162_rn(v.z, v.w);
+    *reinterpret_cast<uint2*>(p) = u;
+  }
+};
+
+// Is replica r part of the aggregated set of this step?  With replicas_to_aggregate == world
+// every replica is.  With fewer ("backup workers") TF takes the first R gradients to arrive
+// and drops the rest; arrival order is not reproducible, so the set rotates with the step.
+__device__ __forceinline__ bool replica_counts(int r, uint32_t epoch, int world, int R) {
+  if (R >= world) return true;
+  const int d = (r - (int)(epoch % (uint32_t)world) + world) % world;
+  return d < R;
+}
+
+template <typename G, typename O>
+__global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
+  const int rank = a.rank_base + blockIdx.y;
+  const int world = a.world;
+  const int tid = threadIdx.x;
+  uint32_t* pad = a.pads[rank];
+  const uint32_t epoch = pad[kSlotEpoch] + 1;
+
+  // -- phase 0: my gradients (written by earlier kernels of this stream) are ready
+  if (blockIdx.x == 0 && tid < world) st_release_sys(a.pads[tid] + kFlagGradsReady + rank, epoch);
+  if (tid < world) wait_flag_geq(pad + kFlagGradsReady + tid, epoch);
+  __syncthreads();
+
+  // -- phase 1: reduce my slice over the replicas, apply, broadcast
+  const long long lo = a.bounds[rank], hi = a.bounds[rank + 1];
+  const float step = a.lr / (float)min(a.replicas_to_aggregate, world);
+  float* master = a.masters[rank];
+  const long long nvec = (hi - lo) >> 2;
+  for (long long v = (long long)blockIdx.x * blockDim.x + tid; v < nvec;
+       v += (long long)gridDim.x * blockDim.x) {
+    const long long i = lo + (v << 2);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < world; ++r) {  // fixed order => bitwise reproducible
+      if (!replica_counts(r, epoch, world, a.replicas_to_aggregate)) continue;
+      const float4 g = Vec4<G>::load(reinterpret_cast<const G*>(a.grads[r]) + i);
+      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+    }
+    float4 w = *reinterpret_cast<const float4*>(master + i);
+    w.x -= step * s.x; w.y -= step * s.y; w.z -= step * s.z; w.w -= step * s.w;
+    *reinterpret_cast<float4*>(master + i) = w;
+    for (int r = 0; r < world; ++r) {
+      O* dst = reinterpret_cast<O*>(a.outs[r]) + i;
+      if (reinterpret_cast<void*>(dst) != reinterpret_cast<void*>(master + i)) Vec4<O>::store(dst, w);
+    }
+  }
+
+  // -- phase 2: when every CTA of this rank is done, tell the peers and wait for theirs
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool s_last;
+  if (tid == 0) s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (s_last) {
+    __threadfence_system();
+    if (tid < world) st_release_sys(a.pads[tid] + kFlagParamsDone + rank, epoch);
+    if (tid < world) wait_flag_geq(pad + kFlagParamsDone + tid, epoch);
+    __syncthreads();
+    if (tid == 0) {
+      pad[kSlotCtaDone] = 0;
+      pad[kSlotEpoch] = epoch;
+      if (a.global_steps) *a.global_steps[rank] += 1ull;  // one step per aggregated update
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) push_async_kernel(const CommArgs a, long long n) {
+  const int rank = a.rank_base + blockIdx.y;
+  const float* g = reinterpret_cast<const float*>(a.grads[rank]);
+  const float nlr = -a.lr;
+  for (int r = 0; r < a.world; ++r) {
+    const long long lo = a.bounds[r], hi = a.bounds[r + 1];
+    float* master = a.masters[r];
+    const long long nvec = (hi - lo) >> 2;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
+         v += (long long)gridDim.x * blockDim.x) {
+      const long long i = lo + (v << 2);
+      const float4 gv = *reinterpret_cast<const float4*>(g + i);
+      red_add_v4f32_sys(master + i, make_float4(nlr * gv.x, nlr * gv.y, nlr * gv.z, nlr * gv.w));
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.global_steps)
+    atomicAdd_system(a.global_steps[0], 1ull);  // the chief's shard holds global_step
+}
+
+template <typename O>
+__global__ void __launch_bounds__(256) pull_kernel(const CommArgs a, int include_self) {
+  const int rank = a.rank_base + blockIdx.y;
+  O* dst = reinterpret_cast<O*>(a.outs[rank]);
+  for (int rr = 0; rr < a.world; ++rr) {
+    const int r = (rank + rr) % a.world;  // start with the local slice, then walk the peers
+    if (r == rank && !include_self) continue;
+    const long long lo = a.bounds[r], hi = a.bounds[r + 1];
+    const float* src = a.masters[r];
+    const long long nvec = (hi - lo) >> 2;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
+         v += (long long)gridDim.x * blockDim.x) {
+      const long long i = lo + (v << 2);
+      if (reinterpret_cast<const void*>(dst + i) == reinterpret_cast<const void*>(src + i)) continue;
+      Vec4<O>::store(dst + i, ld_relaxed_sys_v4(reinterpret_cast<const float4*>(src + i)));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(32) barrier_kernel(uint32_t* const* pads, int world, int rank_base) {
+  const int rank = rank_base + blockIdx.y;
+  uint32_t* pad = pads[rank];
+  const uint32_t epoch = pad[kSlotBarrierEpoch] + 1;
+  const int tid = threadIdx.x;
+  __threadfence_system();
+  if (tid < world) st_release_sys(pads[tid] + kFlagBarrier + rank, epoch);
+  if (tid < world) wait_flag_geq(pad + kFlagBarrier + tid, epoch);
+  __syncwarp();
+  if (tid == 0) pad[kSlotBarrierEpoch] = epoch;
+}
+
+}  // namespace b200ps
+
+using namespace b200ps;
+
+static int comm_grid(long long max_elems, int local_ranks, int want) {
+  int ctas = (int)std::min<long long>(std::max<long long>((max_elems / 4 + 255) / 256, 1), want);
+  if (local_ranks > 1) ctas = std::max(1, std::min(ctas, sm_count() / local_ranks));  // co-resident
+  return ctas;
+}
+
+extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* const* outs,
+                                    const void* const* grads, const int64_t* bounds,
+                                    uint64_t* const* global_steps, int32_t world, int32_t rank_base,
+                                    int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
+                                    int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
+                                    int32_t max_ctas, b200ps_stream_t stream) {
+  B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "push_sync: world=%d out of range", world);
+  B200PS_REQUIRE(local_ranks >= 1 && rank_base >= 0 && rank_base + local_ranks <= world, "push_sync: bad ranks");
+  B200PS_REQUIRE(grad_dtype == out_dtype, "push_sync: gradient and working-copy dtypes must match");
+  B200PS_REQUIRE(replicas_to_aggregate >= 1, "push_sync: replicas_to_aggregate < 1");
+  CommArgs a;
+  a.pads = pads; a.masters = masters; a.outs = outs; a.grads = grads;
+  a.bounds = reinterpret_cast<const long long*>(bounds);
+  a.global_steps = reinterpret_cast<unsigned long long* const*>(global_steps);
+  a.world = world; a.rank_base = rank_base; a.replicas_to_aggregate = replicas_to_aggregate; a.lr = lr;
+  const int want = max_ctas > 0 ? max_ctas : sm_count();
+  dim3 grid(comm_grid(max_shard_elems, local_ranks, want), local_ranks);
+  cudaStream_t s = as_stream(stream);
+  if (grad_dtype == B200PS_DT_F32) push_sync_sgd_kernel<float, float><<<grid, 256, 0, s>>>(a);
+  else push_sync_sgd_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>(a);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
+                                 uint64_t* const* global_steps, int32_t world, int32_t rank_base,
+                                 int32_t local_ranks, int64_t total_elems, float lr, int32_t max_ctas,
+                                 b200ps_stream_t stream) {
+  B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "push_async: world=%d out of range", world);
+  CommArgs a{};
+  a.masters = masters; a.grads = grads; a.bounds = reinterpret_cast<const long long*>(bounds);
+  a.global_steps = reinterpret_cast<unsigned long long* const*>(global_steps);
+  a.world = world; a.rank_base = rank_base; a.lr = lr;
+  const int want = max_ctas > 0 ? max_ctas : sm_count();
+  dim3 grid(comm_grid(total_elems / std::max(world, 1), 1, want), local_ranks);
+  push_async_kernel<<<grid, 256, 0, as_stream(stream)>>>(a, total_elems);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ps_pull(float* const* masters, void* const* outs, const int64_t* bounds, int32_t world,
+                           int32_t rank_base, int32_t local_ranks, int64_t max_shard_elems,
+                           int32_t out_dtype, int32_t include_self, int32_t max_ctas,
+                           b200ps_stream_t stream) {
+  B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "pull: world=%d out of range", world);
+  CommArgs a{};
+  a.masters = masters; a.outs = outs; a.bounds = reinterpret_cast<const long long*>(bounds);
+  a.world = world; a.rank_base = rank_base;
+  const int want = max_ctas > 0 ? max_ctas : sm_count();
+  dim3 grid(comm_grid(max_shard_elems, 1, want), local_ranks);
+  if (out_dtype == B200PS_DT_F32) pull_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(a, include_self);
+  else pull_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(a, include_self);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ps_barrier(uint32_t* const* pads, int32_t world, int32_t rank_base, int32_t local_ranks,
+                              b200ps_stream_t stream) {
+  B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "barrier: world=%d out of range", world);
+  barrier_kernel<<<dim3(1, local_ranks), 32, 0, as_stream(stream)>>>(pads, world, rank_base);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ps_signal_pad_words(void) { return kPadWords; }

@@ -1,0 +1,209 @@
+/* b200ps — C ABI of the native sm_100a library (libb200ps.so).
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on and
+ * returns 0 on success or a negative b200ps error code (b200ps_last_error() gives the
+ * text).  Nothing here synchronises the stream.  The Python package reaches these through
+ * ctypes (b200ps/ops/native.py); C/C++ embedders include this header and link the .so.
+ *
+ * Citations of the form (example.py:95) point into the reference tree
+ * Amano-Ginji/distributed-tensorflow-example and name the behaviour each kernel replaces.
+ */
+#ifndef B200PS_H_
+#define B200PS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200ps_stream_t; /* cudaStream_t */
+
+enum {
+  B200PS_OK = 0,
+  B200PS_ERR_INVALID = -1, /* bad argument (shape, alignment, dtype, size limit) */
+  B200PS_ERR_CUDA = -2,    /* a CUDA runtime/driver call failed */
+  B200PS_ERR_UNSUPPORTED = -3
+};
+
+/* Text of the last error raised on the calling thread. */
+const char* b200ps_last_error(void);
+/* Library version string, e.g. "b200ps 0.1 sm_100a". */
+const char* b200ps_version(void);
+/* Number of kernel launches issued by this library in this process (all threads). */
+uint64_t b200ps_launch_count(void);
+
+/* ------------------------------------------------------------------------------------
+ * K2/K7: tcgen05 + TMA GEMM with fused epilogues.
+ *   C[M,N] = epilogue( alpha * op(A)[M,K] * op(B)[K,N] )
+ * A is stored either K-major ([M,K] row-major, a_mn_major = 0) or MN-major ([K,M]
+ * row-major, a_mn_major = 1); B either K-major ([N,K] row-major, b_mn_major = 0) or
+ * MN-major ([K,N] row-major, b_mn_major = 1).  lda/ldb/ldc/ldaux are row strides in
+ * ELEMENTS of the stored 2-D arrays.  Operand rows must be 16-byte aligned.
+ * Replaces the Eigen CPU matmuls behind tf.matmul (example.py:95,97) and their
+ * autodiff gradients (example.py:118).
+ * ---------------------------------------------------------------------------------- */
+enum { B200PS_DT_BF16 = 0, B200PS_DT_F32 = 1 }; /* F32 operands run as kind::tf32 */
+enum { B200PS_ACT_NONE = 0, B200PS_ACT_SIGMOID = 1 };
+enum {
+  B200PS_EPI_STORE = 0,      /* C = act(alpha*acc + bias) * dsigmoid(aux)              */
+  B200PS_EPI_ATOMIC_ADD = 1, /* C += alpha*acc  (fp32 C, red.global.add; for split-K)  */
+  B200PS_EPI_SGD = 2         /* master -= lr*alpha*acc ; lowp = bf16(master) if lowp   */
+};
+
+typedef struct b200ps_gemm_args {
+  int32_t M, N, K;
+  int32_t ab_dtype; /* B200PS_DT_* of A and B */
+  int32_t a_mn_major, b_mn_major;
+  const void* A;
+  int64_t lda;
+  const void* B;
+  int64_t ldb;
+  void* C; /* may be NULL for B200PS_EPI_SGD */
+  int64_t ldc;
+  int32_t c_dtype; /* B200PS_DT_* */
+  int32_t epilogue;
+  float alpha;
+  const float* bias; /* [N] or NULL */
+  int32_t act;
+  const void* aux; /* [M,N] activation a (c_dtype); C *= a*(1-a). NULL = off */
+  int64_t ldaux;
+  int32_t split_k;     /* >= 1; > 1 requires B200PS_EPI_ATOMIC_ADD */
+  float* sgd_master;   /* [M,N] fp32, row stride ldc (EPI_SGD) */
+  void* sgd_lowp;      /* [M,N] bf16 shadow, row stride ldc, or NULL (EPI_SGD) */
+  float sgd_lr;
+  int32_t max_ctas;    /* 0 = one CTA per SM */
+} b200ps_gemm_args;
+
+int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * K6/K8: fused MLP head for narrow outputs (C <= 32, H <= 256): bias1 + sigmoid,
+ * head GEMM, stable log-softmax cross-entropy, accuracy count and, when train != 0,
+ * dZ2 (for the first-layer wgrad GEMM), dW2, db2, db1.  (example.py:96-103,127-128)
+ *   z2 [B,H] is the first-layer pre-activation WITHOUT bias.  loss_sum and correct are
+ *   accumulated into (+=).  grad_scale multiplies dZ3 (1/global_batch for a mean loss).
+ * ---------------------------------------------------------------------------------- */
+int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const float* b2,
+                    const int32_t* labels, float* a2_out, float* dz2, float* dw2, float* db2,
+                    float* db1, float* loss_sum, int32_t* correct, float* probs_out, int32_t B,
+                    int32_t H, int32_t C, int32_t train, float grad_scale, float loss_scale,
+                    b200ps_stream_t stream);
+
+/* Wide-head softmax cross-entropy: logits [B,C] (ld = row stride) -> dlogits (same dtype,
+ * may alias logits, may be NULL), loss_sum += , correct += .  C <= 16384. */
+int b200ps_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, float* loss_sum,
+                      int32_t* correct, int32_t B, int32_t C, int64_t ld, int32_t dtype,
+                      float grad_scale, float loss_scale, b200ps_stream_t stream);
+
+/* out[n] = scale * sum_m x[m,n]  (bias gradients). out is fp32 and is overwritten. */
+int b200ps_colsum(const void* x, float* out, int32_t M, int32_t N, int64_t ld, int32_t dtype,
+                  float scale, b200ps_stream_t stream);
+
+/* K1 (single shard): params -= lr*grad_scale*grads ; lowp = bf16(params) if lowp != NULL.
+ * (ApplyGradientDescent, example.py:108) */
+int b200ps_sgd_apply(float* params, const void* grads, int32_t grad_dtype, void* lowp, uint64_t n,
+                     float lr, float grad_scale, b200ps_stream_t stream);
+
+/* K11: Adam with TF's ApplyAdam formula (model_export.py:38). beta_pow = {beta1^t, beta2^t}
+ * on the device; call b200ps_adam_advance once per step after all variables are applied. */
+int b200ps_adam_apply(float* params, const float* grads, float* m, float* v, uint64_t n, float lr,
+                      float beta1, float beta2, float eps, const float* beta_pow,
+                      b200ps_stream_t stream);
+int b200ps_adam_advance(float* beta_pow, float beta1, float beta2, b200ps_stream_t stream);
+
+/* Linear regression forward + gradients (model_export.py:35-36): loss = sum((y-yp)^2)*inv_n. */
+int b200ps_linreg_fwd_bwd(const float* x, const float* y, const float* w, const float* b,
+                          float* ypred, float* loss, float* gw, float* gb, int32_t B, int32_t D,
+                          float inv_n, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * K9: on-device synthetic input pipelines (replace example.py:60-62,165; lr2.py:87-155;
+ * input_pipeline*.py).  Pure functions of (seed, offset + row).
+ * ---------------------------------------------------------------------------------- */
+int b200ps_synth_mnist(float* x, float* onehot, int32_t* labels, int32_t B, int32_t D, int32_t C,
+                       uint64_t seed, uint64_t offset, b200ps_stream_t stream);
+int b200ps_synth_dense_bf16(void* x, int32_t* labels, int32_t B, int32_t D, int32_t C,
+                            uint64_t seed, uint64_t offset, b200ps_stream_t stream);
+/* CSR batch: row_ptr[B+1], fid/fval sized for B*(nnz_mean+spread). skew = 1 uniform ids. */
+int b200ps_synth_sparse(int32_t* row_ptr, int64_t* fid, float* fval, float* labels, int32_t B,
+                        int32_t nnz_mean, int32_t spread, int64_t F, float skew, uint64_t seed,
+                        uint64_t offset, b200ps_stream_t stream);
+/* tf.random_normal initialiser (example.py:84-85, lr2.py:384), Philox + Box-Muller. */
+int b200ps_init_normal(float* out, uint64_t n, float mean, float stddev, uint64_t seed,
+                       uint64_t stream_id, b200ps_stream_t stream);
+int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * K4/K5: sparse logistic regression over a row-sharded [F,1] weight (lr2.py:390-396).
+ * w_shards: device array of `world` shard base pointers (peer-mapped); feature id f lives
+ * at w_shards[f / rows_per_shard][f % rows_per_shard].  do_forward computes z, p, loss, dz;
+ * do_update scatters -lr*dz*fval with red.global.add (and -lr*sum(dz) into *bias, and
+ * *global_step += 1).  Both set = one fused Hogwild step.  Update-only launches read dz_in.
+ * K10: streaming-AUC histograms (lr2.py:400): bucket = #thresholds strictly below pred.
+ * ---------------------------------------------------------------------------------- */
+int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, const float* fval,
+                     const float* labels, float* const* w_shards, float* bias, float* pred,
+                     float* dz_out, const float* dz_in, float* loss_sum, uint64_t* global_step,
+                     int32_t B, int64_t rows_per_shard, int32_t do_forward, int32_t do_update,
+                     float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+int b200ps_auc_hist(const float* pred, const float* labels, int32_t B, const float* thresholds,
+                    int32_t T, uint64_t* hist_pos, uint64_t* hist_neg, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * K1/K3/K12 + pull: parameter-server traffic as kernels over peer-mapped memory.
+ * All pointer tables are DEVICE arrays with `world` entries holding addresses valid in the
+ * calling process (local or IPC-mapped).  bounds[world+1] are the owner ranges of the flat
+ * parameter space (multiples of 8 elements).  masters[r] must be indexable by the GLOBAL
+ * element index inside r's range.  rank_base/local_ranks: one launch drives ranks
+ * [rank_base, rank_base+local_ranks) — >1 only for single-GPU emulation of several ranks.
+ * pads[r]: b200ps_signal_pad_words() zero-initialised uint32 words per rank.
+ * ---------------------------------------------------------------------------------- */
+int b200ps_signal_pad_words(void);
+/* sync replicas: reduce-scatter + mean + SGD on the owner + broadcast, bracketed by the
+ * "gradients ready" / "slices landed" flag exchanges (example.py:110-123,147-152). */
+int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* const* outs,
+                         const void* const* grads, const int64_t* bounds,
+                         uint64_t* const* global_steps, int32_t world, int32_t rank_base,
+                         int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
+                         int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
+                         int32_t max_ctas, b200ps_stream_t stream);
+/* async (Hogwild): red.add of -lr*g into every owner's master; no barrier (example.py:118). */
+int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
+                      uint64_t* const* global_steps, int32_t world, int32_t rank_base,
+                      int32_t local_ranks, int64_t total_elems, float lr, int32_t max_ctas,
+                      b200ps_stream_t stream);
+/* pull: copy peer-owned slices of the masters into this rank's working copy. */
+int b200ps_pull(float* const* masters, void* const* outs, const int64_t* bounds, int32_t world,
+                int32_t rank_base, int32_t local_ranks, int64_t max_shard_elems,
+                int32_t out_dtype, int32_t include_self, int32_t max_ctas,
+                b200ps_stream_t stream);
+int b200ps_barrier(uint32_t* const* pads, int32_t world, int32_t rank_base, int32_t local_ranks,
+                   b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * N1: symmetric memory over CUDA IPC (replaces tf.train.Server, example.py:38-40).
+ * ---------------------------------------------------------------------------------- */
+int b200ps_symm_alloc(uint64_t bytes, void** ptr_out, void* handle_out /* 64 bytes or NULL */);
+int b200ps_symm_open(const void* handle /* 64 bytes */, void** ptr_out);
+int b200ps_symm_close(void* ptr);
+int b200ps_symm_free(void* ptr);
+int b200ps_device_count(int32_t* n);
+int b200ps_can_access_peer(int32_t dev, int32_t peer, int32_t* ok);
+
+/* ------------------------------------------------------------------------------------
+ * Host-side native helpers (no GPU needed).
+ * ---------------------------------------------------------------------------------- */
+/* CRC-32C used by tfevents / tensor-bundle files (example.py:154, model_export.py:53). */
+uint32_t b200ps_crc32c_extend(uint32_t init_crc, const void* data, uint64_t n);
+/* libsvm text -> CSR (lr2.py:57-84).  Count first, then parse into caller-sized arrays.
+ * parse returns 0 or -(1-based line number) of the first malformed line. */
+int b200ps_libsvm_count(const char* buf, uint64_t len, uint64_t* rows, uint64_t* nnz);
+int64_t b200ps_libsvm_parse(const char* buf, uint64_t len, float* labels, int32_t* row_ptr,
+                            int64_t* fid, float* fval, uint64_t max_rows, uint64_t max_nnz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PS_H_ */

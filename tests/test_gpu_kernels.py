@@ -1,0 +1,307 @@
+"""Non-GEMM native kernels vs PyTorch fp32/fp64 references (K1, K3-K6, K9-K12)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def test_mlp_tail_matches_autograd(native_lib):
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(0)
+    B, H, Cn = 100, 100, 10
+    z2 = torch.randn(B, H, device=DEV, generator=g)
+    b1 = torch.randn(H, device=DEV, generator=g) * 0.1
+    w2 = torch.randn(H, Cn, device=DEV, generator=g) * 0.3
+    b2 = torch.randn(Cn, device=DEV, generator=g) * 0.1
+    labels = torch.randint(0, Cn, (B,), device=DEV, generator=g, dtype=torch.int32)
+
+    z2r = z2.clone().requires_grad_(True)
+    b1r, w2r, b2r = (t.clone().requires_grad_(True) for t in (b1, w2, b2))
+    a2 = torch.sigmoid(z2r + b1r)
+    logits = a2 @ w2r + b2r
+    loss = torch.nn.functional.cross_entropy(logits, labels.long())
+    loss.backward()
+
+    loss_sum = torch.zeros(1, device=DEV)
+    correct = torch.zeros(1, device=DEV, dtype=torch.int32)
+    dz2 = torch.empty(B, H, device=DEV)
+    dw2 = torch.empty(H, Cn, device=DEV)
+    db2 = torch.empty(Cn, device=DEV)
+    db1 = torch.empty(H, device=DEV)
+    ops.mlp_tail(z2, b1, w2, b2, labels, loss_sum=loss_sum, correct=correct, dz2=dz2, dw2=dw2,
+                 db2=db2, db1=db1)
+    torch.cuda.synchronize()
+    assert abs(loss_sum.item() - loss.item()) < 1e-4
+    assert correct.item() == (logits.argmax(1) == labels).sum().item()
+    assert torch.allclose(dz2, z2r.grad, atol=1e-6, rtol=1e-4)
+    assert torch.allclose(dw2, w2r.grad, atol=1e-6, rtol=1e-4)
+    assert torch.allclose(db2, b2r.grad, atol=1e-6, rtol=1e-4)
+    assert torch.allclose(db1, b1r.grad, atol=1e-6, rtol=1e-4)
+
+
+def test_mlp_tail_eval_large_batch(native_lib):
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(1)
+    B, H, Cn = 10000, 100, 10
+    z2 = torch.randn(B, H, device=DEV, generator=g)
+    b1 = torch.zeros(H, device=DEV)
+    w2 = torch.randn(H, Cn, device=DEV, generator=g)
+    b2 = torch.zeros(Cn, device=DEV)
+    labels = torch.randint(0, Cn, (B,), device=DEV, generator=g, dtype=torch.int32)
+    loss_sum = torch.zeros(1, device=DEV)
+    correct = torch.zeros(1, device=DEV, dtype=torch.int32)
+    ops.mlp_tail(z2, b1, w2, b2, labels, loss_sum=loss_sum, correct=correct, train=False)
+    logits = torch.sigmoid(z2) @ w2
+    ref = torch.nn.functional.cross_entropy(logits, labels.long())
+    assert abs(loss_sum.item() - ref.item()) < 1e-3
+    assert correct.item() == (logits.argmax(1) == labels).sum().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_softmax_ce(native_lib, dtype):
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(2)
+    B, Cn = 64, 8192
+    logits = (torch.randn(B, Cn, device=DEV, generator=g) * 2).to(dtype)
+    labels = torch.randint(0, Cn, (B,), device=DEV, generator=g, dtype=torch.int32)
+    lr = logits.float().clone().requires_grad_(True)
+    loss = torch.nn.functional.cross_entropy(lr, labels.long())
+    loss.backward()
+    d = torch.empty_like(logits)
+    loss_sum = torch.zeros(1, device=DEV)
+    correct = torch.zeros(1, device=DEV, dtype=torch.int32)
+    ops.softmax_ce(logits, labels, dlogits=d, loss_sum=loss_sum, correct=correct)
+    assert abs(loss_sum.item() - loss.item()) < 2e-3
+    assert correct.item() == (logits.float().argmax(1) == labels).sum().item()
+    tol = 1e-6 if dtype == torch.float32 else 1e-4
+    assert (d.float() - lr.grad).abs().max().item() < tol
+
+
+def test_colsum_sgd_adam(native_lib):
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(1000, 300, device=DEV, generator=g).bfloat16()
+    out = torch.empty(300, device=DEV)
+    ops.colsum(x, out, scale=0.5)
+    assert torch.allclose(out, 0.5 * x.float().sum(0), atol=1e-2, rtol=1e-3)
+
+    p = torch.randn(10007, device=DEV, generator=g)
+    gr = torch.randn(10007, device=DEV, generator=g)
+    want = p - 0.05 * gr
+    lowp = torch.empty(10007, device=DEV, dtype=torch.bfloat16)
+    ops.sgd_apply(p, gr, 0.05, lowp=lowp)
+    assert torch.allclose(p, want, atol=1e-7)
+    assert torch.equal(lowp, p.bfloat16())
+
+    # Adam vs torch.optim.Adam (same formula as TF's ApplyAdam up to eps placement: use TF's)
+    w = torch.randn(513, device=DEV, generator=g)
+    m = torch.zeros_like(w); v = torch.zeros_like(w)
+    bp = torch.tensor([0.9, 0.999], device=DEV)
+    wr = w.double().clone(); mr = torch.zeros_like(wr); vr = torch.zeros_like(wr)
+    for t in range(1, 4):
+        gr = torch.randn(513, device=DEV, generator=g)
+        ops.adam_apply(w, gr, m, v, bp, lr=0.01)
+        ops.adam_advance(bp)
+        gd = gr.double()
+        mr = 0.9 * mr + 0.1 * gd
+        vr = 0.999 * vr + 0.001 * gd * gd
+        lr_t = 0.01 * math.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t)
+        wr = wr - lr_t * mr / (vr.sqrt() + 1e-8)
+    assert torch.allclose(w.double(), wr, atol=1e-5)
+
+
+def test_linreg(native_lib):
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(4)
+    x = torch.rand(100, 1, device=DEV, generator=g) * 100
+    y = x + 20 * torch.sin(x / 10)
+    w = torch.randn(1, 1, device=DEV, generator=g); b = torch.zeros(1, device=DEV)
+    wr = w.clone().requires_grad_(True); br = b.clone().requires_grad_(True)
+    loss = (((y - (x @ wr + br)) ** 2) / 1000).sum()
+    loss.backward()
+    lo = torch.zeros(1, device=DEV); gw = torch.zeros(1, device=DEV); gb = torch.zeros(1, device=DEV)
+    ops.linreg_fwd_bwd(x, y.reshape(-1), w, b, loss=lo, gw=gw, gb=gb, inv_n=1 / 1000)
+    assert torch.allclose(lo, loss.detach().reshape(1), rtol=1e-4)
+    assert torch.allclose(gw, wr.grad.reshape(1), rtol=1e-4)
+    assert torch.allclose(gb, br.grad.reshape(1), rtol=1e-4)
+
+
+def test_synth_generators(native_lib):
+    from b200ps import ops
+    x = torch.empty(512, 784, device=DEV); lab = torch.empty(512, device=DEV, dtype=torch.int32)
+    oh = torch.empty(512, 10, device=DEV)
+    ops.synth_mnist(x, lab, onehot=oh, seed=7, offset=100)
+    assert 0 <= x.min().item() and x.max().item() <= 1
+    assert torch.equal(oh.argmax(1).int(), lab) and set(lab.tolist()) <= set(range(10))
+    x2 = torch.empty(256, 784, device=DEV); lab2 = torch.empty(256, device=DEV, dtype=torch.int32)
+    ops.synth_mnist(x2, lab2, seed=7, offset=356)      # rows 256.. of the first call
+    assert torch.equal(x2, x[256:]) and torch.equal(lab2, lab[256:])
+
+    xb = torch.empty(64, 256, device=DEV, dtype=torch.bfloat16)
+    lb = torch.empty(64, device=DEV, dtype=torch.int32)
+    ops.synth_dense_bf16(xb, lb, classes=256, seed=3)
+    assert xb.float().abs().max().item() <= 1.0 + 1e-3 and lb.max().item() < 256
+
+    B, nnz, spread, F = 500, 100, 20, 1 << 24
+    rp = torch.empty(B + 1, device=DEV, dtype=torch.int32)
+    fid = torch.empty(B * (nnz + spread), device=DEV, dtype=torch.int64)
+    fv = torch.empty(B * (nnz + spread), device=DEV)
+    y = torch.empty(B, device=DEV)
+    ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=5)
+    lens = (rp[1:] - rp[:-1])
+    assert rp[0].item() == 0 and lens.min().item() >= nnz - spread and lens.max().item() <= nnz + spread
+    n = rp[-1].item()
+    assert 0 <= fid[:n].min().item() and fid[:n].max().item() < F
+    assert set(y.tolist()) <= {0.0, 1.0} and 0.2 < y.mean().item() < 0.8
+
+    w = torch.empty(100003, device=DEV)
+    ops.init_normal(w, seed=1, stream_id=3)
+    assert abs(w.mean().item()) < 0.02 and abs(w.std().item() - 1) < 0.02
+
+
+def _sparse_batch(B=500, nnz=100, spread=20, F=1 << 20, seed=5):
+    from b200ps import ops
+    rp = torch.empty(B + 1, device=DEV, dtype=torch.int32)
+    fid = torch.empty(B * (nnz + spread), device=DEV, dtype=torch.int64)
+    fv = torch.empty(B * (nnz + spread), device=DEV)
+    y = torch.empty(B, device=DEV)
+    ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=seed)
+    return rp, fid, fv, y
+
+
+@pytest.mark.parametrize("world", [1, 4])
+def test_sparse_lr_vs_dense_reference(native_lib, world):
+    from b200ps import ops
+    F = 1 << 20
+    rp, fid, fv, y = _sparse_batch(F=F)
+    B = y.numel(); n = rp[-1].item()
+    g = torch.Generator(device=DEV).manual_seed(9)
+    W = torch.randn(F, device=DEV, generator=g) * 0.1
+    rows = F // world
+    shards = [W[r * rows:(r + 1) * rows].clone() for r in range(world)]
+    table = ops.device_ptr_table([s.data_ptr() for s in shards], DEV)
+    bias = torch.full((1,), 0.25, device=DEV)
+    # float64 reference
+    row_of = torch.repeat_interleave(torch.arange(B, device=DEV), (rp[1:] - rp[:-1]).long())
+    z = torch.zeros(B, device=DEV, dtype=torch.float64).index_add_(
+        0, row_of, W.double()[fid[:n]] * fv[:n].double()) + 0.25
+    p_ref = torch.sigmoid(z)
+    loss_ref = torch.nn.functional.binary_cross_entropy_with_logits(z, y.double())
+    dz_ref = (p_ref - y.double()) / B
+    lr = 0.5
+    W_ref = W.double().index_add(0, fid[:n], -lr * dz_ref[row_of] * fv[:n].double())
+    b_ref = 0.25 - lr * dz_ref.sum().item()
+
+    pred = torch.empty(B, device=DEV); loss = torch.zeros(1, device=DEV)
+    gstep = torch.zeros(1, device=DEV, dtype=torch.int64)
+    ops.sparse_lr(rp, fid, fv, y, table, bias, rows_per_shard=rows, pred=pred, loss_sum=loss,
+                  global_step=gstep, forward=True, update=True, lr=lr)
+    torch.cuda.synchronize()
+    assert torch.allclose(pred.double(), p_ref, atol=1e-5)
+    assert abs(loss.item() - loss_ref.item()) < 1e-5
+    got = torch.cat(shards).double()
+    assert (got - W_ref).abs().max().item() < 1e-5     # Hogwild within one launch: tiny read/write overlap
+    assert abs(bias.item() - b_ref) < 1e-5 and gstep.item() == 1
+
+
+def test_auc_hist(native_lib):
+    from b200ps import ops
+    from b200ps.metrics.auc import StreamingAUC, auc_from_counts_reference
+    g = torch.Generator(device=DEV).manual_seed(11)
+    pred = torch.rand(5000, device=DEV, generator=g)
+    pred[:7] = torch.tensor([0., 1., 0.5, 1 / 199, 2 / 199, 198 / 199, 0.25], device=DEV)
+    y = (torch.rand(5000, device=DEV, generator=g) < pred).float()
+    m = StreamingAUC(num_thresholds=200, device=DEV)
+    m.update(pred[:3000], y[:3000]); m.update(pred[3000:], y[3000:])
+    tp, fn, tn, fp = m.counts()
+    rtp, rfn, rtn, rfp = auc_from_counts_reference(pred.cpu().numpy(), y.cpu().numpy(), 200)
+    assert (tp == rtp).all() and (fn == rfn).all() and (tn == rtn).all() and (fp == rfp).all()
+    assert 0.6 < m.result() < 1.0
+
+
+def _virtual_ranks(world, n, dtype):
+    """One GPU, `world` emulated ranks: full-size working copies, grads, pads on the same device."""
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(13)
+    shard = ((n + world - 1) // world + 7) // 8 * 8
+    total = shard * world
+    bounds = torch.tensor([min(r * shard, total) for r in range(world + 1)], device=DEV, dtype=torch.int64)
+    init = torch.randn(total, device=DEV, generator=g)
+    work = [init.to(dtype).clone() for _ in range(world)]
+    if dtype == torch.float32:
+        masters = work                                     # master lives in place in the working copy
+        master_ptrs = [w.data_ptr() for w in work]
+    else:
+        masters = [init[r * shard:(r + 1) * shard].clone() for r in range(world)]
+        master_ptrs = [m.data_ptr() - 4 * r * shard for r, m in enumerate(masters)]
+    grads = [(torch.randn(total, device=DEV, generator=g)).to(dtype) for _ in range(world)]
+    pads = [torch.zeros(ops.signal_pad_words(), device=DEV, dtype=torch.int32) for _ in range(world)]
+    gsteps = [torch.zeros(1, device=DEV, dtype=torch.int64) for _ in range(world)]
+    T = lambda ts: ops.device_ptr_table([t if isinstance(t, int) else t.data_ptr() for t in ts], DEV)
+    return dict(shard=shard, total=total, bounds=bounds, init=init, work=work, masters=masters,
+                grads=grads, pads=pads, gsteps=gsteps, t_pads=T(pads), t_masters=T(master_ptrs),
+                t_outs=T(work), t_grads=T(grads), t_gsteps=T(gsteps))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("world,R", [(1, 1), (4, 4), (4, 3)])
+def test_push_sync_virtual_ranks(native_lib, dtype, world, R):
+    from b200ps import ops
+    v = _virtual_ranks(world, 79510, dtype)
+    lr = 0.1
+    expected = v["init"].clone()
+    for step in range(1, 3):
+        ops.push_sync_sgd(v["t_pads"], v["t_masters"], v["t_outs"], v["t_grads"], v["bounds"], v["t_gsteps"],
+                          world=world, rank_base=0, local_ranks=world, max_shard_elems=v["shard"],
+                          dtype=dtype, replicas_to_aggregate=R, lr=lr)
+        torch.cuda.synchronize()
+        sel = [r for r in range(world) if R >= world or ((r - step % world) % world) < R]
+        s = torch.zeros_like(expected)
+        for r in sel:                                   # same fixed order as the kernel
+            s += v["grads"][r].float()
+        expected = expected - (lr / min(R, world)) * s
+        for r in range(world):
+            assert torch.equal(v["work"][r], v["work"][0]), "replicas diverged"
+            assert v["gsteps"][r].item() == step
+        if dtype == torch.float32:
+            assert torch.equal(v["work"][0], expected)   # bitwise: fixed reduction order
+        else:
+            got = torch.cat(v["masters"])
+            assert torch.allclose(got, expected, atol=1e-6)
+            assert torch.equal(v["work"][0], got.bfloat16())
+
+
+def test_push_async_and_pull_virtual_ranks(native_lib):
+    from b200ps import ops
+    world = 4
+    v = _virtual_ranks(world, 79510, torch.float32)
+    lr = 0.01
+    for r in range(world):          # each worker pushes once, in any order: updates must all land
+        ops.push_async(v["t_masters"], v["t_grads"], v["bounds"], v["t_gsteps"], world=world, rank_base=r,
+                       total_elems=v["total"], lr=lr)
+    torch.cuda.synchronize()
+    want = v["init"].double()
+    for r in range(world):
+        want = want - lr * v["grads"][r].double()
+    owners = torch.cat([v["work"][r][v["shard"] * r: v["shard"] * (r + 1)] for r in range(world)])
+    assert (owners.double() - want).abs().max().item() < 1e-5        # update conservation
+    assert v["gsteps"][0].item() == world                             # global_step counts every push
+    ops.pull(v["t_masters"], v["t_outs"], v["bounds"], world=world, rank_base=0, local_ranks=world,
+             max_shard_elems=v["shard"], dtype=torch.float32)
+    torch.cuda.synchronize()
+    for r in range(world):
+        assert torch.equal(v["work"][r], owners)
+
+
+def test_barrier_virtual_ranks(native_lib):
+    from b200ps import ops
+    world = 8
+    pads = [torch.zeros(ops.signal_pad_words(), device=DEV, dtype=torch.int32) for _ in range(world)]
+    t = ops.device_ptr_table([p.data_ptr() for p in pads], DEV)
+    for _ in range(3):
+        ops.barrier(t, world=world, rank_base=0, local_ranks=world)
+    torch.cuda.synchronize()
+    assert all(p[97].item() == 3 for p in pads)
