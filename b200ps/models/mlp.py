@@ -1,0 +1,197 @@
+"""MLP models (N5): the MNIST sigmoid MLP of example.py and the wide bf16 stress model.
+
+``SigmoidMLP`` is example.py:77-128: x[.,784] -> sigmoid(x W1 + b1) -> a2 W2 + b2 -> softmax,
+mean cross-entropy, plain SGD; accuracy = mean(argmax == label).  Variable names, shapes and
+creation order follow the checkpoint contract of SURVEY §2.7
+(``weights/Variable`` [784,100], ``weights/Variable_1`` [100,10], ``biases/Variable`` [100],
+``biases/Variable_1`` [10]); weights are stored [in,out] like the reference.
+
+GPU step (per worker), all native kernels:
+    z2   = x W1            tcgen05 tf32 GEMM, split-K with fp32 red.add          (K2/K8)
+    tail = bias+sigmoid, head GEMM, softmax-CE, accuracy, dZ2, dW2, db2, db1     (K6)
+    dW1  = x^T dZ2         tcgen05 tf32 GEMM straight into the push buffer       (K7)
+    push = sync reduce-scatter+SGD+broadcast  |  async peer red.add              (K1/K3)
+Deviation kept from SURVEY §7.1: the loss uses a stable log-softmax instead of the
+reference's ``-sum(y * log(softmax))`` (example.py:98,103), equal wherever that is finite.
+
+``WideMLP`` is BASELINE.json config 4 (8 x 8192 x 8192, bf16, sigmoid, softmax-CE head).
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from .. import ops
+
+
+# --------------------------------------------------------------------------------------
+# plain PyTorch restatement: CPU/gloo mode and the test oracle
+# --------------------------------------------------------------------------------------
+def mlp_reference_step(params: Dict[str, torch.Tensor], x: torch.Tensor, labels: torch.Tensor,
+                       names=("weights/Variable", "weights/Variable_1", "biases/Variable",
+                              "biases/Variable_1"), train: bool = True):
+    """fp32 forward (+ manual backward) of the sigmoid MLP.  Returns (loss, grads, correct)."""
+    w1, w2, b1, b2 = (params[n].float() for n in names)
+    x = x.float()
+    z2 = x @ w1 + b1
+    a2 = torch.sigmoid(z2)
+    z3 = a2 @ w2 + b2
+    logp = torch.log_softmax(z3, dim=1)
+    B = x.shape[0]
+    idx = labels.long()
+    loss = -logp[torch.arange(B), idx].mean()
+    correct = int((z3.argmax(1) == idx).sum().item())
+    if not train:
+        return loss, None, correct
+    dz3 = torch.softmax(z3, dim=1)
+    dz3[torch.arange(B), idx] -= 1.0
+    dz3 /= B
+    grads = {names[1]: a2.t() @ dz3, names[3]: dz3.sum(0)}
+    dz2 = (dz3 @ w2.t()) * a2 * (1 - a2)
+    grads[names[0]] = x.t() @ dz2
+    grads[names[2]] = dz2.sum(0)
+    return loss, grads, correct
+
+
+class SigmoidMLP:
+    W1, W2, B1, B2 = "weights/Variable", "weights/Variable_1", "biases/Variable", "biases/Variable_1"
+
+    def __init__(self, in_dim: int = 784, hidden: int = 100, classes: int = 10, split_k: int = 5):
+        self.in_dim, self.hidden, self.classes = in_dim, hidden, classes
+        self.split_k = split_k
+        self._bufs: Dict[Tuple[int, int], dict] = {}
+
+    # -- variables in the reference's creation order (example.py:70-90) --------------------
+    def register(self, store) -> None:
+        if hasattr(store, "note_untracked_variable"):
+            store.note_untracked_variable("global_step")
+        store.register(self.W1, (self.in_dim, self.hidden), init="normal", stddev=1.0)
+        store.register(self.W2, (self.hidden, self.classes), init="normal", stddev=1.0)
+        store.register(self.B1, (self.hidden,), init="zeros")
+        store.register(self.B2, (self.classes,), init="zeros")
+
+    def names(self):
+        return (self.W1, self.W2, self.B1, self.B2)
+
+    def _buffers(self, batch: int, device, key: int) -> dict:
+        k = (batch, key)
+        if k not in self._bufs:
+            self._bufs[k] = dict(
+                z2=torch.empty(batch, self.hidden, device=device),
+                dz2=torch.empty(batch, self.hidden, device=device),
+                loss=torch.zeros(1, device=device),
+                correct=torch.zeros(1, device=device, dtype=torch.int32))
+        return self._bufs[k]
+
+    # -- GPU path -------------------------------------------------------------------------
+    def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
+                         global_batch: Optional[int] = None):
+        """Forward + backward of one worker's batch; gradients land in ``store.grad(...)``.
+        Returns the (device) loss tensor accumulator and the correct-count tensor."""
+        B = x.shape[0]
+        bufs = self._buffers(B, x.device, 0 if rank is None else rank)
+        z2, dz2, loss, correct = bufs["z2"], bufs["dz2"], bufs["loss"], bufs["correct"]
+        w1 = store.var(self.W1, rank)
+        loss.zero_(); correct.zero_()
+        if self.split_k > 1:
+            z2.zero_()
+            ops.gemm(x, w1, z2, b_mn_major=True, epilogue=ops.EPI_ATOMIC_ADD, split_k=self.split_k)
+        else:
+            ops.gemm(x, w1, z2, b_mn_major=True)
+        ops.mlp_tail(z2, store.var(self.B1, rank), store.var(self.W2, rank), store.var(self.B2, rank),
+                     labels, loss_sum=loss, correct=correct, dz2=dz2, dw2=store.grad(self.W2, rank),
+                     db2=store.grad(self.B2, rank), db1=store.grad(self.B1, rank), train=True,
+                     grad_scale=1.0 / B, loss_scale=1.0 / B)
+        ops.gemm(x, dz2, store.grad(self.W1, rank), a_mn_major=True, b_mn_major=True)
+        return loss, correct
+
+    def evaluate(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None):
+        """Accuracy and mean loss over a (possibly large) batch, e.g. the 10 000-image test set
+        in one call like example.py:187."""
+        B = x.shape[0]
+        z2 = torch.empty(B, self.hidden, device=x.device)
+        loss = torch.zeros(1, device=x.device)
+        correct = torch.zeros(1, device=x.device, dtype=torch.int32)
+        ops.gemm(x, store.var(self.W1, rank), z2, b_mn_major=True)
+        ops.mlp_tail(z2, store.var(self.B1, rank), store.var(self.W2, rank), store.var(self.B2, rank),
+                     labels, loss_sum=loss, correct=correct, train=False, loss_scale=1.0 / B)
+        return correct.item() / B, loss.item()
+
+
+class WideMLP:
+    """``layers`` dense layers of ``hidden x hidden`` (bf16 working copy, fp32 master), sigmoid
+    between layers, softmax cross-entropy over the last layer's ``hidden`` outputs."""
+
+    def __init__(self, layers: int = 8, hidden: int = 8192, fuse_sgd_in_wgrad: bool = True):
+        self.layers, self.hidden = layers, hidden
+        self.fuse_sgd_in_wgrad = fuse_sgd_in_wgrad
+        self._acts = {}
+
+    def wname(self, l: int) -> str:
+        return "weights/Variable" + (f"_{l}" if l else "")
+
+    def bname(self, l: int) -> str:
+        return "biases/Variable" + (f"_{l}" if l else "")
+
+    def register(self, store) -> None:
+        if hasattr(store, "note_untracked_variable"):
+            store.note_untracked_variable("global_step")
+        std = 4.0 / (self.hidden ** 0.5)   # keeps sigmoid layers away from saturation
+        for l in range(self.layers):
+            store.register(self.wname(l), (self.hidden, self.hidden), group="bf16", init="normal", stddev=std)
+        for l in range(self.layers):
+            store.register(self.bname(l), (self.hidden,), group="fp32", init="zeros")
+
+    def flops_per_step(self, batch: int) -> float:
+        """Executed GEMM FLOPs: fwd + wgrad for every layer, dgrad for all but the first."""
+        per = 2.0 * batch * self.hidden * self.hidden
+        return per * (2 * self.layers + (self.layers - 1))
+
+    def _buffers(self, batch: int, device, key: int):
+        k = (batch, key)
+        if k not in self._acts:
+            D = self.hidden
+            self._acts[k] = dict(
+                acts=[torch.empty(batch, D, device=device, dtype=torch.bfloat16) for _ in range(self.layers + 1)],
+                dz=[torch.empty(batch, D, device=device, dtype=torch.bfloat16) for _ in range(2)],
+                loss=torch.zeros(1, device=device), correct=torch.zeros(1, device=device, dtype=torch.int32))
+        return self._acts[k]
+
+    def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
+                         lr: float = 0.0, local_sgd: bool = False):
+        """One worker's forward/backward.  With ``local_sgd`` (world == 1) the weight update is
+        fused into the wgrad GEMM's epilogue (master -= lr*dW, bf16 copy refreshed) so the
+        1 GB gradient never touches HBM; otherwise gradients go to the symmetric push buffer."""
+        B, L = x.shape[0], self.layers
+        bufs = self._buffers(B, x.device, 0 if rank is None else rank)
+        acts, dzs, loss, correct = bufs["acts"], bufs["dz"], bufs["loss"], bufs["correct"]
+        loss.zero_(); correct.zero_()
+        a = x
+        for l in range(L):
+            out = acts[l + 1]
+            ops.gemm(a, store.var(self.wname(l), rank), out, b_mn_major=True,
+                     bias=store.var(self.bname(l), rank),
+                     act=ops.ACT_SIGMOID if l < L - 1 else ops.ACT_NONE)
+            a = out
+        dz = dzs[0]
+        ops.softmax_ce(acts[L], labels, dlogits=dz, loss_sum=loss, correct=correct,
+                       grad_scale=1.0 / B, loss_scale=1.0 / B)
+        for l in range(L - 1, -1, -1):
+            a_in = x if l == 0 else acts[l]
+            w = store.var(self.wname(l), rank)
+            ops.colsum(dz, store.grad(self.bname(l), rank))
+            dz_prev = None
+            if l > 0:   # dgrad first: it must see the pre-update weights
+                dz_prev = dzs[1] if dz is dzs[0] else dzs[0]
+                ops.gemm(dz, w, dz_prev, dsigmoid_of=acts[l])
+            if local_sgd:
+                g = store.groups["bf16"]
+                lo = g.layout.offsets[self.wname(l)] - g.layout.bounds[store.pool.local_ranks[0]]
+                master = g.master.view(store.pool.local_ranks[0], torch.float32)[lo: lo + w.numel()].view_as(w)
+                ops.gemm(a_in, dz, a_mn_major=True, b_mn_major=True, epilogue=ops.EPI_SGD,
+                         sgd_master=master, sgd_lowp=w, sgd_lr=lr)
+            else:
+                ops.gemm(a_in, dz, store.grad(self.wname(l), rank), a_mn_major=True, b_mn_major=True)
+            dz = dz_prev
+        return loss, correct

@@ -188,12 +188,12 @@ def synth_sparse(row_ptr, fid, fval, labels, *, nnz_mean, spread, features, skew
           "synth_sparse")
 
 
-def init_normal(out, *, mean=0.0, stddev=1.0, seed=1, stream_id=0, stream=None):
+def init_normal(out, *, mean=0.0, stddev=1.0, seed=1, stream_id=0, elem_offset=0, stream=None):
     _cuda(out)
     if out.dtype != torch.float32 or not out.is_contiguous():
         raise TypeError("init_normal: contiguous fp32 only")
     check(native.load().b200ps_init_normal(ptr(out), out.numel(), mean, stddev, seed, stream_id,
-                                           stream_ptr(stream)), "init_normal")
+                                           elem_offset, stream_ptr(stream)), "init_normal")
 
 
 def cast_f32_bf16(src, dst, stream=None):

@@ -1,0 +1,2 @@
+from .adam import Adam  # noqa: F401
+from .sgd import AsyncSGD, SyncReplicasSGD  # noqa: F401

@@ -1,0 +1,90 @@
+"""Process context: who am I, which GPU do I drive, how do I reach my peers.
+
+Control plane = ``torch.distributed`` (gloo over 127.0.0.1/TCP) — used only to bootstrap
+(exchange CUDA IPC handles, ready/done barriers, checkpoint broadcast).  Data plane =
+symmetric memory + the kernels of libb200ps.so; NCCL is never called on b200ps's own paths
+(the PyTorch+NCCL baseline lives in ``baseline/ps_nccl.py``).
+
+Launch conventions understood by :func:`init_from_env`:
+* ``torchrun`` / ``python -m torch.distributed.run`` (RANK, LOCAL_RANK, WORLD_SIZE, MASTER_*),
+* a single process (world = 1),
+* ``virtual_world=N``: one process emulating N ranks on one device (tests).
+"""
+from __future__ import annotations
+
+import datetime
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .symm import SymmPool
+
+
+@dataclass
+class Context:
+    rank: int
+    world: int
+    device: torch.device
+    pool: SymmPool
+    group: Optional[object] = None       # gloo control-plane group (None when single process)
+    virtual: bool = False
+
+    @property
+    def is_chief(self) -> bool:
+        return self.rank == 0
+
+    def control_barrier(self, timeout_s: float = 120.0) -> None:
+        if self.group is not None:
+            import torch.distributed as dist
+            dist.monitored_barrier(group=self.group, timeout=datetime.timedelta(seconds=timeout_s))
+
+    def all_reduce_max(self, value: float) -> float:
+        """Max of a host scalar over the ranks (used for max-over-ranks device timings)."""
+        if self.group is None:
+            return float(value)
+        import torch.distributed as dist
+        t = torch.tensor([float(value)], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return float(t.item())
+
+    def all_reduce_sum(self, value: float) -> float:
+        if self.group is None:
+            return float(value)
+        import torch.distributed as dist
+        t = torch.tensor([float(value)], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return float(t.item())
+
+    def close(self) -> None:
+        self.pool.close()
+
+
+def init_from_env(virtual_world: int = 0, device: Optional[str] = None, timeout_s: float = 300.0) -> Context:
+    if virtual_world and virtual_world > 0:
+        dev = torch.device(device or ("cuda:0" if torch.cuda.is_available() else "cpu"))
+        if dev.type == "cuda":
+            torch.cuda.set_device(dev)
+        return Context(0, virtual_world, dev, SymmPool(0, virtual_world, dev, virtual=True), None, True)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if torch.cuda.is_available():
+        dev = torch.device(device or f"cuda:{local_rank % torch.cuda.device_count()}")
+        torch.cuda.set_device(dev)
+    else:
+        dev = torch.device("cpu")
+    if world == 1:
+        return Context(0, 1, dev, SymmPool(0, 1, dev, virtual=True), None, False)
+    import torch.distributed as dist
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29512")
+    if not dist.is_initialized():
+        dist.init_process_group("gloo", rank=rank, world_size=world,
+                                timeout=datetime.timedelta(seconds=timeout_s))
+        group = dist.group.WORLD
+    else:
+        # someone (e.g. the NCCL baseline) already owns the default group: add a gloo one
+        group = dist.new_group(backend="gloo", timeout=datetime.timedelta(seconds=timeout_s))
+    return Context(rank, world, dev, SymmPool(rank, world, dev, group=group), group, False)

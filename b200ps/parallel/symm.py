@@ -1,0 +1,131 @@
+"""Symmetric memory (N1): the same buffer on every rank, mapped into every rank's address space.
+
+This is what replaces the per-task gRPC server of the reference (``tf.train.Server``,
+example.py:38-40, lr2.py:331): a worker does not *connect* to the parameter server, it *maps*
+every shard, and the kernels in ``csrc/kernels/ps_comm.cu`` move the bytes over NVLink.
+
+* multi-process (one process per GPU): ``cudaMalloc`` + CUDA IPC handles, exchanged once over
+  the control-plane process group (gloo) — ``b200ps_symm_alloc/open`` in ``csrc/symm/symm.cu``;
+* single process: ``world`` *virtual ranks* on one device (all "peer" pointers are local) —
+  the configuration every multi-rank kernel is unit-tested in, and the degenerate world=1
+  case of a single-GPU run.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from ..ops import native
+
+
+class _RawCudaBuffer:
+    """Exposes a raw device address to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int, owner=None):
+        self.ptr, self.nbytes, self._owner = int(ptr), int(nbytes), owner
+        self.__cuda_array_interface__ = {
+            "shape": (self.nbytes,), "typestr": "|u1", "data": (self.ptr, False), "version": 2,
+            "strides": None,
+        }
+
+
+def tensor_from_ptr(ptr: int, nbytes: int, device, owner=None) -> torch.Tensor:
+    """uint8 tensor aliasing ``nbytes`` of device memory at ``ptr`` (no ownership transfer)."""
+    holder = _RawCudaBuffer(ptr, nbytes, owner)
+    t = torch.as_tensor(holder, device=device)
+    t._b200ps_holder = holder  # keep the holder (and its owner) alive with the tensor
+    return t
+
+
+@dataclass
+class SymmBuffer:
+    """One symmetric allocation: ``nbytes`` on every rank."""
+    name: str
+    nbytes: int
+    ptrs: List[int]                 # address of every rank's copy, valid in THIS process
+    local: List[torch.Tensor]       # uint8 views of the copies this process owns (1 per local rank)
+    local_ranks: List[int]
+
+    def view(self, rank: int, dtype: torch.dtype, offset_bytes: int = 0, numel: Optional[int] = None):
+        """Typed tensor over the copy of local rank ``rank``."""
+        i = self.local_ranks.index(rank)
+        esz = torch.empty((), dtype=dtype).element_size()
+        if numel is None:
+            numel = (self.nbytes - offset_bytes) // esz
+        return self.local[i][offset_bytes: offset_bytes + numel * esz].view(dtype)
+
+
+class SymmPool:
+    """Allocator of symmetric buffers for a group of ``world`` ranks.
+
+    ``rank`` is this process's rank; with ``virtual=True`` this single process plays all
+    ``world`` ranks on one device.
+    """
+
+    def __init__(self, rank: int, world: int, device, group=None, virtual: bool = False):
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        self.group = group
+        self.virtual = virtual or world == 1
+        self.local_ranks = list(range(world)) if self.virtual else [rank]
+        self._buffers = []
+        self._opened: List[int] = []
+        self._owned: List[int] = []
+        if not self.virtual and group is None:
+            raise ValueError("multi-process symmetric memory needs a control-plane process group")
+
+    def alloc(self, name: str, nbytes: int) -> SymmBuffer:
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        if self.virtual:
+            local = [torch.zeros(nbytes, dtype=torch.uint8, device=self.device) for _ in self.local_ranks]
+            buf = SymmBuffer(name, nbytes, [t.data_ptr() for t in local], local, list(self.local_ranks))
+            self._buffers.append(buf)
+            return buf
+        import torch.distributed as dist
+        lib = native.load()
+        with torch.cuda.device(self.device):
+            ptr = C.c_void_p()
+            handle = (C.c_ubyte * 64)()
+            native.check(lib.b200ps_symm_alloc(nbytes, C.byref(ptr), handle), "symm_alloc")
+        self._owned.append(ptr.value)
+        handles: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=self.group)
+        ptrs = []
+        with torch.cuda.device(self.device):
+            for r in range(self.world):
+                if r == self.rank:
+                    ptrs.append(ptr.value)
+                    continue
+                p = C.c_void_p()
+                hb = (C.c_ubyte * 64).from_buffer_copy(handles[r])
+                native.check(lib.b200ps_symm_open(hb, C.byref(p)), f"symm_open(rank {r})")
+                self._opened.append(p.value)
+                ptrs.append(p.value)
+        local = [tensor_from_ptr(ptr.value, nbytes, self.device, owner=self)]
+        buf = SymmBuffer(name, nbytes, ptrs, local, [self.rank])
+        self._buffers.append(buf)
+        dist.barrier(group=self.group)   # every rank has mapped every copy before first use
+        return buf
+
+    def close(self):
+        if self.virtual:
+            self._buffers.clear()
+            return
+        lib = native.load()
+        torch.cuda.synchronize(self.device)
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                lib.b200ps_symm_close(p)
+            self._opened.clear()
+            if self.group is not None:
+                import torch.distributed as dist
+                try:
+                    dist.barrier(group=self.group)  # nobody still maps our memory
+                except Exception:
+                    pass
+            for p in self._owned:
+                lib.b200ps_symm_free(p)
+            self._owned.clear()
+        self._buffers.clear()

@@ -1,0 +1,226 @@
+"""Training engines: the public step API of the GPU path.
+
+A *trainer* owns a ParameterStore, a model and a replica optimizer, and exposes
+
+    trainer.step(x, labels)            # inputs already on the device (or None = reuse)
+    trainer.step_from_host(x, labels)  # pinned host inputs -> H2D -> step -> loss back on the host
+
+The step body (pull/prepare, forward, backward, push/apply) is launch-bound for the small
+models, so after a warm-up it is captured once into a CUDA graph and replayed; all kernels
+in it are native (libb200ps.so).  Cross-rank synchronisation lives inside the push kernel,
+so a replay needs no host-side collective.
+
+Mirrors the worker loop of example.py:158-184 / lr2.py:434-451 minus the per-step host
+fetches: the loss stays on the device unless the caller asks for it.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from .models.mlp import SigmoidMLP, WideMLP
+from .models.sparse_lr import SparseLR
+from .optim.sgd import AsyncSGD, SyncReplicasSGD
+from .ps.store import ParameterStore
+
+
+class _GraphedStep:
+    """Warm up eagerly, then capture ``body`` into a CUDA graph and replay it."""
+
+    def __init__(self, body, device, use_graph: bool, warmup: int = 2):
+        self.body, self.device = body, device
+        self.use_graph = use_graph and device.type == "cuda"
+        self.warmup, self.calls, self.graph = warmup, 0, None
+
+    def __call__(self):
+        if not self.use_graph:
+            self.body()
+            return
+        if self.graph is None:
+            if self.calls < self.warmup:
+                self.calls += 1
+                self.body()
+                return
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.body()
+            self.graph = g
+        self.graph.replay()
+
+
+class _TrainerBase:
+    def __init__(self, ctx, mode: str, lr: float, replicas_to_aggregate: Optional[int], placement: str,
+                 seed: int):
+        self.ctx = ctx
+        self.device = ctx.device
+        self.mode = mode
+        self.lr = float(lr)
+        self.store = ParameterStore(ctx.pool, placement=placement, seed=seed)
+        if mode == "sync":
+            self.opt = SyncReplicasSGD(lr, replicas_to_aggregate, ctx.world)
+        elif mode == "async":
+            self.opt = AsyncSGD(lr)
+        else:
+            raise ValueError("mode must be 'sync' or 'async'")
+        self.local_ranks = list(ctx.pool.local_ranks)
+        self.local_step = 0
+        self._loss_host = torch.zeros(1).pin_memory() if self.device.type == "cuda" else torch.zeros(1)
+
+    @property
+    def global_step(self) -> int:
+        return self.store.global_step
+
+    def read_loss(self) -> float:
+        """Device -> pinned host copy of the last step's loss (synchronises the stream)."""
+        self._loss_host.copy_(self.last_loss, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(self._loss_host.item())
+
+    def close(self):
+        self.ctx.close()
+
+
+class MLPTrainer(_TrainerBase):
+    """MNIST sigmoid MLP (example.py) under sync or async PS updates."""
+
+    def __init__(self, ctx, batch_size: int = 100, lr: float = 0.0005, mode: str = "sync",
+                 replicas_to_aggregate: Optional[int] = None, placement: str = "flat_shard",
+                 seed: int = 1, use_graph: bool = True, model: Optional[SigmoidMLP] = None):
+        super().__init__(ctx, mode, lr, replicas_to_aggregate, placement, seed)
+        self.model = model or SigmoidMLP()
+        self.batch_size = batch_size
+        self.model.register(self.store)
+        self.store.build()
+        self.store.initialize()
+        dev = self.device
+        self.x = {r: torch.zeros(batch_size, self.model.in_dim, device=dev) for r in self.local_ranks}
+        self.labels = {r: torch.zeros(batch_size, device=dev, dtype=torch.int32) for r in self.local_ranks}
+        self._losses = {}
+        self._corrects = {}
+        self._step = _GraphedStep(self._body, dev, use_graph)
+        if ctx.group is not None:
+            ctx.control_barrier()
+
+    def _body(self):
+        st = self.store
+        self.opt.prepare(st)
+        for r in self.local_ranks:
+            loss, correct = self.model.forward_backward(st, self.x[r], self.labels[r], rank=r)
+            self._losses[r], self._corrects[r] = loss, correct
+            if self.mode == "async":
+                self.opt.apply(st, rank=r)
+        if self.mode == "sync":
+            self.opt.apply(st)
+
+    @property
+    def last_loss(self) -> torch.Tensor:
+        return self._losses[self.local_ranks[0]]
+
+    @property
+    def last_correct(self) -> torch.Tensor:
+        return self._corrects[self.local_ranks[0]]
+
+    def step(self, x: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None, rank=None):
+        r = self.local_ranks[0] if rank is None else rank
+        if x is not None:
+            self.x[r].copy_(x, non_blocking=True)
+        if labels is not None:
+            self.labels[r].copy_(labels, non_blocking=True)
+        self._step()
+        self.local_step += 1
+
+    def step_from_host(self, x_pinned: torch.Tensor, labels_pinned: torch.Tensor) -> float:
+        """The end-to-end call: pinned host batch in, loss (python float) out."""
+        self.step(x_pinned, labels_pinned)
+        return self.read_loss()
+
+    def evaluate(self, x: torch.Tensor, labels: torch.Tensor):
+        return self.model.evaluate(self.store, x, labels, rank=self.local_ranks[0])
+
+
+class WideMLPTrainer(_TrainerBase):
+    """BASELINE.json config 4: 8 x 8192 x 8192 bf16 sigmoid MLP, synchronous PS."""
+
+    def __init__(self, ctx, batch_size: int = 4096, layers: int = 8, hidden: int = 8192, lr: float = 0.01,
+                 replicas_to_aggregate: Optional[int] = None, seed: int = 1, use_graph: bool = True):
+        super().__init__(ctx, "sync", lr, replicas_to_aggregate, "flat_shard", seed)
+        self.model = WideMLP(layers, hidden)
+        self.batch_size = batch_size
+        self.model.register(self.store)
+        self.store.build()
+        self.store.initialize()
+        dev = self.device
+        self.x = {r: torch.zeros(batch_size, hidden, device=dev, dtype=torch.bfloat16) for r in self.local_ranks}
+        self.labels = {r: torch.zeros(batch_size, device=dev, dtype=torch.int32) for r in self.local_ranks}
+        self._losses, self._corrects = {}, {}
+        self.local_sgd = ctx.world == 1
+        self._step = _GraphedStep(self._body, dev, use_graph)
+        if ctx.group is not None:
+            ctx.control_barrier()
+
+    def _body(self):
+        st = self.store
+        for r in self.local_ranks:
+            loss, correct = self.model.forward_backward(st, self.x[r], self.labels[r], rank=r, lr=self.lr,
+                                                        local_sgd=self.local_sgd)
+            self._losses[r], self._corrects[r] = loss, correct
+        if self.local_sgd:
+            st.push_sync(self.lr, groups=("fp32",))            # biases; weights were fused into wgrad
+        else:
+            st.push_sync(self.lr, self.opt.replicas_to_aggregate)
+
+    @property
+    def last_loss(self) -> torch.Tensor:
+        return self._losses[self.local_ranks[0]]
+
+    def step(self, x=None, labels=None, rank=None):
+        r = self.local_ranks[0] if rank is None else rank
+        if x is not None:
+            self.x[r].copy_(x, non_blocking=True)
+        if labels is not None:
+            self.labels[r].copy_(labels, non_blocking=True)
+        self._step()
+        self.local_step += 1
+
+    def step_from_host(self, x_pinned, labels_pinned) -> float:
+        self.step(x_pinned, labels_pinned)
+        return self.read_loss()
+
+
+class SparseLRTrainer(_TrainerBase):
+    """lr2.py's trainer over a row-sharded weight: async (default, like the reference) or sync."""
+
+    def __init__(self, ctx, features: int, lr: float = 0.001, mode: str = "async",
+                 placement: str = "flat_shard", seed: int = 1):
+        super().__init__(ctx, mode, lr, None, placement, seed)
+        self.model = SparseLR(features)
+        self.model.register(self.store)
+        self.store.build()
+        self.store.initialize()
+        self._last = None
+        if ctx.group is not None:
+            ctx.control_barrier()
+
+    @property
+    def last_loss(self) -> torch.Tensor:
+        return self._last
+
+    def step(self, batch, rank=None):
+        """``batch`` = (row_ptr int32[B+1], fid int64[nnz], fval f32[nnz], labels f32[B]) on the device."""
+        if self.mode == "async":
+            self._last = self.model.step_async(self.store, batch, self.lr, rank=rank)
+        else:
+            self._last = self.model.step_sync(self.store, batch, self.lr, rank=rank)
+        self.local_step += 1
+
+    def step_from_host(self, batch_pinned, dev_bufs) -> float:
+        for src, dst in zip(batch_pinned, dev_bufs):
+            dst[: src.numel()].copy_(src, non_blocking=True)
+        n = batch_pinned[3].numel()
+        self.step((dev_bufs[0][: n + 1], dev_bufs[1], dev_bufs[2], dev_bufs[3][:n]))
+        return self.read_loss()
+
+    def predict(self, batch):
+        return self.model.predict(self.store, batch)

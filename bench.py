@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""Headline benchmark (driver contract in the task statement).
+
+    python bench.py --gpus N --steps K --warmup W [--config mnist_mlp_sync] [--impl b200ps]
+
+N > 1 is launched by the driver as ``python -m torch.distributed.run --nproc-per-node N ...
+bench.py --gpus N ...`` (one rank per GPU).  Rank 0 prints ONE JSON line.
+
+Metric (BASELINE.json): examples/sec, device-timed with CUDA events, max over ranks, weak
+scaling (fixed per-GPU batch).  Primary config = BASELINE.json config 2, the reference's own
+workload: example.py's MNIST 784-100-10 sigmoid MLP, batch 100 per worker, synchronous
+parameter-server updates.  ``extra`` carries the other configs measured by the same rules
+(async MLP, sparse LR, wide bf16 MLP).  Inputs: a device-resident synthetic epoch
+(55 000 x 784 fp32 = 172 MB > the 126 MB L2) streamed batch by batch, so every step's inputs
+come from HBM.  ``e2e`` repeats the measurement through the public trainer API with the
+batch starting in pinned host memory and the loss read back to the host every step.
+
+``--impl reference``: the unmodified reference cannot run here (TensorFlow 0.8-0.12 on
+Python 2, not installable offline) -> prints {"impl":"reference","unavailable":..}.
+``--impl baseline``: the PyTorch+NCCL(+cuBLAS) implementation of the same PS semantics
+(baseline/ps_nccl.py) — BASELINE.md's fallback baseline — measured by the same protocol.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MNIST_TRAIN = 55000
+
+
+# ----------------------------------------------------------------------------------------
+# clocks sampled DURING the timed regions (NVML, background thread)
+# ----------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, device_index: int):
+        self.samples, self.reasons, self._stop = [], set(), threading.Event()
+        self.max_mhz = None
+        self.active = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+        }
+        while not self._stop.is_set():
+            if self.active.is_set():
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for k, bit in names.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+            else:
+                time.sleep(0.0005)
+
+    def start(self):
+        if self.nv is not None:
+            self.t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.nv is not None and self.t.is_alive():
+            self.t.join(timeout=2)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "samples": len(s), "reasons": sorted(self.reasons)}
+
+
+def _physical_gpu_index(local_index: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_index])
+        except Exception:
+            return local_index
+    return local_index
+
+
+# ----------------------------------------------------------------------------------------
+# measurement helpers
+# ----------------------------------------------------------------------------------------
+def timed_region(ctx, torch, sampler, steps, fn):
+    """barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks."""
+    ctx.control_barrier()
+    torch.cuda.synchronize()
+    st, en = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active.set()
+    st.record()
+    for i in range(steps):
+        fn(i)
+    en.record()
+    torch.cuda.synchronize()
+    sampler.active.clear()
+    ms = st.elapsed_time(en)
+    ctx.control_barrier()
+    return ctx.all_reduce_max(ms)
+
+
+def wall_region(ctx, torch, sampler, steps, fn):
+    ctx.control_barrier()
+    torch.cuda.synchronize()
+    sampler.active.set()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        fn(i)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    sampler.active.clear()
+    ctx.control_barrier()
+    return ctx.all_reduce_max(ms)
+
+
+def launches_of(fn, native):
+    a = native.launch_count()
+    fn()
+    return native.launch_count() - a
+
+
+# ----------------------------------------------------------------------------------------
+# configs (b200ps arm)
+# ----------------------------------------------------------------------------------------
+def bench_mnist(ctx, args, sampler, mode):
+    import torch
+    from b200ps import ops
+    from b200ps.ops import native
+    from b200ps.train import MLPTrainer
+    B = 100
+    tr = MLPTrainer(ctx, batch_size=B, lr=0.0005, mode=mode, use_graph=not args.no_graph)
+    dev = ctx.device
+    n_batches = MNIST_TRAIN // B
+    data = torch.empty(MNIST_TRAIN, 784, device=dev)
+    labels = torch.empty(MNIST_TRAIN, device=dev, dtype=torch.int32)
+    ops.synth_mnist(data, labels, seed=1, offset=ctx.rank * MNIST_TRAIN)   # worker-sharded epoch
+    xs, ys = data.view(n_batches, B, 784), labels.view(n_batches, B)
+
+    # launches per step, counted on an eager (pre-capture) step of the very same body
+    tr.step(xs[0], ys[0])
+    per_step = launches_of(lambda: tr.step(xs[1], ys[1]), native)
+    for i in range(3):                       # graph capture happens here
+        tr.step(xs[2 + i], ys[2 + i])
+    loss0 = tr.read_loss()
+
+    def dev_step(i):
+        j = i % n_batches
+        tr.step(xs[j], ys[j])
+
+    for i in range(max(args.warmup, 3)):
+        dev_step(i)
+    ms = timed_region(ctx, torch, sampler, args.steps, dev_step)
+    loss1 = tr.read_loss()
+
+    # ---- end to end: pinned host batch -> H2D -> step -> loss D2H, every step
+    ring = min(64, n_batches)
+    hx = xs[:ring].cpu().pin_memory()
+    hy = ys[:ring].cpu().pin_memory()
+
+    def e2e_step(i):
+        tr.step_from_host(hx[i % ring], hy[i % ring])
+
+    for i in range(max(args.warmup, 3)):
+        e2e_step(i)
+    ms_e2e = wall_region(ctx, torch, sampler, args.steps, e2e_step)
+    acc, test_loss = tr.evaluate(data[:10000], labels[:10000])
+    gstep = tr.global_step
+    out = {
+        "value": B * ctx.world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
+        "gpu_launches": per_step * args.steps, "launches_per_step": per_step,
+        "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
+                "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 4},
+        "loss_first": loss0, "loss_last": loss1, "train_subset_accuracy": acc, "global_step": gstep,
+        "config": {"model": "mnist_sigmoid_mlp_784_100_10", "global_batch": B * ctx.world,
+                   "per_gpu_batch": B, "seq_len": None, "mode": mode,
+                   "parallelism": f"dp{ctx.world}+ps_shard{ctx.world}", "lr": 0.0005,
+                   "inputs": "device-resident synthetic epoch 55000x784 fp32 (172 MB > 126 MB L2), "
+                             "streamed sequentially; no explicit L2 flush",
+                   "cuda_graph": not args.no_graph},
+    }
+    tr.store  # keep alive until here
+    return out
+
+
+def bench_wide(ctx, args, sampler):
+    import torch
+    from b200ps import ops
+    from b200ps.ops import native
+    from b200ps.train import WideMLPTrainer
+    B, L, D = args.wide_batch, args.wide_layers, args.wide_hidden
+    tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.01, use_graph=not args.no_graph)
+    dev = ctx.device
+    ring = 4                                   # 4 x 64 MB input batches: inputs + 1 GB weights >> L2
+    xs = torch.empty(ring, B, D, device=dev, dtype=torch.bfloat16)
+    ys = torch.empty(ring, B, device=dev, dtype=torch.int32)
+    for i in range(ring):
+        ops.synth_dense_bf16(xs[i], ys[i], classes=D, seed=3, offset=(ctx.rank * ring + i) * B)
+    tr.step(xs[0], ys[0])
+    per_step = launches_of(lambda: tr.step(xs[1], ys[1]), native)
+    for i in range(3):
+        tr.step(xs[i % ring], ys[i % ring])
+    loss0 = tr.read_loss()
+    steps = max(1, min(args.steps, args.wide_max_steps))
+
+    def dev_step(i):
+        tr.step(xs[i % ring], ys[i % ring])
+
+    for i in range(3):
+        dev_step(i)
+    ms = timed_region(ctx, torch, sampler, steps, dev_step)
+    loss1 = tr.read_loss()
+    hx, hy = xs[:2].cpu().pin_memory(), ys[:2].cpu().pin_memory()
+
+    def e2e_step(i):
+        tr.step_from_host(hx[i % 2], hy[i % 2])
+
+    e2e_step(0)
+    ms_e2e = wall_region(ctx, torch, sampler, steps, e2e_step)
+    flops = tr.model.flops_per_step(B)
+    peak = _measured_peaks().get("bf16_tflops_sustained")
+    tf = flops / (ms / steps / 1e3) / 1e12
+    return {
+        "value": B * ctx.world * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
+        "gpu_launches": per_step * steps, "launches_per_step": per_step,
+        "tflops_per_gpu": tf, "fraction_of_measured_bf16_sustained": (tf / peak) if peak else None,
+        "e2e": {"value": B * ctx.world * steps / (ms_e2e / 1e3), "unit": "examples/s",
+                "h2d_bytes_per_step": B * D * 2 + B * 4, "d2h_bytes_per_step": 4},
+        "loss_first": loss0, "loss_last": loss1,
+        "config": {"model": f"wide_sigmoid_mlp_{L}x{D}", "global_batch": B * ctx.world, "per_gpu_batch": B,
+                   "dtype": "bf16 (fp32 master, fp32 accumulate)", "mode": "sync",
+                   "parallelism": f"dp{ctx.world}+ps_shard{ctx.world}",
+                   "inputs": f"ring of {ring} device batches; 1.07 GB of weights per step >> L2"},
+    }
+
+
+def bench_sparse(ctx, args, sampler, mode="async"):
+    import torch
+    from b200ps import ops
+    from b200ps.ops import native
+    from b200ps.train import SparseLRTrainer
+    F, B, nnz, spread = 1 << 24, args.sparse_batch, 100, 20
+    tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
+    dev = ctx.device
+    ring = 64
+    cap = B * (nnz + spread)
+    batches = []
+    for i in range(ring):
+        rp = torch.empty(B + 1, device=dev, dtype=torch.int32)
+        fid = torch.empty(cap, device=dev, dtype=torch.int64)
+        fv = torch.empty(cap, device=dev)
+        y = torch.empty(B, device=dev)
+        ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=5,
+                         offset=(ctx.rank * ring + i) * B)
+        batches.append((rp, fid, fv, y))
+    per_step = launches_of(lambda: tr.step(batches[0]), native)
+    for i in range(max(args.warmup, 3)):
+        tr.step(batches[i % ring])
+    loss0 = tr.read_loss()
+    ms = timed_region(ctx, torch, sampler, args.steps, lambda i: tr.step(batches[i % ring]))
+    loss1 = tr.read_loss()
+    host = [tuple(t.cpu().pin_memory() for t in batches[i]) for i in range(4)]
+    dev_bufs = (torch.empty(B + 1, device=dev, dtype=torch.int32), torch.empty(cap, device=dev, dtype=torch.int64),
+                torch.empty(cap, device=dev), torch.empty(B, device=dev))
+    tr.step_from_host(host[0], dev_bufs)
+    ms_e2e = wall_region(ctx, torch, sampler, args.steps, lambda i: tr.step_from_host(host[i % 4], dev_bufs))
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    return {
+        "value": B * ctx.world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
+        "gpu_launches": per_step * args.steps, "launches_per_step": per_step,
+        "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "loss_first": loss0, "loss_last": loss1, "global_step": tr.global_step,
+        "config": {"model": "sparse_lr_2^24_features_~100nnz", "global_batch": B * ctx.world,
+                   "per_gpu_batch": B, "mode": mode, "parallelism": f"dp{ctx.world}+row_shard{ctx.world}",
+                   "inputs": f"ring of {ring} device CSR batches; 64 MB weight vector, random rows"},
+    }
+
+
+def _measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def _baseline_number(config: str, n: int):
+    try:
+        d = json.load(open(os.path.join(ROOT, "baseline", "measured.json")))
+        return d.get(config, {}).get(str(n))
+    except Exception:
+        return None
+
+
+# ----------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200ps", choices=["b200ps", "reference", "baseline"])
+    ap.add_argument("--config", default="all",
+                    choices=["all", "mnist_mlp_sync", "mnist_mlp_async", "wide_mlp", "sparse_lr"])
+    ap.add_argument("--no-graph", dest="no_graph", action="store_true")
+    ap.add_argument("--wide-batch", dest="wide_batch", type=int, default=4096)
+    ap.add_argument("--wide-layers", dest="wide_layers", type=int, default=8)
+    ap.add_argument("--wide-hidden", dest="wide_hidden", type=int, default=8192)
+    ap.add_argument("--wide-max-steps", dest="wide_max_steps", type=int, default=20)
+    ap.add_argument("--sparse-batch", dest="sparse_batch", type=int, default=500)
+    args = ap.parse_args()
+
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "reference = Python-2 scripts on TensorFlow 0.8-0.12; no installable "
+                                         "artefact in /root/reference and no TensorFlow wheel offline "
+                                         "(pip install attempt recorded in DESIGN.md)"}))
+        return 0
+    if args.impl == "baseline":
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import ps_nccl
+        return ps_nccl.main_from_bench(args)
+
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: bench.py measures the GPU path only"}))
+        return 1
+    import build as _build
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        _build.build(quiet=True)
+    from b200ps.ops import native
+    from b200ps.parallel.context import init_from_env
+    ctx = init_from_env()
+    if ctx.world != args.gpus and ctx.rank == 0:
+        print(f"[bench] note: --gpus {args.gpus} but WORLD_SIZE={ctx.world}", file=sys.stderr)
+    native.load()
+    sampler = ClockSampler(_physical_gpu_index(ctx.device.index or 0))
+    sampler.start()
+
+    primary_name = "mnist_mlp_sync" if args.config == "all" else args.config
+    runners = {
+        "mnist_mlp_sync": lambda: bench_mnist(ctx, args, sampler, "sync"),
+        "mnist_mlp_async": lambda: bench_mnist(ctx, args, sampler, "async"),
+        "wide_mlp": lambda: bench_wide(ctx, args, sampler),
+        "sparse_lr": lambda: bench_sparse(ctx, args, sampler, "async"),
+    }
+    primary = runners[primary_name]()
+    extra = {}
+    if args.config == "all":
+        for name in ("mnist_mlp_async", "sparse_lr", "wide_mlp"):
+            try:
+                extra[name] = runners[name]()
+            except Exception as e:  # an extra config must never cost the headline line
+                extra[name] = {"error": f"{type(e).__name__}: {e}"}
+    sampler.stop()
+    if ctx.rank == 0:
+        base = _baseline_number(primary_name, ctx.world)
+        line = {
+            "metric": "examples/sec (device-timed, max over ranks)", "value": primary["value"],
+            "unit": "examples/s", "n_gpus": ctx.world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": primary["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (primary["value"] / base) if base else None,
+            "dtype": "tf32 tensor-core math on fp32 storage (fp32 master/accumulate)"
+                     if primary_name.startswith("mnist") else "bf16",
+            "data": "synthetic (on-device Philox generators), random-init weights",
+            "config": primary["config"], "clocks": sampler.summary(), "e2e": primary["e2e"],
+            "gpu_launches": primary["gpu_launches"], "impl": "b200ps",
+            "detail": {k: v for k, v in primary.items() if k not in ("value", "ms_per_step", "config", "e2e",
+                                                                     "gpu_launches")},
+            "extra": extra,
+        }
+        for name, ex in extra.items():
+            b = _baseline_number(name, ctx.world)
+            if b and "value" in ex:
+                ex["vs_baseline"] = ex["value"] / b
+        print(json.dumps(line))
+        sys.stdout.flush()
+    ctx.control_barrier()
+    os._exit(0)   # skip CUDA IPC teardown ordering issues at interpreter exit
+
+
+if __name__ == "__main__":
+    sys.exit(main())

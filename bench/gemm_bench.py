@@ -25,7 +25,7 @@ def timeit(fn, iters=20, warm=5):
 def main():
     dev = "cuda"
     out = []
-    for (M, N, K) in [(4096, 8192, 8192), (8192, 8192, 4096), (2048, 2048, 2048), (100, 100, 784)]:
+    for (M, N, K) in [(4096, 8192, 8192), (8192, 8192, 4096), (2048, 2048, 2048), (1024, 8192, 8192)]:
         for name, a_mn, b_mn in [("fwd  A[M,K] B[K,N]", False, True), ("dgrad A[M,K] B[N,K]", False, False),
                                  ("wgrad A[K,M] B[K,N]", True, True)]:
             a = torch.randn((K, M) if a_mn else (M, K), device=dev).bfloat16()

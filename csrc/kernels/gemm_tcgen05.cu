@@ -139,6 +139,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     const uint32_t b_lbo = p.b_mn ? BLOCK_K * kRowBytes : 16;
     const uint32_t a_kstep = p.a_mn ? UMMA_K * kRowBytes : 32;  // bytes per UMMA_K advance
     const uint32_t b_kstep = p.b_mn ? UMMA_K * kRowBytes : 32;
+    // MN-major tf32 must use the 128B swizzle with 32-byte atoms (4 k-rows per atom => the
+    // two 4-row groups of one K=8 MMA are 512 B apart); everything else is plain SWIZZLE_128B.
+    const uint32_t a_type = (kTf32 && p.a_mn) ? 1u : 2u, a_sbo = (kTf32 && p.a_mn) ? 512u : 1024u;
+    const uint32_t b_type = (kTf32 && p.b_mn) ? 1u : 2u, b_sbo = (kTf32 && p.b_mn) ? 512u : 1024u;
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -158,8 +162,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
           const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
-            const uint64_t bdesc = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
+            const uint64_t adesc = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, a_sbo, a_type);
+            const uint64_t bdesc = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, b_sbo, b_type);
             const uint32_t accumulate = (kb > kb0 || k > 0) ? 1u : 0u;
             if (kTf32) umma_tf32(d_tmem, adesc, bdesc, idesc, accumulate);
             else       umma_f16(d_tmem, adesc, bdesc, idesc, accumulate);
@@ -339,7 +343,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 // host side
 // ------------------------------------------------------------------------------------
 static int encode_map(CUtensorMap* map, const void* ptr, bool f32, uint64_t inner, uint64_t outer,
-                      uint64_t row_stride_elems, uint32_t box_inner, uint32_t box_outer) {
+                      uint64_t row_stride_elems, uint32_t box_inner, uint32_t box_outer,
+                      bool atom32 = false) {
   tensormap_encode_fn enc = get_tensormap_encode();
   if (!enc) return set_error(B200PS_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const uint64_t esz = f32 ? 4 : 2;
@@ -349,7 +354,8 @@ static int encode_map(CUtensorMap* map, const void* ptr, bool f32, uint64_t inne
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return set_error(B200PS_ERR_CUDA,
@@ -372,10 +378,10 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   CUtensorMap tmA, tmB;
   int rc;
   if (!a.a_mn_major) rc = encode_map(&tmA, a.A, kTf32, a.K, a.M, a.lda, BLOCK_K, kBlockM);
-  else               rc = encode_map(&tmA, a.A, kTf32, a.M, a.K, a.lda, ATOM_MN, BLOCK_K);
+  else               rc = encode_map(&tmA, a.A, kTf32, a.M, a.K, a.lda, ATOM_MN, BLOCK_K, kTf32);
   if (rc) return rc;
   if (!a.b_mn_major) rc = encode_map(&tmB, a.B, kTf32, a.K, a.N, a.ldb, BLOCK_K, BLOCK_N);
-  else               rc = encode_map(&tmB, a.B, kTf32, a.N, a.K, a.ldb, ATOM_MN, BLOCK_K);
+  else               rc = encode_map(&tmB, a.B, kTf32, a.N, a.K, a.ldb, ATOM_MN, BLOCK_K, kTf32);
   if (rc) return rc;
 
   GemmParams p;

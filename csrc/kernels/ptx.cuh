@@ -168,14 +168,16 @@ __device__ __forceinline__ void tmem_ld_wait() {
 //   bits [0,14)  start address >> 4      bits [16,30) leading byte offset >> 4
 //   bits [32,46) stride byte offset >> 4 bits [46,48) version = 1
 //   bits [61,64) layout type (2 = SWIZZLE_128B)
+//                             (1 = SWIZZLE_128B with 32-byte atoms: the only layout the
+//                              hardware accepts for MN-major tf32 operands)
 __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
+                                                         uint32_t sbo_bytes, uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr & 0x3ffff) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fff) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fff) << 32;
   d |= static_cast<uint64_t>(1) << 46;
-  d |= static_cast<uint64_t>(2) << 61;
+  d |= static_cast<uint64_t>(layout_type) << 61;
   return d;
 }
 // Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulation.

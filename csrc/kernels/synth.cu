@@ -166,11 +166,12 @@ __global__ void __launch_bounds__(128) synth_sparse_fill_kernel(const int* __res
 // N(0,1) initialiser (tf.random_normal, example.py:84-85; lr2.py:384): Box-Muller on Philox,
 // deterministic per (seed, element index).
 __global__ void __launch_bounds__(256) init_normal_kernel(float* __restrict__ out, size_t n, float mean,
-                                                          float stddev, uint64_t seed, uint64_t stream_id) {
+                                                          float stddev, uint64_t seed, uint64_t stream_id,
+                                                          uint64_t quad_offset) {
   const size_t quads = (n + 3) / 4;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < quads;
        q += (size_t)gridDim.x * blockDim.x) {
-    const Philox r = philox4x32(q, stream_id, seed);
+    const Philox r = philox4x32(q + quad_offset, stream_id, seed);
     float g[4];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -233,9 +234,10 @@ extern "C" int b200ps_synth_sparse(int32_t* row_ptr, int64_t* fid, float* fval, 
 }
 
 extern "C" int b200ps_init_normal(float* out, uint64_t n, float mean, float stddev, uint64_t seed,
-                                  uint64_t stream_id, b200ps_stream_t stream) {
+                                  uint64_t stream_id, uint64_t elem_offset, b200ps_stream_t stream) {
   if (n == 0) return 0;
-  init_normal_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, as_stream(stream)>>>(out, n, mean, stddev, seed, stream_id);
+  B200PS_REQUIRE(elem_offset % 4 == 0, "init_normal: elem_offset must be a multiple of 4");
+  init_normal_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, as_stream(stream)>>>(out, n, mean, stddev, seed, stream_id, elem_offset / 4);
   B200PS_LAUNCH_CHECK();
   return 0;
 }

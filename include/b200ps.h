@@ -130,9 +130,11 @@ int b200ps_synth_dense_bf16(void* x, int32_t* labels, int32_t B, int32_t D, int3
 int b200ps_synth_sparse(int32_t* row_ptr, int64_t* fid, float* fval, float* labels, int32_t B,
                         int32_t nnz_mean, int32_t spread, int64_t F, float skew, uint64_t seed,
                         uint64_t offset, b200ps_stream_t stream);
-/* tf.random_normal initialiser (example.py:84-85, lr2.py:384), Philox + Box-Muller. */
+/* tf.random_normal initialiser (example.py:84-85, lr2.py:384), Philox + Box-Muller.
+ * out[i] is element (elem_offset + i) of stream stream_id, so shards of one variable can be
+ * initialised independently (elem_offset % 4 == 0). */
 int b200ps_init_normal(float* out, uint64_t n, float mean, float stddev, uint64_t seed,
-                       uint64_t stream_id, b200ps_stream_t stream);
+                       uint64_t stream_id, uint64_t elem_offset, b200ps_stream_t stream);
 int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t stream);
 
 /* ------------------------------------------------------------------------------------

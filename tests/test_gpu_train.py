@@ -1,0 +1,164 @@
+"""End-to-end GPU training paths: trainers, ParameterStore, virtual-rank sync/async."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _mnist_batches(n, B=100, seed=1, offset=0):
+    from b200ps import ops
+    x = torch.empty(n * B, 784, device=DEV); y = torch.empty(n * B, device=DEV, dtype=torch.int32)
+    ops.synth_mnist(x, y, seed=seed, offset=offset)
+    return x.view(n, B, 784), y.view(n, B)
+
+
+def test_mlp_step_matches_reference_math(native_lib):
+    from b200ps.models.mlp import mlp_reference_step
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    ctx = init_from_env(virtual_world=1)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.0005, mode="sync", use_graph=False)
+    xs, ys = _mnist_batches(1)
+    params = {k: v.clone() for k, v in tr.store.state_dict().items()}
+    loss_ref, grads_ref, correct_ref = mlp_reference_step(params, xs[0].cpu(), ys[0].cpu())
+    tr.step(xs[0], ys[0])
+    torch.cuda.synchronize()
+    assert abs(tr.read_loss() - loss_ref.item()) < 5e-2 * max(1.0, abs(loss_ref.item()))  # tf32 GEMM
+    after = tr.store.state_dict()
+    for name in tr.model.names():
+        want = params[name] - 0.0005 * grads_ref[name]
+        err = (after[name] - want).abs().max().item()
+        assert err < 2e-4, (name, err)
+    assert after["global_step"].item() == 1.0
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_mlp_trains_and_graph_matches_eager(native_lib, use_graph):
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    ctx = init_from_env(virtual_world=1)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="sync", use_graph=use_graph)
+    xs, ys = _mnist_batches(50)
+    first = None
+    for i in range(150):
+        tr.step(xs[i % 50], ys[i % 50])
+        if i == 0:
+            first = tr.read_loss()
+    last = tr.read_loss()
+    assert last < first and last == last
+    acc, _ = tr.evaluate(xs.reshape(-1, 784), ys.reshape(-1))
+    assert acc > 0.5, acc
+    assert tr.global_step == 150
+
+
+def test_sync_virtual_ranks_equal_big_batch(native_lib):
+    """4 sync replicas x batch 100 == 1 worker x batch 400 (mean of means), up to fp32 rounding."""
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    xs, ys = _mnist_batches(4)
+    ctx4 = init_from_env(virtual_world=4)
+    tr4 = MLPTrainer(ctx4, batch_size=100, lr=0.01, mode="sync", use_graph=False)
+    for r in range(4):
+        tr4.x[r].copy_(xs[r]); tr4.labels[r].copy_(ys[r])
+    tr4.step()
+    ctx1 = init_from_env(virtual_world=1)
+    tr1 = MLPTrainer(ctx1, batch_size=400, lr=0.01, mode="sync", use_graph=False)
+    tr1.step(xs.reshape(400, 784), ys.reshape(400))
+    torch.cuda.synchronize()
+    a, b = tr4.store.state_dict(), tr1.store.state_dict()
+    for name in tr4.model.names():
+        assert (a[name] - b[name]).abs().max().item() < 2e-4, name
+        # every replica holds the same bytes after the push broadcast
+        for r in range(1, 4):
+            assert torch.equal(tr4.store.var(name, 0), tr4.store.var(name, r))
+    assert tr4.global_step == 1
+
+
+def test_async_virtual_ranks_count_every_update(native_lib):
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    xs, ys = _mnist_batches(4)
+    ctx = init_from_env(virtual_world=4)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="async", use_graph=False,
+                    placement="round_robin_variable")
+    for r in range(4):
+        tr.x[r].copy_(xs[r]); tr.labels[r].copy_(ys[r])
+    l0 = None
+    for i in range(30):
+        tr.step()
+        if i == 0:
+            l0 = tr.read_loss()
+    assert tr.global_step == 4 * 30           # global_step counts ALL workers' updates (example.py:177-179)
+    assert tr.read_loss() < l0
+    # round-robin parity: creation order global_step, W1, W2, b1, b2 over 4 ps -> owners 1, 2, 3, 0
+    m = tr.model
+    assert [tr.store.owner_of(n) for n in (m.W1, m.W2, m.B1, m.B2)] == [1, 2, 3, 0]
+
+
+def test_wide_mlp_small_matches_autograd(native_lib):
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import WideMLPTrainer
+    from b200ps import ops
+    B, L, D = 256, 3, 512
+    for world in (1, 2):
+        ctx = init_from_env(virtual_world=world)
+        tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.5, use_graph=False)
+        xs = torch.empty(world, B, D, device=DEV, dtype=torch.bfloat16)
+        ys = torch.empty(world, B, device=DEV, dtype=torch.int32)
+        for r in range(world):
+            ops.synth_dense_bf16(xs[r], ys[r], classes=D, seed=3, offset=r * B)
+            tr.x[r].copy_(xs[r]); tr.labels[r].copy_(ys[r])
+        before = tr.store.state_dict()
+        # autograd reference on the bf16-rounded weights the kernels actually read
+        ws = [before[tr.model.wname(l)].to(DEV).bfloat16().float().requires_grad_(True) for l in range(L)]
+        bs = [before[tr.model.bname(l)].to(DEV).clone().requires_grad_(True) for l in range(L)]
+        total = 0
+        for r in range(world):
+            a = xs[r].float()
+            for l in range(L):
+                z = a @ ws[l] + bs[l]
+                a = torch.sigmoid(z).bfloat16().float() if l < L - 1 else z
+            total = total + torch.nn.functional.cross_entropy(a, ys[r].long()) / world
+        total.backward()
+        tr.step()
+        torch.cuda.synchronize()
+        after = tr.store.state_dict()
+        for l in range(L):
+            want_w = before[tr.model.wname(l)] - 0.5 * ws[l].grad.cpu()
+            want_b = before[tr.model.bname(l)] - 0.5 * bs[l].grad.cpu()
+            ew = (after[tr.model.wname(l)] - want_w).abs().max().item()
+            eb = (after[tr.model.bname(l)] - want_b).abs().max().item()
+            scale_w = (0.5 * ws[l].grad).abs().max().item()
+            assert ew < 0.05 * scale_w + 1e-5, (world, l, ew, scale_w)
+            assert eb < 0.05 * (0.5 * bs[l].grad).abs().max().item() + 1e-5, (world, l, eb)
+            w_dev = tr.store.var(tr.model.wname(l), 0)
+            assert torch.equal(w_dev.cpu(), after[tr.model.wname(l)].bfloat16())
+
+
+def test_sparse_lr_trainer_learns(native_lib):
+    from b200ps import ops
+    from b200ps.metrics.auc import StreamingAUC
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import SparseLRTrainer
+    F, B, nnz, spread = 1 << 16, 500, 40, 10
+    for mode in ("async", "sync"):
+        ctx = init_from_env(virtual_world=1)
+        tr = SparseLRTrainer(ctx, features=F, lr=0.5, mode=mode)
+        tr.store.sparse_shard(tr.model.W).mul_(0.01)       # start near zero so learning shows quickly
+        batches = []
+        for i in range(40):
+            rp = torch.empty(B + 1, device=DEV, dtype=torch.int32)
+            fid = torch.empty(B * (nnz + spread), device=DEV, dtype=torch.int64)
+            fv = torch.empty(B * (nnz + spread), device=DEV); y = torch.empty(B, device=DEV)
+            ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=5, offset=i * B)
+            batches.append((rp, fid, fv, y))
+        for epoch in range(6):
+            for b in batches[:32]:
+                tr.step(b)
+        assert tr.global_step == 6 * 32
+        auc = StreamingAUC(200, device=DEV)
+        for b in batches[32:]:
+            pred, _ = tr.predict(b)
+            auc.update(pred, b[3])
+        assert auc.result() > 0.6, (mode, auc.result())
