@@ -193,13 +193,15 @@ class SparseLRTrainer(_TrainerBase):
     """lr2.py's trainer over a row-sharded weight: async (default, like the reference) or sync."""
 
     def __init__(self, ctx, features: int, lr: float = 0.001, mode: str = "async",
-                 placement: str = "flat_shard", seed: int = 1):
+                 placement: str = "flat_shard", seed: int = 1, use_graph: bool = True):
         super().__init__(ctx, mode, lr, None, placement, seed)
         self.model = SparseLR(features)
         self.model.register(self.store)
         self.store.build()
         self.store.initialize()
         self._last = None
+        self.use_graph = use_graph and self.device.type == "cuda"
+        self._graphs = {}
         if ctx.group is not None:
             ctx.control_barrier()
 
@@ -207,12 +209,32 @@ class SparseLRTrainer(_TrainerBase):
     def last_loss(self) -> torch.Tensor:
         return self._last
 
-    def step(self, batch, rank=None):
-        """``batch`` = (row_ptr int32[B+1], fid int64[nnz], fval f32[nnz], labels f32[B]) on the device."""
+    def _eager(self, batch, rank=None):
         if self.mode == "async":
             self._last = self.model.step_async(self.store, batch, self.lr, rank=rank)
         else:
             self._last = self.model.step_sync(self.store, batch, self.lr, rank=rank)
+
+    def step(self, batch, rank=None):
+        """``batch`` = (row_ptr int32[B+1], fid int64[nnz], fval f32[nnz], labels f32[B]) on the device.
+
+        The step is one or two kernels, i.e. host-launch-bound; a batch whose buffers are reused
+        (a prefetch ring) gets its own CUDA graph on its second visit."""
+        key = tuple(t.data_ptr() for t in batch) + (batch[3].numel(),)
+        ent = self._graphs.get(key) if self.use_graph else None
+        if ent is None:
+            self._eager(batch, rank)
+            if self.use_graph:
+                self._graphs[key] = 1 if key not in self._graphs else self._graphs[key]
+        elif ent == 1:
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._eager(batch, rank)
+            self._graphs[key] = (g, batch)          # keep the batch tensors alive with the graph
+            g.replay()
+        else:
+            ent[0].replay()
         self.local_step += 1
 
     def step_from_host(self, batch_pinned, dev_bufs) -> float:

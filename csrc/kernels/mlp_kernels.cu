@@ -24,11 +24,11 @@ constexpr int kTailRows = 128;
 constexpr int kMaxClasses = 32;
 
 struct TailParams {
-  const float* z2;     // [B,H] pre-activation WITHOUT bias (split-K GEMM output)
-  const float* b1;     // [H]
-  const float* w2;     // [H,C]
-  const float* b2;     // [C]
-  const int* labels;   // [B] class ids
+  const float* __restrict__ z2;     // [B,H] pre-activation WITHOUT bias (split-K GEMM output)
+  const float* __restrict__ b1;     // [H]
+  const float* __restrict__ w2;     // [H,C]
+  const float* __restrict__ b2;     // [C]
+  const int* __restrict__ labels;   // [B] class ids
   float* a2_out;       // [B,H] or null
   float* dz2;          // [B,H] (train)
   float* dw2;          // [H,C] (train)
@@ -79,12 +79,30 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailPar
 
   for (int r0 = row_begin; r0 < row_end; r0 += kTailRows) {
     const int nrows = min(kTailRows, row_end - r0);
-    // (1) a2 = sigmoid(z2 + b1)
-    for (int i = tid; i < nrows * H; i += kTailThreads) {
-      const int r = i / H, h = i - r * H;
-      const float a = sigmoidf_acc(p.z2[(size_t)(r0 + r) * H + h] + s_b1[h]);
-      s_a2[r * HP + h] = a;
-      if (p.a2_out) p.a2_out[(size_t)(r0 + r) * H + h] = a;
+    // (1) a2 = sigmoid(z2 + b1).  The tile is one contiguous run of nrows*H floats: issue all of
+    // a thread's loads before the first use so the global latency is paid once, not per element.
+    {
+      const float* __restrict__ zsrc = p.z2 + (size_t)r0 * H;
+      const int n = nrows * H;
+      constexpr int kU = 8;
+      for (int base = 0; base < n; base += kU * kTailThreads) {
+        float v[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int i = base + u * kTailThreads + tid;
+          v[u] = i < n ? __ldg(zsrc + i) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          const int i = base + u * kTailThreads + tid;
+          if (i < n) {
+            const int r = i / H, h = i - r * H;
+            const float a = sigmoidf_acc(v[u] + s_b1[h]);
+            s_a2[r * HP + h] = a;
+            if (p.a2_out) p.a2_out[(size_t)(r0 + r) * H + h] = a;
+          }
+        }
+      }
     }
     __syncthreads();
     // (2) logits z3 = a2 . W2 + b2 : one thread per (row, class)

@@ -120,14 +120,19 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
     }
   }
 
-  // -- phase 2: when every CTA of this rank is done, tell the peers and wait for theirs
-  __threadfence_system();
+  // -- phase 2: when every CTA of this rank is done, tell the peers and wait for theirs.
+  // One system-scope fence per CTA (thread 0, after the block barrier: fences are cumulative
+  // over everything that happened-before them) instead of one per thread.
   __syncthreads();
   __shared__ bool s_last;
-  if (tid == 0) s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
+  if (tid == 0) {
+    __threadfence_system();
+    s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
+  }
   __syncthreads();
   if (s_last) {
-    __threadfence_system();
+    if (tid == 0) __threadfence_system();
+    __syncthreads();
     if (tid < world) st_release_sys(a.pads[tid] + kFlagParamsDone + rank, epoch);
     if (tid < world) wait_flag_geq(pad + kFlagParamsDone + tid, epoch);
     __syncthreads();

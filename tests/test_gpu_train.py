@@ -144,7 +144,7 @@ def test_sparse_lr_trainer_learns(native_lib):
     F, B, nnz, spread = 1 << 16, 500, 40, 10
     for mode in ("async", "sync"):
         ctx = init_from_env(virtual_world=1)
-        tr = SparseLRTrainer(ctx, features=F, lr=0.5, mode=mode)
+        tr = SparseLRTrainer(ctx, features=F, lr=10.0, mode=mode)
         tr.store.sparse_shard(tr.model.W).mul_(0.01)       # start near zero so learning shows quickly
         batches = []
         for i in range(40):
