@@ -274,6 +274,9 @@ def bench_sparse(ctx, args, sampler, mode="async"):
                          offset=(ctx.rank * ring + i) * B)
         batches.append((rp, fid, fv, y))
     per_step = launches_of(lambda: tr.step(batches[0]), native)
+    for _ in range(3):                       # every ring slot: eager visit, graph capture, first replay
+        for b in batches:
+            tr.step(b)
     for i in range(max(args.warmup, 3)):
         tr.step(batches[i % ring])
     loss0 = tr.read_loss()

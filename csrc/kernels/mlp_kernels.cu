@@ -7,6 +7,7 @@
 //   colsum        : bias gradients of the wide layers
 //   sgd / adam    : owner-side optimiser apply (example.py:108, model_export.py:38)
 #include "../common.h"
+#include "../workspace.h"
 #include "ptx.cuh"
 
 namespace b200ps {
@@ -43,31 +44,39 @@ struct TailParams {
   float grad_scale;    // 1/B_global for the mean loss
   float loss_scale;    // 1/B for a mean, 1 for a sum
   int atomic_out;      // gridDim.x > 1
+  long long* dbg;      // optional: clock64() at phase boundaries (thread 0 of CTA 0)
 };
 
+// Thread layout for the matmul-like phases: 512 threads = 128 (row or hidden index) x 4 groups,
+// each thread keeping a full class vector (CP floats) in registers, so every shared-memory
+// operand is read once per 16/32 FMAs instead of once per FMA.
+template <int CP>
 __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailParams p) {
-  extern __shared__ float sm[];
+  extern __shared__ __align__(16) float sm[];
   const int H = p.H, C = p.C;
   const int HP = H + 1;  // pad: conflict-free column walks
-  float* s_w2 = sm;                       // [H*C]
-  float* s_b2 = s_w2 + H * C;             // [C]
-  float* s_b1 = s_b2 + kMaxClasses;       // [H]
-  float* s_a2 = s_b1 + H;                 // [kTailRows * HP]   activations, later dz2
-  float* s_dz3 = s_a2 + kTailRows * HP;   // [kTailRows * kMaxClasses] logits -> probs -> dz3
-  float* s_red = s_dz3 + kTailRows * kMaxClasses;  // [32] block reduction scratch
+  float* s_w2 = sm;                            // [H+1][CP]  (row H unused), zero padded classes
+  float* s_b2 = s_w2 + (H + 1) * CP;           // [CP]
+  float* s_b1 = s_b2 + CP;                     // [H] (+pad to 4)
+  float* s_dz3 = s_b1 + ((H + 3) & ~3);        // [kTailRows][CP]  logits -> dz3
+  float* s_part = s_dz3 + kTailRows * CP;      // [4][128][CP] partial sums
+  float* s_a2 = s_part + 4 * 128 * CP;         // [kTailRows][HP]  activations, later dz2
+  float* s_red = s_a2 + kTailRows * HP;        // [32]
   __shared__ int s_correct;
 
   const int tid = threadIdx.x;
-  for (int i = tid; i < H * C; i += kTailThreads) s_w2[i] = p.w2[i];
-  for (int i = tid; i < C; i += kTailThreads) s_b2[i] = p.b2[i];
-  for (int i = tid; i < H; i += kTailThreads) s_b1[i] = p.b1[i];
+  const int lo7 = tid & 127, grp = tid >> 7;
+  for (int i = tid; i < (H + 1) * CP; i += kTailThreads) {
+    const int h = i / CP, c = i - h * CP;
+    s_w2[i] = (h < H && c < C) ? __ldg(p.w2 + h * C + c) : 0.f;
+  }
+  for (int i = tid; i < CP; i += kTailThreads) s_b2[i] = i < C ? __ldg(p.b2 + i) : 0.f;
+  for (int i = tid; i < H; i += kTailThreads) s_b1[i] = __ldg(p.b1 + i);
   if (tid == 0) s_correct = 0;
 
   const int row_begin = blockIdx.x * p.rows_per_cta;
   const int row_end = min(p.B, row_begin + p.rows_per_cta);
 
-  // per-thread accumulators for the batch reductions (fixed ownership => fixed order)
-  //   dW2: element e = tid + k*kTailThreads for k < kDw2PerThread
   constexpr int kDw2PerThread = 8;  // supports H*C <= 4096
   float acc_dw2[kDw2PerThread];
 #pragma unroll
@@ -75,17 +84,20 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailPar
   float acc_db1 = 0.f;  // thread h < H owns db1[h]
   float acc_db2 = 0.f;  // thread c < C owns db2[c]
   float loss_local = 0.f;
+  const int Hq = (H + 3) >> 2;
   __syncthreads();
+  int dbg_i = 0;
+#define TAIL_MARK() do { if (p.dbg && tid == 0 && blockIdx.x == 0) p.dbg[dbg_i++] = clock64(); } while (0)
+  TAIL_MARK();
 
   for (int r0 = row_begin; r0 < row_end; r0 += kTailRows) {
     const int nrows = min(kTailRows, row_end - r0);
-    // (1) a2 = sigmoid(z2 + b1).  The tile is one contiguous run of nrows*H floats: issue all of
-    // a thread's loads before the first use so the global latency is paid once, not per element.
+    // (1) a2 = sigmoid(z2 + b1); all of a thread's loads are issued before the first use.
     {
       const float* __restrict__ zsrc = p.z2 + (size_t)r0 * H;
       const int n = nrows * H;
       constexpr int kU = 8;
-      for (int base = 0; base < n; base += kU * kTailThreads) {
+      for (int base = 0; base < kTailRows * H; base += kU * kTailThreads) {
         float v[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
@@ -95,88 +107,165 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailPar
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
           const int i = base + u * kTailThreads + tid;
-          if (i < n) {
+          if (i < kTailRows * H) {
             const int r = i / H, h = i - r * H;
-            const float a = sigmoidf_acc(v[u] + s_b1[h]);
+            const float a = sigmoidf_acc(v[u] + s_b1[h]);   // rows >= nrows: finite filler
             s_a2[r * HP + h] = a;
-            if (p.a2_out) p.a2_out[(size_t)(r0 + r) * H + h] = a;
+            if (i < n && p.a2_out) p.a2_out[(size_t)(r0 + r) * H + h] = a;
           }
         }
       }
     }
     __syncthreads();
-    // (2) logits z3 = a2 . W2 + b2 : one thread per (row, class)
-    for (int i = tid; i < nrows * C; i += kTailThreads) {
-      const int r = i / C, c = i - r * C;
-      float z = s_b2[c];
-      const float* a = s_a2 + r * HP;
-#pragma unroll 4
-      for (int h = 0; h < H; ++h) z = fmaf(a[h], s_w2[h * C + c], z);
-      s_dz3[r * kMaxClasses + c] = z;
+    TAIL_MARK();
+    // (2) partial logits over a quarter of the hidden units: thread = (row lo7, quarter grp)
+    {
+      float acc[CP];
+#pragma unroll
+      for (int c = 0; c < CP; ++c) acc[c] = 0.f;
+      const float* a = s_a2 + lo7 * HP;
+      const int h1 = min(H, (grp + 1) * Hq);
+      for (int h = grp * Hq; h < h1; ++h) {
+        const float av = a[h];
+        const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CP);
+#pragma unroll
+        for (int c4 = 0; c4 < CP / 4; ++c4) {
+          const float4 wv = w[c4];
+          acc[4 * c4] = fmaf(av, wv.x, acc[4 * c4]);
+          acc[4 * c4 + 1] = fmaf(av, wv.y, acc[4 * c4 + 1]);
+          acc[4 * c4 + 2] = fmaf(av, wv.z, acc[4 * c4 + 2]);
+          acc[4 * c4 + 3] = fmaf(av, wv.w, acc[4 * c4 + 3]);
+        }
+      }
+      float4* dst = reinterpret_cast<float4*>(s_part + (grp * 128 + lo7) * CP);
+#pragma unroll
+      for (int c4 = 0; c4 < CP / 4; ++c4)
+        dst[c4] = make_float4(acc[4 * c4], acc[4 * c4 + 1], acc[4 * c4 + 2], acc[4 * c4 + 3]);
     }
     __syncthreads();
+    TAIL_MARK();
+    for (int i = tid; i < kTailRows * CP; i += kTailThreads) {
+      const int c = i % CP;
+      s_dz3[i] = s_b2[c] + ((s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]));
+    }
+    __syncthreads();
+    TAIL_MARK();
     // (3) stable log-softmax, loss, accuracy, dz3 = (p - y) * grad_scale : one thread per row
-    if (tid < nrows) {
-      float* z = s_dz3 + tid * kMaxClasses;
-      const int label = p.labels[r0 + tid];
-      float m = z[0];
-      int arg = 0;
-      for (int c = 1; c < C; ++c)
-        if (z[c] > m) { m = z[c]; arg = c; }
-      float se = 0.f;
-      for (int c = 0; c < C; ++c) se += __expf(z[c] - m);
-      const float lse = m + __logf(se);
-      loss_local += (lse - z[label]);
-      if (arg == label) atomicAdd(&s_correct, 1);
-      const float inv = 1.f / se;
-      for (int c = 0; c < C; ++c) {
-        const float pr = __expf(z[c] - m) * inv;
-        if (p.probs_out) p.probs_out[(size_t)(r0 + tid) * C + c] = pr;
-        z[c] = (pr - (c == label ? 1.f : 0.f)) * p.grad_scale;
+    if (tid < kTailRows) {
+      float* z = s_dz3 + tid * CP;
+      if (tid < nrows) {
+        const int label = p.labels[r0 + tid];
+        float m = z[0];
+        int arg = 0;
+        for (int c = 1; c < C; ++c)
+          if (z[c] > m) { m = z[c]; arg = c; }
+        float se = 0.f;
+        for (int c = 0; c < C; ++c) se += __expf(z[c] - m);
+        const float lse = m + __logf(se);
+        loss_local += (lse - z[label]);
+        if (arg == label) atomicAdd(&s_correct, 1);
+        const float inv = 1.f / se;
+        for (int c = 0; c < C; ++c) {
+          const float pr = __expf(z[c] - m) * inv;
+          if (p.probs_out) p.probs_out[(size_t)(r0 + tid) * C + c] = pr;
+          z[c] = (pr - (c == label ? 1.f : 0.f)) * p.grad_scale;
+        }
+        for (int c = C; c < CP; ++c) z[c] = 0.f;
+      } else {
+        for (int c = 0; c < CP; ++c) z[c] = 0.f;   // padded rows contribute nothing below
       }
     }
     __syncthreads();
+    TAIL_MARK();
     if (p.train) {
-      // (4) dW2 += a2^T dz3 ; db2 += sum_r dz3
+      // (4) dW2 += a2^T dz3, db2 += 1^T dz3 : thread = (hidden unit lo7 [H = the ones row], row block grp)
+      {
+        float acc[CP];
+#pragma unroll
+        for (int c = 0; c < CP; ++c) acc[c] = 0.f;
+        if (lo7 <= H) {
+          for (int r = grp * 32; r < grp * 32 + 32; ++r) {
+            const float av = lo7 < H ? s_a2[r * HP + lo7] : 1.f;
+            const float4* dz = reinterpret_cast<const float4*>(s_dz3 + r * CP);
+#pragma unroll
+            for (int c4 = 0; c4 < CP / 4; ++c4) {
+              const float4 d = dz[c4];
+              acc[4 * c4] = fmaf(av, d.x, acc[4 * c4]);
+              acc[4 * c4 + 1] = fmaf(av, d.y, acc[4 * c4 + 1]);
+              acc[4 * c4 + 2] = fmaf(av, d.z, acc[4 * c4 + 2]);
+              acc[4 * c4 + 3] = fmaf(av, d.w, acc[4 * c4 + 3]);
+            }
+          }
+        }
+        float4* dst = reinterpret_cast<float4*>(s_part + (grp * 128 + lo7) * CP);
+#pragma unroll
+        for (int c4 = 0; c4 < CP / 4; ++c4)
+          dst[c4] = make_float4(acc[4 * c4], acc[4 * c4 + 1], acc[4 * c4 + 2], acc[4 * c4 + 3]);
+      }
+      __syncthreads();
+      TAIL_MARK();
 #pragma unroll
       for (int k = 0; k < kDw2PerThread; ++k) {
         const int e = tid + k * kTailThreads;
         if (e < H * C) {
           const int h = e / C, c = e - h * C;
-          float s = 0.f;
-          for (int r = 0; r < nrows; ++r) s = fmaf(s_a2[r * HP + h], s_dz3[r * kMaxClasses + c], s);
-          acc_dw2[k] += s;
+          const int i = h * CP + c;
+          acc_dw2[k] += (s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]);
         }
       }
       if (tid < C) {
-        float s = 0.f;
-        for (int r = 0; r < nrows; ++r) s += s_dz3[r * kMaxClasses + tid];
-        acc_db2 += s;
+        const int i = H * CP + tid;
+        acc_db2 += (s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]);
+      }
+      TAIL_MARK();
+      // (5) dz2 = (dz3 . W2^T) * a2 (1 - a2), in place over s_a2 : thread = (row lo7, quarter grp)
+      {
+        float dz[CP];
+        const float4* src = reinterpret_cast<const float4*>(s_dz3 + lo7 * CP);
+#pragma unroll
+        for (int c4 = 0; c4 < CP / 4; ++c4) {
+          const float4 d = src[c4];
+          dz[4 * c4] = d.x; dz[4 * c4 + 1] = d.y; dz[4 * c4 + 2] = d.z; dz[4 * c4 + 3] = d.w;
+        }
+        float* a = s_a2 + lo7 * HP;
+        const int h1 = min(H, (grp + 1) * Hq);
+        for (int h = grp * Hq; h < h1; ++h) {
+          const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CP);
+          float d = 0.f;
+#pragma unroll
+          for (int c4 = 0; c4 < CP / 4; ++c4) {
+            const float4 wv = w[c4];
+            d = fmaf(dz[4 * c4], wv.x, d);
+            d = fmaf(dz[4 * c4 + 1], wv.y, d);
+            d = fmaf(dz[4 * c4 + 2], wv.z, d);
+            d = fmaf(dz[4 * c4 + 3], wv.w, d);
+          }
+          const float av = a[h];
+          a[h] = d * av * (1.f - av);
+        }
       }
       __syncthreads();
-      // (5) dz2 = (dz3 . W2^T) * a2 (1 - a2)   (overwrites s_a2 in place)
-      for (int i = tid; i < nrows * H; i += kTailThreads) {
+      TAIL_MARK();
+      for (int i = tid; i < nrows * H; i += kTailThreads) {   // coalesced dz2 store
         const int r = i / H, h = i - r * H;
-        const float* dz = s_dz3 + r * kMaxClasses;
-        const float* w = s_w2 + h * C;
-        float d = 0.f;
-        for (int c = 0; c < C; ++c) d = fmaf(dz[c], w[c], d);
-        const float a = s_a2[r * HP + h];
-        d *= a * (1.f - a);
-        s_a2[r * HP + h] = d;
-        p.dz2[(size_t)(r0 + r) * H + h] = d;
+        p.dz2[(size_t)r0 * H + i] = s_a2[r * HP + h];
+      }
+      TAIL_MARK();
+      // (6) db1 += 1^T dz2 : thread = (hidden unit lo7, row block grp), then a fixed-order merge
+      {
+        float sacc = 0.f;
+        if (lo7 < H)
+          for (int r = grp * 32; r < grp * 32 + 32; ++r) sacc += s_a2[r * HP + lo7];
+        s_red[0] = 0.f;  // (keeps s_red initialised for the tail reduction below)
+        s_part[grp * 128 + lo7] = sacc;
       }
       __syncthreads();
-      // (6) db1 += sum_r dz2
-      if (tid < H) {
-        float s = 0.f;
-        for (int r = 0; r < nrows; ++r) s += s_a2[r * HP + tid];
-        acc_db1 += s;
-      }
+      if (tid < H) acc_db1 += (s_part[tid] + s_part[128 + tid]) + (s_part[256 + tid] + s_part[384 + tid]);
     }
     __syncthreads();
   }
 
+  TAIL_MARK();
   // block-level loss reduction in a fixed order
   float l = warp_sum(loss_local);
   if ((tid & 31) == 0) s_red[tid >> 5] = l;
@@ -197,6 +286,293 @@ __global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailPar
     if (tid < C) { if (p.atomic_out) atomicAdd(p.db2 + tid, acc_db2); else p.db2[tid] = acc_db2; }
     if (tid < H) { if (p.atomic_out) atomicAdd(p.db1 + tid, acc_db1); else p.db1[tid] = acc_db1; }
   }
+  TAIL_MARK();
+#undef TAIL_MARK
+}
+
+// ------------------------------------------------------------------------------------
+// mlp_tail v2: the same math spread over many CTAs.  One SM cannot issue the ~80k warp
+// instructions of the head in less than ~20 us, so rows are dealt to CTAs in tiles of 8
+// (one warp per row, lanes over hidden units, class vectors in registers, warp shuffles for
+// the row reductions).  Cross-row sums (dW2, db2, db1, loss) are accumulated per CTA in a
+// fixed order, written to the library workspace, and merged in CTA order by the last CTA to
+// arrive — deterministic, no fp32 atomics.
+// ------------------------------------------------------------------------------------
+constexpr int kT2Threads = 256;
+constexpr int kT2Rows = 8;
+constexpr int kT2MaxPer = 16;   // outputs of dW2 per thread: H*C <= 4096
+
+template <int CP>
+__global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams p, float* __restrict__ scratch,
+                                                              unsigned int* counter) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = p.H, C = p.C;
+  constexpr int CPP = CP + 4;                // padded row: float4 loads of 8 consecutive rows are conflict-free
+  float* s_w2 = sm;                          // [H][CPP], zero padded classes
+  float* s_b2 = s_w2 + H * CPP;              // [CP]
+  float* s_b1 = s_b2 + CP;                   // [H] (+pad)
+  float* s_a2 = s_b1 + ((H + 3) & ~3);       // [8][H]
+  float* s_dz2 = s_a2 + kT2Rows * H;         // [8][H]
+  float* s_dz3 = s_dz2 + kT2Rows * H;        // [8][CP]
+  __shared__ float s_loss[kT2Rows];
+  __shared__ int s_corr[kT2Rows];
+  __shared__ bool s_last;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < H * CP; i += kT2Threads) {
+    const int h = i / CP, c = i - h * CP;
+    s_w2[h * CPP + c] = c < C ? __ldg(p.w2 + h * C + c) : 0.f;
+  }
+  for (int i = tid; i < CP; i += kT2Threads) s_b2[i] = i < C ? __ldg(p.b2 + i) : 0.f;
+  for (int i = tid; i < H; i += kT2Threads) s_b1[i] = __ldg(p.b1 + i);
+
+  const int row_begin = blockIdx.x * p.rows_per_cta;
+  const int row_end = min(p.B, row_begin + p.rows_per_cta);
+  const int HK = (H + 31) >> 5;   // hidden units per lane (<= 4)
+  const int P = H * C + C + H + 1;
+
+  // gradient outputs owned by this thread (fixed ownership => fixed summation order)
+  int eh[kT2MaxPer], ec[kT2MaxPer];
+  float acc[kT2MaxPer];
+#pragma unroll
+  for (int j = 0; j < kT2MaxPer; ++j) {
+    const int e = tid + j * kT2Threads;
+    eh[j] = e < H * C ? e / C : -1;
+    ec[j] = e < H * C ? e - (e / C) * C : 0;
+    acc[j] = 0.f;
+  }
+  float acc_b2 = 0.f, acc_b1a = 0.f, acc_b1b = 0.f;   // thread c < C ; threads h = tid, tid + 256 < H
+  float loss_w = 0.f;
+  int corr_w = 0;
+  int dbg_i = 0;
+#define T2_MARK() do { if (p.dbg && tid == 0) p.dbg[blockIdx.x * 16 + dbg_i++] = clock64(); } while (0)
+  T2_MARK();
+  __syncthreads();
+  T2_MARK();
+
+  for (int r0 = row_begin; r0 < row_end; r0 += kT2Rows) {
+    const int r = r0 + warp;
+    const bool row_ok = r < row_end;
+    // (a) a = sigmoid(z2 + b1) for this lane's hidden units (label fetched in the same batch of loads)
+    const int label = row_ok ? __ldg(p.labels + r) : 0;
+    float zk[4], ak[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      zk[k] = (row_ok && k < HK && h < H) ? __ldg(p.z2 + (size_t)r * H + h) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      const bool ok = row_ok && k < HK && h < H;
+      ak[k] = ok ? sigmoidf_acc(zk[k] + s_b1[h]) : 0.f;
+      if (k < HK && h < H) {
+        s_a2[warp * H + h] = ak[k];
+        if (ok && p.a2_out) p.a2_out[(size_t)r * H + h] = ak[k];
+      }
+    }
+    // (b) logits: per-lane partial over its hidden units, then a recursive-halving reduce that
+    // leaves class c's total in lanes c and c+16 (CP=16) / lane c (CP=32): 16+ shuffles, not 80
+    float zc[CP];
+#pragma unroll
+    for (int c = 0; c < CP; ++c) zc[c] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      if (k < HK && h < H) {
+        const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CPP);
+#pragma unroll
+        for (int c4 = 0; c4 < CP / 4; ++c4) {
+          const float4 wv = w[c4];
+          zc[4 * c4] = fmaf(ak[k], wv.x, zc[4 * c4]);
+          zc[4 * c4 + 1] = fmaf(ak[k], wv.y, zc[4 * c4 + 1]);
+          zc[4 * c4 + 2] = fmaf(ak[k], wv.z, zc[4 * c4 + 2]);
+          zc[4 * c4 + 3] = fmaf(ak[k], wv.w, zc[4 * c4 + 3]);
+        }
+      }
+    }
+    if (CP == 16) {   // fold the two half-warps first so that 16 lanes x 16 classes remain
+#pragma unroll
+      for (int c = 0; c < CP; ++c) zc[c] += __shfl_xor_sync(0xffffffffu, zc[c], 16);
+    }
+    // halving over lane bits: after the step for bit b, a lane keeps only the classes whose
+    // bit b equals its own lane bit b
+#pragma unroll
+    for (int bit = (CP == 32 ? 16 : 8), n = CP / 2; bit >= 1; bit >>= 1, n >>= 1) {
+      const bool up = (lane & bit) != 0;
+#pragma unroll
+      for (int j = 0; j < n; ++j) {
+        const float send = up ? zc[j] : zc[j + n];
+        const float keep = up ? zc[j + n] : zc[j];
+        zc[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+      }
+    }
+    const int myc = lane & (CP - 1);            // the class this lane now owns
+    float z = zc[0] + s_b2[myc];
+    // (c) stable log-softmax across the lanes of the (half-)warp that own real classes
+    const bool cls_ok = myc < C;
+    float m = cls_ok ? z : -INFINITY;
+    int arg = myc;
+#pragma unroll
+    for (int o = CP / 2; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, m, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+    }
+    const float e = cls_ok ? __expf(z - m) : 0.f;
+    float se = e;
+#pragma unroll
+    for (int o = CP / 2; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+    const float zl = __shfl_sync(0xffffffffu, z, label & (CP - 1));
+    const float pr = e / se;
+    if (row_ok && lane == 0) {
+      loss_w += m + __logf(se) - zl;
+      corr_w += (arg == label) ? 1 : 0;
+    }
+    const float mine = (row_ok && cls_ok) ? (pr - (myc == label ? 1.f : 0.f)) * p.grad_scale : 0.f;
+    if (row_ok && p.probs_out && lane < CP && cls_ok) p.probs_out[(size_t)r * C + myc] = pr;
+    if (lane < CP) s_dz3[warp * CP + lane] = mine;
+    T2_MARK();
+    __syncwarp();
+    {   // every lane needs the whole dz3 row for (d): broadcast reads back from shared memory
+      const float4* dz = reinterpret_cast<const float4*>(s_dz3 + warp * CP);
+#pragma unroll
+      for (int c4 = 0; c4 < CP / 4; ++c4) {
+        const float4 d = dz[c4];
+        zc[4 * c4] = d.x; zc[4 * c4 + 1] = d.y; zc[4 * c4 + 2] = d.z; zc[4 * c4 + 3] = d.w;
+      }
+    }
+    if (p.train) {
+      // (d) dz2 = (dz3 . W2^T) * a (1 - a)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int h = lane + 32 * k;
+        if (k < HK && h < H) {
+          const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CPP);
+          float d = 0.f;
+#pragma unroll
+          for (int c4 = 0; c4 < CP / 4; ++c4) {
+            const float4 wv = w[c4];
+            d = fmaf(zc[4 * c4], wv.x, d);
+            d = fmaf(zc[4 * c4 + 1], wv.y, d);
+            d = fmaf(zc[4 * c4 + 2], wv.z, d);
+            d = fmaf(zc[4 * c4 + 3], wv.w, d);
+          }
+          d *= ak[k] * (1.f - ak[k]);
+          s_dz2[warp * H + h] = d;
+          if (row_ok) p.dz2[(size_t)r * H + h] = d;
+        }
+      }
+      T2_MARK();
+      __syncthreads();
+      T2_MARK();
+      // (e) this tile's contribution to dW2 / db2 / db1 (padded rows hold zeros)
+#pragma unroll
+      for (int j = 0; j < kT2MaxPer; ++j) {
+        if (eh[j] >= 0) {
+          float t = 0.f;
+#pragma unroll
+          for (int w8 = 0; w8 < kT2Rows; ++w8) t = fmaf(s_a2[w8 * H + eh[j]], s_dz3[w8 * CP + ec[j]], t);
+          acc[j] += t;
+        }
+      }
+      if (tid < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < kT2Rows; ++w8) t += s_dz3[w8 * CP + tid];
+        acc_b2 += t;
+      }
+      if (tid < H) {
+        float t = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < kT2Rows; ++w8) t += s_dz2[w8 * H + tid];
+        acc_b1a += t;
+      }
+      if (tid + kT2Threads < H) {
+        float t = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < kT2Rows; ++w8) t += s_dz2[w8 * H + tid + kT2Threads];
+        acc_b1b += t;
+      }
+      T2_MARK();
+      __syncthreads();
+    }
+  }
+
+  if (lane == 0) { s_loss[warp] = loss_w; s_corr[warp] = corr_w; }
+  __syncthreads();
+  float loss_cta = 0.f;
+  if (tid == 0) {
+    int corr = 0;
+    for (int w8 = 0; w8 < kT2Rows; ++w8) { loss_cta += s_loss[w8]; corr += s_corr[w8]; }
+    if (p.correct && corr) atomicAdd(p.correct, corr);   // integer: order-independent
+  }
+
+  if (gridDim.x == 1) {
+    if (tid == 0 && p.loss_sum) *p.loss_sum += loss_cta * p.loss_scale;
+    if (p.train) {
+#pragma unroll
+      for (int j = 0; j < kT2MaxPer; ++j)
+        if (eh[j] >= 0) p.dw2[tid + j * kT2Threads] = acc[j];
+      if (tid < C) p.db2[tid] = acc_b2;
+      if (tid < H) p.db1[tid] = acc_b1a;
+      if (tid + kT2Threads < H) p.db1[tid + kT2Threads] = acc_b1b;
+    }
+    return;
+  }
+
+  // partials -> workspace, last CTA merges them in CTA order
+  float* mine = scratch + (size_t)blockIdx.x * P;
+  if (p.train) {
+#pragma unroll
+    for (int j = 0; j < kT2MaxPer; ++j)
+      if (eh[j] >= 0) mine[tid + j * kT2Threads] = acc[j];
+    if (tid < C) mine[H * C + tid] = acc_b2;
+    if (tid < H) mine[H * C + C + tid] = acc_b1a;
+    if (tid + kT2Threads < H) mine[H * C + C + tid + kT2Threads] = acc_b1b;
+  }
+  if (tid == 0) mine[P - 1] = loss_cta;
+  T2_MARK();
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  }
+  T2_MARK();
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int first = p.train ? 0 : P - 1;
+  // 4 outputs x 8 partials = 32 independent loads in flight per thread; sums stay in CTA order
+  for (int o0 = first + tid; o0 < P; o0 += 4 * kT2Threads) {
+    float t[4] = {0.f, 0.f, 0.f, 0.f};
+    for (unsigned int b0 = 0; b0 < gridDim.x; b0 += 8) {
+      float v[4][8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int o = o0 + q * kT2Threads;
+          v[q][u] = (o < P && b0 + u < gridDim.x) ? __ldcg(scratch + (size_t)(b0 + u) * P + o) : 0.f;
+        }
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t[q] += v[q][u];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int o = o0 + q * kT2Threads;
+      if (o >= P) continue;
+      if (o < H * C) p.dw2[o] = t[q];
+      else if (o < H * C + C) p.db2[o - H * C] = t[q];
+      else if (o < P - 1) p.db1[o - H * C - C] = t[q];
+      else if (p.loss_sum) *p.loss_sum += t[q] * p.loss_scale;
+    }
+  }
+  T2_MARK();
+  if (tid == 0) *counter = 0;   // self-resetting for the next launch
+#undef T2_MARK
 }
 
 // ------------------------------------------------------------------------------------
@@ -408,6 +784,10 @@ __global__ void __launch_bounds__(256) linreg_fwd_bwd_kernel(const float* __rest
 
 using namespace b200ps;
 
+static void* g_tail_dbg = nullptr;
+// Debug hook: device buffer of >= 32 int64 receiving clock64() at the tail kernel's phase boundaries.
+extern "C" int b200ps_mlp_tail_set_debug(void* dev_buf) { g_tail_dbg = dev_buf; return 0; }
+
 extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const float* b2,
                                const int32_t* labels, float* a2_out, float* dz2, float* dw2,
                                float* db2, float* db1, float* loss_sum, int32_t* correct,
@@ -415,34 +795,31 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
                                float grad_scale, float loss_scale, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail: bad shape");
   B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail: C=%d > %d (use gemm + softmax_ce)", C, kMaxClasses);
-  B200PS_REQUIRE(H <= 256 && H * C <= 4096, "mlp_tail: H=%d too wide for the fused head", H);
+  B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail: H=%d too wide for the fused head (<= 128)", H);
   B200PS_REQUIRE(!train || (dz2 && dw2 && db2 && db1), "mlp_tail: training needs gradient outputs");
   TailParams p;
   p.z2 = z2; p.b1 = b1; p.w2 = w2; p.b2 = b2; p.labels = labels; p.a2_out = a2_out; p.dz2 = dz2;
   p.dw2 = dw2; p.db2 = db2; p.db1 = db1; p.loss_sum = loss_sum; p.correct = correct;
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
-  // training on small batches: one CTA => fixed reduction order (bitwise reproducible)
-  int ctas = 1;
-  if (B > 2 * kTailRows) ctas = std::min((B + kTailRows - 1) / kTailRows, 4 * sm_count());
-  p.rows_per_cta = ((B + ctas - 1) / ctas + kTailRows - 1) / kTailRows * kTailRows;
+  p.dbg = reinterpret_cast<long long*>(g_tail_dbg);
+  // rows are dealt to CTAs in tiles of 8; at most one CTA per SM so the merge stays short
+  int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
+  p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;
   ctas = (B + p.rows_per_cta - 1) / p.rows_per_cta;
-  p.atomic_out = ctas > 1 ? 1 : 0;
+  p.atomic_out = 0;
   cudaStream_t s = as_stream(stream);
-  if (p.atomic_out && train) {
-    B200PS_CUDA_CHECK(cudaMemsetAsync(dw2, 0, sizeof(float) * H * C, s));
-    B200PS_CUDA_CHECK(cudaMemsetAsync(db2, 0, sizeof(float) * C, s));
-    B200PS_CUDA_CHECK(cudaMemsetAsync(db1, 0, sizeof(float) * H, s));
-  }
-  const size_t smem = sizeof(float) * ((size_t)H * C + kMaxClasses + H + (size_t)kTailRows * (H + 1) +
-                                       (size_t)kTailRows * kMaxClasses + 32);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    B200PS_CUDA_CHECK(cudaFuncSetAttribute(mlp_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)smem));
-    smem_set = smem;
-  }
-  mlp_tail_kernel<<<ctas, kTailThreads, smem, s>>>(p);
+  const int CP = C <= 16 ? 16 : 32;
+  const int P = H * C + C + H + 1;
+  Workspace ws;
+  int rc = get_workspace(sizeof(float) * (size_t)ctas * P, &ws);
+  if (rc) return rc;
+  const size_t smem = sizeof(float) * ((size_t)H * (CP + 4) + CP + ((H + 3) & ~3) + 2 * (size_t)kT2Rows * H +
+                                       (size_t)kT2Rows * CP);
+  if (CP == 16)
+    mlp_tail2_kernel<16><<<ctas, kT2Threads, smem, s>>>(p, reinterpret_cast<float*>(ws.data), ws.counters);
+  else
+    mlp_tail2_kernel<32><<<ctas, kT2Threads, smem, s>>>(p, reinterpret_cast<float*>(ws.data), ws.counters);
   B200PS_LAUNCH_CHECK();
   return 0;
 }

@@ -52,8 +52,10 @@ struct CommArgs {
 
 template <typename T> struct Vec4;
 template <> struct Vec4<float> {
+  // L2-only (never a stale L1 line; peer data is not cached in the local L2 at all); ordered
+  // after the flag acquire, and — unlike a volatile sys-scope load — free to be batched
   static __device__ __forceinline__ float4 load(const float* p) {
-    return ld_relaxed_sys_v4(reinterpret_cast<const float4*>(p));
+    return __ldcg(reinterpret_cast<const float4*>(p));
   }
   static __device__ __forceinline__ void store(float* p, float4 v) {
     *reinterpret_cast<float4*>(p) = v;
@@ -61,8 +63,7 @@ template <> struct Vec4<float> {
 };
 template <> struct Vec4<__nv_bfloat16> {
   static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
-    uint2 u;
-    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(u.x), "=r"(u.y) : "l"(p) : "memory");
+    uint2 u = __ldcg(reinterpret_cast<const uint2*>(p));
     const float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.x));
     const float2 b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.y));
     return make_float4(a.x, a.y, b.x, b.y);
@@ -93,7 +94,8 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   const uint32_t epoch = pad[kSlotEpoch] + 1;
 
   // -- phase 0: my gradients (written by earlier kernels of this stream) are ready
-  if (blockIdx.x == 0 && tid < world) st_release_sys(a.pads[tid] + kFlagGradsReady + rank, epoch);
+  // (relaxed store: the gradients were written by EARLIER kernels, i.e. are already visible)
+  if (blockIdx.x == 0 && tid < world) st_relaxed_sys(a.pads[tid] + kFlagGradsReady + rank, epoch);
   if (tid < world) wait_flag_geq(pad + kFlagGradsReady + tid, epoch);
   __syncthreads();
 
@@ -102,21 +104,43 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   const float step = a.lr / (float)min(a.replicas_to_aggregate, world);
   float* master = a.masters[rank];
   const long long nvec = (hi - lo) >> 2;
-  for (long long v = (long long)blockIdx.x * blockDim.x + tid; v < nvec;
-       v += (long long)gridDim.x * blockDim.x) {
-    const long long i = lo + (v << 2);
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kU = 4;   // independent float4s per thread per trip: all loads issue before any use
+  for (long long v0 = (long long)blockIdx.x * blockDim.x + tid; v0 < nvec; v0 += kU * stride) {
+    float4 s[kU], w[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      const long long v = v0 + u * stride;
+      if (v < nvec) w[u] = *reinterpret_cast<const float4*>(master + lo + (v << 2));
+    }
     for (int r = 0; r < world; ++r) {  // fixed order => bitwise reproducible
       if (!replica_counts(r, epoch, world, a.replicas_to_aggregate)) continue;
-      const float4 g = Vec4<G>::load(reinterpret_cast<const G*>(a.grads[r]) + i);
-      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      const G* gsrc = reinterpret_cast<const G*>(a.grads[r]) + lo;
+      float4 g[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long v = v0 + u * stride;
+        if (v < nvec) g[u] = Vec4<G>::load(gsrc + (v << 2));
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long v = v0 + u * stride;
+        if (v < nvec) { s[u].x += g[u].x; s[u].y += g[u].y; s[u].z += g[u].z; s[u].w += g[u].w; }
+      }
     }
-    float4 w = *reinterpret_cast<const float4*>(master + i);
-    w.x -= step * s.x; w.y -= step * s.y; w.z -= step * s.z; w.w -= step * s.w;
-    *reinterpret_cast<float4*>(master + i) = w;
-    for (int r = 0; r < world; ++r) {
-      O* dst = reinterpret_cast<O*>(a.outs[r]) + i;
-      if (reinterpret_cast<void*>(dst) != reinterpret_cast<void*>(master + i)) Vec4<O>::store(dst, w);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= nvec) continue;
+      const long long i = lo + (v << 2);
+      float4 x = w[u];
+      x.x -= step * s[u].x; x.y -= step * s[u].y; x.z -= step * s[u].z; x.w -= step * s[u].w;
+      *reinterpret_cast<float4*>(master + i) = x;
+      for (int r = 0; r < world; ++r) {
+        O* dst = reinterpret_cast<O*>(a.outs[r]) + i;
+        if (reinterpret_cast<void*>(dst) != reinterpret_cast<void*>(master + i)) Vec4<O>::store(dst, x);
+      }
     }
   }
 
@@ -126,14 +150,14 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   __syncthreads();
   __shared__ bool s_last;
   if (tid == 0) {
-    __threadfence_system();
+    __threadfence();   // gpu scope here; the last CTA issues the one system-scope fence
     s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
   }
   __syncthreads();
   if (s_last) {
-    if (tid == 0) __threadfence_system();
+    if (tid == 0) __threadfence_system();   // the one system-scope fence ordering every CTA's stores
     __syncthreads();
-    if (tid < world) st_release_sys(a.pads[tid] + kFlagParamsDone + rank, epoch);
+    if (tid < world) st_relaxed_sys(a.pads[tid] + kFlagParamsDone + rank, epoch);
     if (tid < world) wait_flag_geq(pad + kFlagParamsDone + tid, epoch);
     __syncthreads();
     if (tid == 0) {
@@ -199,7 +223,8 @@ __global__ void __launch_bounds__(32) barrier_kernel(uint32_t* const* pads, int 
 using namespace b200ps;
 
 static int comm_grid(long long max_elems, int local_ranks, int want) {
-  int ctas = (int)std::min<long long>(std::max<long long>((max_elems / 4 + 255) / 256, 1), want);
+  // ~4 float4 per thread: few CTAs for small payloads (fences/atomics are per CTA)
+  int ctas = (int)std::min<long long>(std::max<long long>((max_elems / 16 + 255) / 256, 1), want);
   if (local_ranks > 1) ctas = std::max(1, std::min(ctas, sm_count() / local_ranks));  // co-resident
   return ctas;
 }

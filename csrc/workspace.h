@@ -1,0 +1,22 @@
+// b200ps — per-device scratch workspace owned by the library.
+//
+// A few kernels need global memory beyond their inputs and outputs (cross-CTA partial sums,
+// arrival counters).  The workspace is allocated with cudaMalloc on first use and grown on
+// demand, one per device; it is NOT keyed by stream, so launches that use it must not overlap
+// on the GPU (they do not in this framework: one training stream per process).  Growth is an
+// allocation and therefore must happen in an eager call before any CUDA-graph capture.
+#pragma once
+#include "common.h"
+
+namespace b200ps {
+
+struct Workspace {
+  void* data = nullptr;         // scratch bytes (contents undefined between launches)
+  size_t capacity = 0;
+  unsigned int* counters = nullptr;  // 64 zero-initialised uint32 arrival counters (self-resetting)
+};
+
+// Returns the current device's workspace with at least `bytes` of scratch.
+int get_workspace(size_t bytes, Workspace* out);
+
+}  // namespace b200ps

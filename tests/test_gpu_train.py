@@ -141,10 +141,10 @@ def test_sparse_lr_trainer_learns(native_lib):
     from b200ps.metrics.auc import StreamingAUC
     from b200ps.parallel.context import init_from_env
     from b200ps.train import SparseLRTrainer
-    F, B, nnz, spread = 1 << 16, 500, 40, 10
+    F, B, nnz, spread = 1 << 12, 500, 40, 10
     for mode in ("async", "sync"):
         ctx = init_from_env(virtual_world=1)
-        tr = SparseLRTrainer(ctx, features=F, lr=10.0, mode=mode)
+        tr = SparseLRTrainer(ctx, features=F, lr=5.0, mode=mode)
         tr.store.sparse_shard(tr.model.W).mul_(0.01)       # start near zero so learning shows quickly
         batches = []
         for i in range(40):
@@ -161,4 +161,4 @@ def test_sparse_lr_trainer_learns(native_lib):
         for b in batches[32:]:
             pred, _ = tr.predict(b)
             auc.update(pred, b[3])
-        assert auc.result() > 0.6, (mode, auc.result())
+        assert auc.result() > 0.65, (mode, auc.result())
