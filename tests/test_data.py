@@ -1,0 +1,165 @@
+"""Data layer (P18-P24): parser, batch formatter, sharding, loaders, queues — CPU only."""
+import threading
+import time
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from b200ps.data import libsvm, provider, synthetic
+from b200ps.data import queue as Q
+
+
+def test_parse_line_space_and_tab():
+    s = libsvm.Sample().parse_line_libsvm("1 3:0.5\t7:2 11:1e-3\n")
+    assert s.label == 1 and s.indices == [3, 7, 11] and s.values == [0.5, 2.0, 1e-3]
+    s2 = libsvm.Sample().parse_line_libsvm("0")
+    assert s2.label == 0 and s2.indices == []
+
+
+def test_format_samples_sparse_matches_reference_layout_and_csr():
+    lines = ["1 5:1.5 9:2", "0 2:0.25", "1 9:1 5:3 100:0.5"]
+    samples = [libsvm.Sample().parse_line_libsvm(l) for l in lines]
+    labels, fids, fvals, sp_indices, size = libsvm.Sample.format_samples_sparse(samples)
+    assert labels.shape == (3, 1) and size == 3
+    assert fids == [5, 9, 2, 9, 5, 100] and fvals == [1.5, 2.0, 0.25, 1.0, 3.0, 0.5]
+    assert sp_indices == [[0, 5], [0, 9], [1, 2], [2, 9], [2, 5], [2, 100]]     # [row, fid] (lr2.py:82)
+    rp, fid, fv, y = libsvm.Sample.format_samples_csr(samples)
+    rp2, fid2, fv2, y2 = libsvm.csr_from_sparse_triple(sp_indices, fids, fvals, labels)
+    assert rp.tolist() == [0, 2, 3, 6] == rp2.tolist()
+    assert np.array_equal(fid, fid2) and np.allclose(fv, fv2) and np.array_equal(y, y2)
+
+
+_line = st.tuples(st.integers(0, 1),
+                  st.lists(st.tuples(st.integers(0, 10 ** 9), st.floats(-100, 100, allow_nan=False, width=32)),
+                           max_size=12))
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.lists(_line, min_size=1, max_size=20), st.booleans())
+def test_native_parser_equals_python_parser(rows, tabs):
+    sep = "\t" if tabs else " "
+    text = "".join(str(lab) + "".join(f"{sep}{i}:{v!r}" for i, v in feats) + "\n" for lab, feats in rows)
+    rp, fid, fv, y = libsvm.parse_buffer(text.encode())
+    samples = [libsvm.Sample().parse_line_libsvm(l) for l in text.splitlines() if len(l) >= 2]
+    rp2, fid2, fv2, y2 = libsvm.Sample.format_samples_csr(samples)
+    assert np.array_equal(rp, rp2) and np.array_equal(fid, fid2) and np.array_equal(y, y2)
+    assert np.allclose(fv, fv2, rtol=1e-6, atol=1e-30)
+
+
+def test_native_parser_reports_bad_line():
+    with pytest.raises(ValueError, match="line 2"):
+        libsvm.parse_buffer(b"1 3:1\n0 oops\n")
+
+
+def test_file_sharding_rules():
+    files = ",".join(f"f{i}" for i in range(7)) + ","
+    gl = provider.DataProvider.GetFileList
+    assert gl(files, 3, 0) == ["f0", "f3", "f6"] and gl(files, 3, 1) == ["f1", "f4"] and gl(files, 3, 2) == ["f2", "f5"]
+    dp = provider.DataProvider(1, 0, 3, "all")
+    threads = dp.InitThreads([f"f{i}" for i in range(7)], 7, 3)
+    assert [t.files for t in threads] == [["f0", "f3", "f6"], ["f1", "f4"], ["f2", "f5"]]   # files[tid::thread_num]
+
+
+def test_provider_all_mode_and_sampling(tmp_path):
+    tr = synthetic.write_libsvm_files(str(tmp_path / "train"), 4, 250, features=300)
+    te = synthetic.write_libsvm_files(str(tmp_path / "test"), 2, 100, features=300)
+    dp = provider.DataProvider(2, 1, 2, "all", ",".join(tr), ",".join(te), batch_size=64, seed=3)
+    with pytest.raises(RuntimeError):
+        dp.LoadData()                      # the stale reference test calls this without init()
+    dp.init(); dp.LoadData()
+    assert len(dp.train_samples) == 500 and len(dp.test_samples) == 100      # files[1::2]
+    sizes = [len(b) for b in dp.NextBatch("train")]
+    assert sizes == [64] * 7 + [52]
+    before = [s.indices for s in dp.train_samples[:20]]
+    dp.Shuffle()
+    assert sorted(map(tuple, before)) != [] and len(dp.train_samples) == 500
+    labels, fids, fvals, sp, n = dp.GetTestSamplesSampled(0.1, 1000)
+    assert n == 10 and labels.shape == (10, 1)
+    half = provider.DataProvider(1, 0, 2, "all", ",".join(tr), ",".join(te), train_sampling_rate=0.5, seed=7)
+    half.init(); half.LoadData()
+    assert 380 < len(half.train_samples) < 620 and len(half.test_samples) == 200
+
+
+def test_provider_queue_mode(tmp_path):
+    tr = synthetic.write_libsvm_files(str(tmp_path / "train"), 2, 120, features=300)
+    te = synthetic.write_libsvm_files(str(tmp_path / "test"), 1, 80, features=300, seed=9)
+    dp = provider.DataProvider(1, 0, 2, "queue", ",".join(tr), ",".join(te), batch_size=50,
+                               train_queue_capacity=200, test_queue_capacity=200, seed=1)
+    dp.init(); dp.LoadData()
+    for _ in range(6):                      # the loaders loop over the files forever
+        batches = list(dp.NextBatch("train"))
+        assert len(batches) == 1 and len(batches[0]) == 50          # one batch per "epoch"
+    test_b = dp.NextBatchQueue("test")
+    train_ids = {tuple(s.indices) for f in tr for s in [libsvm.Sample().parse_line_libsvm(l) for l in open(f)]}
+    assert all(tuple(s.indices) not in train_ids for s in test_b)   # is_train honoured: test queue gets test rows
+    t0 = time.time(); dp.close(); assert time.time() - t0 < 10
+
+
+def test_fifo_queue_semantics():
+    q = Q.FIFOQueue(3)
+    q.enqueue_many([1, 2, 3])
+    with pytest.raises(Q.DeadlineExceededError):
+        q.enqueue(4, timeout=0.05)
+    assert q.dequeue() == 1 and q.size() == 2
+    assert q.dequeue_many(2) == [2, 3]
+    with pytest.raises(Q.DeadlineExceededError):
+        q.dequeue(timeout=0.05)
+    t = threading.Thread(target=lambda: (time.sleep(0.05), q.enqueue(9)))
+    t.start()
+    assert q.dequeue(timeout=2) == 9
+    t.join()
+    q.enqueue(5)
+    q.close()
+    assert q.dequeue() == 5                     # closed queues still drain
+    with pytest.raises(Q.QueueClosedError):
+        q.dequeue()
+    with pytest.raises(Q.QueueClosedError):
+        q.enqueue(1)
+
+
+def test_batcher_and_slice_producer_pipeline():
+    data = list(range(10)); labels = [i % 3 for i in range(10)]
+    src = Q.slice_input_producer([data, labels], shuffle=False, capacity=4, num_epochs=2)
+    b = Q.Batcher(src, 5, capacity=5)
+    coord = Q.Coordinator()
+    threads = Q.start_queue_runners(coord)
+    got = [b.next(timeout=5) for _ in range(4)]
+    assert [x for batch in got for x, _ in batch] == data + data            # order kept, two epochs
+    with pytest.raises(Q.QueueClosedError):
+        b.next(timeout=5)                                                     # end of input propagates
+    coord.request_stop(); coord.join(threads)
+
+
+def test_coordinator_surfaces_producer_errors():
+    q = Q.FIFOQueue(2)
+    def boom():
+        raise ValueError("bad producer")
+    coord = Q.Coordinator()
+    threads = Q.QueueRunner(q, [boom]).create_threads(coord)
+    coord.wait_for_stop(2)
+    with pytest.raises(ValueError, match="bad producer"):
+        coord.join(threads)
+
+
+def test_synthetic_mnist_next_batch_epochs():
+    ds = synthetic.SyntheticMNIST(250, seed=1)
+    x, y = ds.next_batch(100)
+    assert x.shape == (100, 784) and y.shape == (100,) and 0 <= float(x.min()) and float(x.max()) <= 1
+    ds.next_batch(100)
+    assert ds.epochs_completed == 0
+    ds.next_batch(100)                          # wraps: reshuffle + new epoch
+    assert ds.epochs_completed == 1
+    oh = synthetic.SyntheticMNIST(50, one_hot=True)
+    assert oh.next_batch(10)[1].shape == (10, 10) and oh.labels.shape == (50, 10)
+    sets = synthetic.read_data_sets("/nonexistent")
+    assert sets.train.num_examples == 55000 and sets.test.num_examples == 10000
+
+
+def test_gfile_hdfs_mapping(tmp_path, monkeypatch):
+    (tmp_path / "user").mkdir(); (tmp_path / "user" / "part-0").write_text("1 1:1\n0 2:1\n")
+    with pytest.raises(IOError):
+        libsvm.GFile("hdfs://localhost:9000/user/part-0")
+    monkeypatch.setenv("B200PS_HDFS_ROOT", str(tmp_path))
+    assert libsvm.count_lines("hdfs://localhost:9000/user/part-0") == 2
+    assert libsvm.list_files(str(tmp_path / "user")) == [str(tmp_path / "user" / "part-0")]

@@ -1,0 +1,150 @@
+"""Persistence / observability (P14, P25, P26, P28): checkpoints, export, events, logging — CPU only."""
+import os
+import re
+import struct
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from b200ps.io import crc32c, events, exporter, log, proto as pb, saver, tf_bundle
+
+
+def test_crc32c_known_vectors_native_and_python():
+    # RFC 3720 test vectors
+    assert crc32c.crc32c(b"123456789") == 0xE3069283
+    assert crc32c.crc32c(b"\x00" * 32) == 0x8A9136AA
+    assert crc32c.crc32c(b"\xff" * 32) == 0x62A8AB43
+    assert crc32c._crc_py(bytes(range(32))) == 0x46DD794E == crc32c.crc32c(bytes(range(32)))
+    m = crc32c.masked_crc32c(b"hello")
+    assert crc32c.unmask(m) == crc32c.crc32c(b"hello")
+
+
+def test_bundle_roundtrip_names_shapes_dtypes(tmp_path):
+    rng = np.random.RandomState(0)
+    t = {"global_step": np.float32(12), "weights/Variable": rng.randn(784, 100).astype(np.float32),
+         "weights/Variable_1": rng.randn(100, 10).astype(np.float32), "biases/Variable": np.zeros(100, np.float32),
+         "biases/Variable_1": np.zeros(10, np.float32), "counter": np.arange(5, dtype=np.int64)}
+    prefix = str(tmp_path / "model.ckpt-12")
+    tf_bundle.write_bundle(prefix, t)
+    assert sorted(os.listdir(tmp_path)) == ["model.ckpt-12.data-00000-of-00001", "model.ckpt-12.index"]
+    header, index = tf_bundle.read_bundle_index(prefix)
+    assert header == {"num_shards": 1, "endianness": 0, "version_producer": 1}
+    assert index["global_step"]["shape"] == () and index["global_step"]["dtype"] == 1          # DT_FLOAT scalar
+    assert index["weights/Variable"]["shape"] == (784, 100) and index["counter"]["dtype"] == 9  # DT_INT64
+    # entries are laid out back to back in key order
+    off = 0
+    for name in sorted(t):
+        assert index[name]["offset"] == off
+        off += index[name]["size"]
+    assert off == os.path.getsize(prefix + ".data-00000-of-00001")
+    back = tf_bundle.read_bundle(prefix)
+    assert all(np.array_equal(back[k], t[k]) and back[k].dtype == np.asarray(t[k]).dtype for k in t)
+
+
+def test_bundle_golden_bytes(tmp_path):
+    """Pin the on-disk format: header proto, entry proto, block trailer, footer magic."""
+    prefix = str(tmp_path / "g")
+    tf_bundle.write_bundle(prefix, {"b": np.array([1.0, 2.0], np.float32)})
+    raw = open(prefix + ".index", "rb").read()
+    assert raw[-8:] == struct.pack("<Q", 0xDB4775248B80FB57)
+    data = struct.pack("<ff", 1.0, 2.0)
+    assert open(prefix + ".data-00000-of-00001", "rb").read() == data
+    header = bytes([0x08, 0x01, 0x1A, 0x02, 0x08, 0x01])            # num_shards=1, version{producer=1}
+    entry = (bytes([0x08, 0x01, 0x12, 0x04, 0x12, 0x02, 0x08, 0x02, 0x28, 0x08, 0x35]) +
+             struct.pack("<I", crc32c.masked_crc32c(data)))         # dtype, shape{dim{size=2}}, size=8, crc
+    block = (bytes([0, 0, len(header)]) + header + bytes([0, 1, len(entry)]) + b"b" + entry +
+             struct.pack("<II", 0, 1))                               # restart array [0], count 1
+    assert raw.startswith(block + b"\x00" + struct.pack("<I", crc32c.masked_crc32c(block + b"\x00")))
+    # index block key is the short successor of the last key ("b" -> "c")
+    entries = dict(tf_bundle.read_table(raw))
+    assert set(entries) == {b"", b"b"} and entries[b""] == header and entries[b"b"] == entry
+
+
+def test_bundle_detects_corruption(tmp_path):
+    prefix = str(tmp_path / "c")
+    tf_bundle.write_bundle(prefix, {"w": np.ones(64, np.float32)})
+    p = prefix + ".data-00000-of-00001"
+    raw = bytearray(open(p, "rb").read()); raw[10] ^= 0xFF; open(p, "wb").write(raw)
+    with pytest.raises(ValueError, match="checksum"):
+        tf_bundle.read_bundle(prefix)
+    idx = bytearray(open(prefix + ".index", "rb").read()); idx[3] ^= 0x01; open(prefix + ".index", "wb").write(idx)
+    with pytest.raises(ValueError):
+        tf_bundle.read_bundle_index(prefix)
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.dictionaries(st.text(alphabet="abcdefghij/_0123456789", min_size=1, max_size=40),
+                       st.lists(st.floats(-1e6, 1e6, width=32), max_size=50), min_size=1, max_size=40))
+def test_table_fuzz_roundtrip(d):
+    items = [(k.encode(), struct.pack(f"<{len(v)}f", *v)) for k, v in d.items()]
+    back = tf_bundle.read_table(tf_bundle.build_table(items))
+    assert back == sorted(items)
+
+
+def test_table_many_entries_span_restarts_and_blocks():
+    items = [(f"var/{i:05d}".encode(), bytes([i % 251]) * 700) for i in range(900)]   # > 262144 B => several blocks
+    back = tf_bundle.read_table(tf_bundle.build_table(items))
+    assert back == items
+
+
+def test_saver_state_file_and_max_to_keep(tmp_path):
+    s = saver.Saver(max_to_keep=2)
+    for step in (10, 20, 30):
+        s.save({"w": np.full((2, 2), step, np.float32), "global_step": np.float32(step)}, str(tmp_path / "model.ckpt"), step)
+    txt = open(tmp_path / "checkpoint").read()
+    assert txt.splitlines()[0] == 'model_checkpoint_path: "model.ckpt-30"'
+    assert re.findall(r'all_model_checkpoint_paths: "(.*)"', txt) == ["model.ckpt-20", "model.ckpt-30"]
+    assert not os.path.exists(tmp_path / "model.ckpt-10.index")
+    latest = saver.latest_checkpoint(str(tmp_path))
+    assert latest.endswith("model.ckpt-30") and saver.Saver.restore(latest)["global_step"] == 30
+    assert saver.latest_checkpoint(str(tmp_path / "nothing")) is None
+
+
+def test_events_roundtrip_and_tensorboard_reads_it(tmp_path):
+    w = events.SummaryWriter(str(tmp_path))
+    for step in range(5):
+        w.add_summary({"cost": 2.0 / (step + 1), "accuracy": 0.1 * step}, step)
+    w.close()
+    f = events.find_event_files(str(tmp_path))
+    assert len(f) == 1 and os.path.basename(f[0]).startswith("events.out.tfevents.")
+    recs = list(events.read_events(f[0]))
+    assert recs[0][3] == "brain.Event:2" and [r[1] for r in recs[1:]] == list(range(5))
+    assert recs[3][2]["cost"] == pytest.approx(2.0 / 3) and recs[3][2]["accuracy"] == pytest.approx(0.2)
+    tb = pytest.importorskip("tensorboard.backend.event_processing.event_file_loader")
+    seen = {}
+    for ev in tb.EventFileLoader(f[0]).Load():
+        for v in ev.summary.value:
+            seen.setdefault(v.tag, []).append(ev.step)
+    assert seen == {"cost": list(range(5)), "accuracy": list(range(5))}
+
+
+def test_exporter_layout_and_signatures(tmp_path):
+    e = exporter.Exporter(saver.Saver())
+    with pytest.raises(RuntimeError):
+        e.export(str(tmp_path), "0003", {})
+    e.init(None, named_graph_signatures={"inputs": exporter.generic_signature({"x": "Placeholder:0"}),
+                                         "outputs": exporter.generic_signature({"y": "test/add:0"})})
+    out = e.export(str(tmp_path / "model"), "0003", {"test/weights": np.ones((1, 1), np.float32),
+                                                     "test/bias": np.zeros(1, np.float32)})
+    assert os.path.basename(out) == "00000003"                              # '0003' -> int 3 -> %08d
+    assert sorted(os.listdir(out)) == ["assets", "export.data-00000-of-00001", "export.index", "export.meta", "signature.json"]
+    assert exporter.parse_signatures_from_meta(os.path.join(out, "export.meta")) == {
+        "inputs": {"x": "Placeholder:0"}, "outputs": {"y": "test/add:0"}}
+    sigs, variables = exporter.load_export(out)
+    assert sigs["outputs"] == {"y": "test/add:0"} and variables["test/weights"].shape == (1, 1)
+
+
+def test_log_prefix_format():
+    log.set_role("worker", 3)
+    msg = log.format_message("hello", now=0)
+    assert re.fullmatch(r" \[\d{4}-\d\d-\d\d \d\d:\d\d:\d\d\] \[worker:3\] hello", msg)
+
+
+def test_proto_codec_roundtrip():
+    msg = pb.f_varint(1, 300) + pb.f_bytes(2, "abc") + pb.f_fixed32(6, 0xDEADBEEF) + pb.f_msg(3, pb.f_varint(1, -1))
+    d = pb.decode(msg)
+    assert d[1] == [300] and d[2] == [b"abc"] and d[6] == [0xDEADBEEF]
+    assert pb.decode(d[3][0])[1] == [(1 << 64) - 1]
+    with pytest.raises(ValueError):
+        pb.decode(b"\x0a\x05ab")
