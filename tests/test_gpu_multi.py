@@ -1,0 +1,49 @@
+"""Real multi-GPU runs (one process per GPU over CUDA-IPC symmetric memory): P6-P9, P25."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_multi_gpu_trainers(native_lib, tmp_path):
+    n = min(_ngpu(), 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", "29613", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), str(tmp_path)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    if os.path.isdir(os.path.join(ROOT, "gpurun_out")):          # keep the ranks' output for post-mortems
+        open(os.path.join(ROOT, "gpurun_out", "multi_worker.log"), "w").write(r.stdout + r.stderr)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-6000:]
+    res = json.load(open(tmp_path / "result.json"))
+    assert res["world"] == n
+    assert res["sync_digests_equal"] and res["sync_global_step"] == 60
+    assert res["sync_loss"][1] < res["sync_loss"][0] and res["sync_acc"] > 0.2
+    assert res["async_global_step"] == 40 * n and res["async_loss"][1] < res["async_loss"][0]
+    assert res["wide_digests_equal"] and res["wide_loss"][1] < res["wide_loss"][0]
+    assert res["sparse_async_global_step"] == 10 * n and res["sparse_sync_global_step"] == 10
+    assert res["barrier_epoch"] == 5
+    # a checkpoint taken on n GPUs restores on one (P25)
+    from b200ps.io.saver import Saver, latest_checkpoint
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    from b200ps import ops
+    ck = latest_checkpoint(str(tmp_path))
+    assert ck.endswith("model.ckpt-60")
+    ctx = init_from_env(virtual_world=1)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="sync", use_graph=False)
+    tr.store.load_state_dict(Saver.restore(ck))
+    assert tr.global_step == 60
+    x = torch.empty(2000, 784, device="cuda"); y = torch.empty(2000, device="cuda", dtype=torch.int32)
+    ops.synth_mnist(x, y, seed=1, offset=0)
+    acc, _ = tr.evaluate(x, y)
+    assert abs(acc - res["sync_acc"]) < 1e-6
