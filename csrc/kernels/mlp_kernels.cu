@@ -14,14 +14,6 @@ namespace b200ps {
 
 __device__ __forceinline__ float sigmoidf_acc(float x) { return 1.f / (1.f + __expf(-x)); }
 
-// ------------------------------------------------------------------------------------
-// mlp_tail: rows are processed in tiles of kTailRows; one CTA owns a contiguous row range.
-// With a single CTA (B <= kTailRows * iterations) every reduction has a fixed order, so
-// the sync-replica path is bitwise reproducible; with several CTAs partial sums are merged
-// with fp32 atomics (the caller zeroes the outputs first).
-// ------------------------------------------------------------------------------------
-constexpr int kTailThreads = 512;
-constexpr int kTailRows = 128;
 constexpr int kMaxClasses = 32;
 
 struct TailParams {
@@ -43,256 +35,12 @@ struct TailParams {
   int rows_per_cta;
   float grad_scale;    // 1/B_global for the mean loss
   float loss_scale;    // 1/B for a mean, 1 for a sum
-  int atomic_out;      // gridDim.x > 1
-  long long* dbg;      // optional: clock64() at phase boundaries (thread 0 of CTA 0)
+  int atomic_out;      // unused (kept for ABI stability of the struct)
 };
 
-// Thread layout for the matmul-like phases: 512 threads = 128 (row or hidden index) x 4 groups,
-// each thread keeping a full class vector (CP floats) in registers, so every shared-memory
-// operand is read once per 16/32 FMAs instead of once per FMA.
-template <int CP>
-__global__ void __launch_bounds__(kTailThreads, 1) mlp_tail_kernel(const TailParams p) {
-  extern __shared__ __align__(16) float sm[];
-  const int H = p.H, C = p.C;
-  const int HP = H + 1;  // pad: conflict-free column walks
-  float* s_w2 = sm;                            // [H+1][CP]  (row H unused), zero padded classes
-  float* s_b2 = s_w2 + (H + 1) * CP;           // [CP]
-  float* s_b1 = s_b2 + CP;                     // [H] (+pad to 4)
-  float* s_dz3 = s_b1 + ((H + 3) & ~3);        // [kTailRows][CP]  logits -> dz3
-  float* s_part = s_dz3 + kTailRows * CP;      // [4][128][CP] partial sums
-  float* s_a2 = s_part + 4 * 128 * CP;         // [kTailRows][HP]  activations, later dz2
-  float* s_red = s_a2 + kTailRows * HP;        // [32]
-  __shared__ int s_correct;
-
-  const int tid = threadIdx.x;
-  const int lo7 = tid & 127, grp = tid >> 7;
-  for (int i = tid; i < (H + 1) * CP; i += kTailThreads) {
-    const int h = i / CP, c = i - h * CP;
-    s_w2[i] = (h < H && c < C) ? __ldg(p.w2 + h * C + c) : 0.f;
-  }
-  for (int i = tid; i < CP; i += kTailThreads) s_b2[i] = i < C ? __ldg(p.b2 + i) : 0.f;
-  for (int i = tid; i < H; i += kTailThreads) s_b1[i] = __ldg(p.b1 + i);
-  if (tid == 0) s_correct = 0;
-
-  const int row_begin = blockIdx.x * p.rows_per_cta;
-  const int row_end = min(p.B, row_begin + p.rows_per_cta);
-
-  constexpr int kDw2PerThread = 8;  // supports H*C <= 4096
-  float acc_dw2[kDw2PerThread];
-#pragma unroll
-  for (int k = 0; k < kDw2PerThread; ++k) acc_dw2[k] = 0.f;
-  float acc_db1 = 0.f;  // thread h < H owns db1[h]
-  float acc_db2 = 0.f;  // thread c < C owns db2[c]
-  float loss_local = 0.f;
-  const int Hq = (H + 3) >> 2;
-  __syncthreads();
-  int dbg_i = 0;
-#define TAIL_MARK() do { if (p.dbg && tid == 0 && blockIdx.x == 0) p.dbg[dbg_i++] = clock64(); } while (0)
-  TAIL_MARK();
-
-  for (int r0 = row_begin; r0 < row_end; r0 += kTailRows) {
-    const int nrows = min(kTailRows, row_end - r0);
-    // (1) a2 = sigmoid(z2 + b1); all of a thread's loads are issued before the first use.
-    {
-      const float* __restrict__ zsrc = p.z2 + (size_t)r0 * H;
-      const int n = nrows * H;
-      constexpr int kU = 8;
-      for (int base = 0; base < kTailRows * H; base += kU * kTailThreads) {
-        float v[kU];
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-          const int i = base + u * kTailThreads + tid;
-          v[u] = i < n ? __ldg(zsrc + i) : 0.f;
-        }
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-          const int i = base + u * kTailThreads + tid;
-          if (i < kTailRows * H) {
-            const int r = i / H, h = i - r * H;
-            const float a = sigmoidf_acc(v[u] + s_b1[h]);   // rows >= nrows: finite filler
-            s_a2[r * HP + h] = a;
-            if (i < n && p.a2_out) p.a2_out[(size_t)(r0 + r) * H + h] = a;
-          }
-        }
-      }
-    }
-    __syncthreads();
-    TAIL_MARK();
-    // (2) partial logits over a quarter of the hidden units: thread = (row lo7, quarter grp)
-    {
-      float acc[CP];
-#pragma unroll
-      for (int c = 0; c < CP; ++c) acc[c] = 0.f;
-      const float* a = s_a2 + lo7 * HP;
-      const int h1 = min(H, (grp + 1) * Hq);
-      for (int h = grp * Hq; h < h1; ++h) {
-        const float av = a[h];
-        const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CP);
-#pragma unroll
-        for (int c4 = 0; c4 < CP / 4; ++c4) {
-          const float4 wv = w[c4];
-          acc[4 * c4] = fmaf(av, wv.x, acc[4 * c4]);
-          acc[4 * c4 + 1] = fmaf(av, wv.y, acc[4 * c4 + 1]);
-          acc[4 * c4 + 2] = fmaf(av, wv.z, acc[4 * c4 + 2]);
-          acc[4 * c4 + 3] = fmaf(av, wv.w, acc[4 * c4 + 3]);
-        }
-      }
-      float4* dst = reinterpret_cast<float4*>(s_part + (grp * 128 + lo7) * CP);
-#pragma unroll
-      for (int c4 = 0; c4 < CP / 4; ++c4)
-        dst[c4] = make_float4(acc[4 * c4], acc[4 * c4 + 1], acc[4 * c4 + 2], acc[4 * c4 + 3]);
-    }
-    __syncthreads();
-    TAIL_MARK();
-    for (int i = tid; i < kTailRows * CP; i += kTailThreads) {
-      const int c = i % CP;
-      s_dz3[i] = s_b2[c] + ((s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]));
-    }
-    __syncthreads();
-    TAIL_MARK();
-    // (3) stable log-softmax, loss, accuracy, dz3 = (p - y) * grad_scale : one thread per row
-    if (tid < kTailRows) {
-      float* z = s_dz3 + tid * CP;
-      if (tid < nrows) {
-        const int label = p.labels[r0 + tid];
-        float m = z[0];
-        int arg = 0;
-        for (int c = 1; c < C; ++c)
-          if (z[c] > m) { m = z[c]; arg = c; }
-        float se = 0.f;
-        for (int c = 0; c < C; ++c) se += __expf(z[c] - m);
-        const float lse = m + __logf(se);
-        loss_local += (lse - z[label]);
-        if (arg == label) atomicAdd(&s_correct, 1);
-        const float inv = 1.f / se;
-        for (int c = 0; c < C; ++c) {
-          const float pr = __expf(z[c] - m) * inv;
-          if (p.probs_out) p.probs_out[(size_t)(r0 + tid) * C + c] = pr;
-          z[c] = (pr - (c == label ? 1.f : 0.f)) * p.grad_scale;
-        }
-        for (int c = C; c < CP; ++c) z[c] = 0.f;
-      } else {
-        for (int c = 0; c < CP; ++c) z[c] = 0.f;   // padded rows contribute nothing below
-      }
-    }
-    __syncthreads();
-    TAIL_MARK();
-    if (p.train) {
-      // (4) dW2 += a2^T dz3, db2 += 1^T dz3 : thread = (hidden unit lo7 [H = the ones row], row block grp)
-      {
-        float acc[CP];
-#pragma unroll
-        for (int c = 0; c < CP; ++c) acc[c] = 0.f;
-        if (lo7 <= H) {
-          for (int r = grp * 32; r < grp * 32 + 32; ++r) {
-            const float av = lo7 < H ? s_a2[r * HP + lo7] : 1.f;
-            const float4* dz = reinterpret_cast<const float4*>(s_dz3 + r * CP);
-#pragma unroll
-            for (int c4 = 0; c4 < CP / 4; ++c4) {
-              const float4 d = dz[c4];
-              acc[4 * c4] = fmaf(av, d.x, acc[4 * c4]);
-              acc[4 * c4 + 1] = fmaf(av, d.y, acc[4 * c4 + 1]);
-              acc[4 * c4 + 2] = fmaf(av, d.z, acc[4 * c4 + 2]);
-              acc[4 * c4 + 3] = fmaf(av, d.w, acc[4 * c4 + 3]);
-            }
-          }
-        }
-        float4* dst = reinterpret_cast<float4*>(s_part + (grp * 128 + lo7) * CP);
-#pragma unroll
-        for (int c4 = 0; c4 < CP / 4; ++c4)
-          dst[c4] = make_float4(acc[4 * c4], acc[4 * c4 + 1], acc[4 * c4 + 2], acc[4 * c4 + 3]);
-      }
-      __syncthreads();
-      TAIL_MARK();
-#pragma unroll
-      for (int k = 0; k < kDw2PerThread; ++k) {
-        const int e = tid + k * kTailThreads;
-        if (e < H * C) {
-          const int h = e / C, c = e - h * C;
-          const int i = h * CP + c;
-          acc_dw2[k] += (s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]);
-        }
-      }
-      if (tid < C) {
-        const int i = H * CP + tid;
-        acc_db2 += (s_part[i] + s_part[128 * CP + i]) + (s_part[2 * 128 * CP + i] + s_part[3 * 128 * CP + i]);
-      }
-      TAIL_MARK();
-      // (5) dz2 = (dz3 . W2^T) * a2 (1 - a2), in place over s_a2 : thread = (row lo7, quarter grp)
-      {
-        float dz[CP];
-        const float4* src = reinterpret_cast<const float4*>(s_dz3 + lo7 * CP);
-#pragma unroll
-        for (int c4 = 0; c4 < CP / 4; ++c4) {
-          const float4 d = src[c4];
-          dz[4 * c4] = d.x; dz[4 * c4 + 1] = d.y; dz[4 * c4 + 2] = d.z; dz[4 * c4 + 3] = d.w;
-        }
-        float* a = s_a2 + lo7 * HP;
-        const int h1 = min(H, (grp + 1) * Hq);
-        for (int h = grp * Hq; h < h1; ++h) {
-          const float4* w = reinterpret_cast<const float4*>(s_w2 + h * CP);
-          float d = 0.f;
-#pragma unroll
-          for (int c4 = 0; c4 < CP / 4; ++c4) {
-            const float4 wv = w[c4];
-            d = fmaf(dz[4 * c4], wv.x, d);
-            d = fmaf(dz[4 * c4 + 1], wv.y, d);
-            d = fmaf(dz[4 * c4 + 2], wv.z, d);
-            d = fmaf(dz[4 * c4 + 3], wv.w, d);
-          }
-          const float av = a[h];
-          a[h] = d * av * (1.f - av);
-        }
-      }
-      __syncthreads();
-      TAIL_MARK();
-      for (int i = tid; i < nrows * H; i += kTailThreads) {   // coalesced dz2 store
-        const int r = i / H, h = i - r * H;
-        p.dz2[(size_t)r0 * H + i] = s_a2[r * HP + h];
-      }
-      TAIL_MARK();
-      // (6) db1 += 1^T dz2 : thread = (hidden unit lo7, row block grp), then a fixed-order merge
-      {
-        float sacc = 0.f;
-        if (lo7 < H)
-          for (int r = grp * 32; r < grp * 32 + 32; ++r) sacc += s_a2[r * HP + lo7];
-        s_red[0] = 0.f;  // (keeps s_red initialised for the tail reduction below)
-        s_part[grp * 128 + lo7] = sacc;
-      }
-      __syncthreads();
-      if (tid < H) acc_db1 += (s_part[tid] + s_part[128 + tid]) + (s_part[256 + tid] + s_part[384 + tid]);
-    }
-    __syncthreads();
-  }
-
-  TAIL_MARK();
-  // block-level loss reduction in a fixed order
-  float l = warp_sum(loss_local);
-  if ((tid & 31) == 0) s_red[tid >> 5] = l;
-  __syncthreads();
-  if (tid == 0) {
-    float tot = 0.f;
-    for (int w = 0; w < kTailThreads / 32; ++w) tot += s_red[w];
-    tot *= p.loss_scale;
-    if (p.loss_sum) { if (p.atomic_out) atomicAdd(p.loss_sum, tot); else *p.loss_sum += tot; }
-    if (p.correct) atomicAdd(p.correct, s_correct);
-  }
-  if (p.train) {
-#pragma unroll
-    for (int k = 0; k < kDw2PerThread; ++k) {
-      const int e = tid + k * kTailThreads;
-      if (e < H * C) { if (p.atomic_out) atomicAdd(p.dw2 + e, acc_dw2[k]); else p.dw2[e] = acc_dw2[k]; }
-    }
-    if (tid < C) { if (p.atomic_out) atomicAdd(p.db2 + tid, acc_db2); else p.db2[tid] = acc_db2; }
-    if (tid < H) { if (p.atomic_out) atomicAdd(p.db1 + tid, acc_db1); else p.db1[tid] = acc_db1; }
-  }
-  TAIL_MARK();
-#undef TAIL_MARK
-}
-
 // ------------------------------------------------------------------------------------
-// mlp_tail v2: the same math spread over many CTAs.  One SM cannot issue the ~80k warp
-// instructions of the head in less than ~20 us, so rows are dealt to CTAs in tiles of 8
+// mlp_tail: one SM cannot issue the ~80k warp instructions of the head in less than ~20 us
+// (measured), so rows are dealt to CTAs in tiles of 8
 // (one warp per row, lanes over hidden units, class vectors in registers, warp shuffles for
 // the row reductions).  Cross-row sums (dW2, db2, db1, loss) are accumulated per CTA in a
 // fixed order, written to the library workspace, and merged in CTA order by the last CTA to
@@ -344,11 +92,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
   float acc_b2 = 0.f, acc_b1a = 0.f, acc_b1b = 0.f;   // thread c < C ; threads h = tid, tid + 256 < H
   float loss_w = 0.f;
   int corr_w = 0;
-  int dbg_i = 0;
-#define T2_MARK() do { if (p.dbg && tid == 0) p.dbg[blockIdx.x * 16 + dbg_i++] = clock64(); } while (0)
-  T2_MARK();
   __syncthreads();
-  T2_MARK();
 
   for (int r0 = row_begin; r0 < row_end; r0 += kT2Rows) {
     const int r = r0 + warp;
@@ -432,7 +176,6 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
     const float mine = (row_ok && cls_ok) ? (pr - (myc == label ? 1.f : 0.f)) * p.grad_scale : 0.f;
     if (row_ok && p.probs_out && lane < CP && cls_ok) p.probs_out[(size_t)r * C + myc] = pr;
     if (lane < CP) s_dz3[warp * CP + lane] = mine;
-    T2_MARK();
     __syncwarp();
     {   // every lane needs the whole dz3 row for (d): broadcast reads back from shared memory
       const float4* dz = reinterpret_cast<const float4*>(s_dz3 + warp * CP);
@@ -463,9 +206,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
           if (row_ok) p.dz2[(size_t)r * H + h] = d;
         }
       }
-      T2_MARK();
       __syncthreads();
-      T2_MARK();
       // (e) this tile's contribution to dW2 / db2 / db1 (padded rows hold zeros)
 #pragma unroll
       for (int j = 0; j < kT2MaxPer; ++j) {
@@ -494,7 +235,6 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
         for (int w8 = 0; w8 < kT2Rows; ++w8) t += s_dz2[w8 * H + tid + kT2Threads];
         acc_b1b += t;
       }
-      T2_MARK();
       __syncthreads();
     }
   }
@@ -532,13 +272,11 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
     if (tid + kT2Threads < H) mine[H * C + C + tid + kT2Threads] = acc_b1b;
   }
   if (tid == 0) mine[P - 1] = loss_cta;
-  T2_MARK();
   __syncthreads();
   if (tid == 0) {
     __threadfence();
     s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
   }
-  T2_MARK();
   __syncthreads();
   if (!s_last) return;
   __threadfence();
@@ -570,9 +308,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
       else if (p.loss_sum) *p.loss_sum += t[q] * p.loss_scale;
     }
   }
-  T2_MARK();
   if (tid == 0) *counter = 0;   // self-resetting for the next launch
-#undef T2_MARK
 }
 
 // ------------------------------------------------------------------------------------
@@ -784,10 +520,6 @@ __global__ void __launch_bounds__(256) linreg_fwd_bwd_kernel(const float* __rest
 
 using namespace b200ps;
 
-static void* g_tail_dbg = nullptr;
-// Debug hook: device buffer of >= 32 int64 receiving clock64() at the tail kernel's phase boundaries.
-extern "C" int b200ps_mlp_tail_set_debug(void* dev_buf) { g_tail_dbg = dev_buf; return 0; }
-
 extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const float* b2,
                                const int32_t* labels, float* a2_out, float* dz2, float* dw2,
                                float* db2, float* db1, float* loss_sum, int32_t* correct,
@@ -802,7 +534,6 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
   p.dw2 = dw2; p.db2 = db2; p.db1 = db1; p.loss_sum = loss_sum; p.correct = correct;
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
-  p.dbg = reinterpret_cast<long long*>(g_tail_dbg);
   // rows are dealt to CTAs in tiles of 8; at most one CTA per SM so the merge stays short
   int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
   p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;
