@@ -555,6 +555,89 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
   return 0;
 }
 
+// ------------------------------------------------------------------------------------
+// b200ps_mlp_tail_static: the same head computation for hosts that must not allocate.
+//
+// b200ps_mlp_tail above takes its cross-CTA scratch from the library workspace, which is
+// cudaMalloc'ed (and grown) on demand.  Some embedders cannot tolerate that: a serving or
+// simulation process that has handed the whole device to its own memory plan (a later
+// cudaMalloc from a plug-in fails, or silently eats another tenant's budget), and control
+// loops with a latency bound, where cudaMalloc's implicit device-wide synchronisation is not
+// acceptable at step time.  For them the partial sums live in a fixed array inside this
+// library's device image instead.
+//
+//   * capacity: kTailStaticFloats floats (1 MiB) of partials + one arrival counter, resident
+//     on every GPU that loads libb200ps.so until the process exits;
+//   * a launch needs ctas * (H*C + C + H + 1) floats (ctas = row tiles, at most one per SM);
+//     larger problems are refused with B200PS_ERR_INVALID — use b200ps_mlp_tail for those;
+//   * the array is shared by every call and keeps the previous call's contents: the counter
+//     is cleared on the stream before each launch, the partials are always fully rewritten
+//     before they are read.  Two calls whose kernels overlap on the GPU (different streams,
+//     no ordering between them) race on it — serialise them;
+//   * the first call on each device looks the array's device address up with
+//     cudaGetSymbolAddress (one-time set-up, cached per device).  Make that first call during
+//     start-up, before any stream capture is begun;
+//   * no cudaMalloc / cudaFree / allocating library routine is reached from this entry point.
+// ------------------------------------------------------------------------------------
+constexpr size_t kTailStaticFloats = 256 * 1024;
+constexpr size_t kTailStaticCounterWords = 64;
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
+static __device__ __align__(256) float g_tail_static_scratch[kTailStaticFloats + kTailStaticCounterWords];
+static float* g_tail_static_addr[64] = {nullptr};   // per-device result of the symbol look-up
+
+extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const float* w2, const float* b2,
+                                      const int32_t* labels, float* a2_out, float* dz2, float* dw2,
+                                      float* db2, float* db1, float* loss_sum, int32_t* correct,
+                                      float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
+                                      float grad_scale, float loss_scale, b200ps_stream_t stream) {
+  B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail_static: bad shape");
+  B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail_static: C=%d > %d", C, kMaxClasses);
+  B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail_static: H=%d too wide for the fused head (<= 128)", H);
+  B200PS_REQUIRE(!train || (dz2 && dw2 && db2 && db1), "mlp_tail_static: training needs gradient outputs");
+  TailParams p;
+  p.z2 = z2; p.b1 = b1; p.w2 = w2; p.b2 = b2; p.labels = labels; p.a2_out = a2_out; p.dz2 = dz2;
+  p.dw2 = dw2; p.db2 = db2; p.db1 = db1; p.loss_sum = loss_sum; p.correct = correct;
+  p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
+  p.grad_scale = grad_scale; p.loss_scale = loss_scale;
+  int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
+  p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;
+  ctas = (B + p.rows_per_cta - 1) / p.rows_per_cta;
+  p.atomic_out = 0;
+  const int CP = C <= 16 ? 16 : 32;
+  const size_t P = (size_t)H * C + C + H + 1;
+  const size_t need = (size_t)ctas * P;
+  B200PS_REQUIRE(need <= kTailStaticFloats,
+                 "mlp_tail_static: B=%d H=%d C=%d needs %zu bytes of static scratch, the built-in maximum is "
+                 "%zu bytes (use b200ps_mlp_tail, which allocates a workspace)",
+                 B, H, C, need * sizeof(float), kTailStaticFloats * sizeof(float));
+
+  // one-time, per-device set-up: resolve the array's device address with that device current
+  int dev = 0;
+  B200PS_CUDA_CHECK(cudaGetDevice(&dev));
+  B200PS_REQUIRE(dev >= 0 && dev < 64, "mlp_tail_static: device index %d out of range", dev);
+  float* scratch = g_tail_static_addr[dev];
+  if (scratch == nullptr) {
+    float* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_tail_static_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return set_error(B200PS_ERR_CUDA, "mlp_tail_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                       cudaGetErrorString(e));
+    g_tail_static_addr[dev] = scratch = ptr;
+  }
+  unsigned int* counter = reinterpret_cast<unsigned int*>(scratch + kTailStaticFloats);
+  cudaStream_t s = as_stream(stream);
+  // the arrival counter must start at zero; a previous call that died mid-way may have left it dirty
+  B200PS_CUDA_CHECK(cudaMemsetAsync(counter, 0, sizeof(unsigned int), s));
+  const size_t smem = sizeof(float) * ((size_t)H * (CP + 4) + CP + ((H + 3) & ~3) + 2 * (size_t)kT2Rows * H +
+                                       (size_t)kT2Rows * CP);
+  if (CP == 16)
+    mlp_tail2_kernel<16><<<ctas, kT2Threads, smem, s>>>(p, scratch, counter);
+  else
+    mlp_tail2_kernel<32><<<ctas, kT2Threads, smem, s>>>(p, scratch, counter);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int b200ps_softmax_ce(const void* logits, const int32_t* labels, void* dlogits,
                                  float* loss_sum, int32_t* correct, int32_t B, int32_t C, int64_t ld,
                                  int32_t dtype, float grad_scale, float loss_scale,

@@ -91,6 +91,26 @@ int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const flo
                     int32_t H, int32_t C, int32_t train, float grad_scale, float loss_scale,
                     b200ps_stream_t stream);
 
+/* The same head computation, for callers that may not allocate (no counterpart in the
+ * reference, which has no device code at all).  b200ps_mlp_tail draws its cross-CTA scratch
+ * from a cudaMalloc'ed, growable library workspace; a host process that has committed all
+ * device memory to its own plan, or a latency-bound loop that cannot absorb cudaMalloc's
+ * device-wide synchronisation, can call this variant instead: the scratch is a fixed 1 MiB
+ * array inside the library's device image (held by every GPU that loads the library).
+ * Same arguments and results as b200ps_mlp_tail.  Limits and rules:
+ *   - ctas * (H*C + C + H + 1) * 4 bytes must fit in 1 MiB (ctas = ceil(B/8) capped at the SM
+ *     count); otherwise B200PS_ERR_INVALID is returned and nothing is launched;
+ *   - the array is shared by all calls: launches that could overlap on the GPU must be
+ *     serialised by the caller;
+ *   - the first call on a device performs a one-time address look-up; make it at start-up,
+ *     before beginning any stream capture;
+ *   - never calls cudaMalloc/cudaFree or any allocating routine. */
+int b200ps_mlp_tail_static(const float* z2, const float* b1, const float* w2, const float* b2,
+                           const int32_t* labels, float* a2_out, float* dz2, float* dw2,
+                           float* db2, float* db1, float* loss_sum, int32_t* correct,
+                           float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
+                           float grad_scale, float loss_scale, b200ps_stream_t stream);
+
 /* Wide-head softmax cross-entropy: logits [B,C] (ld = row stride) -> dlogits (same dtype,
  * may alias logits, may be NULL), loss_sum += , correct += .  C <= 16384. */
 int b200ps_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, float* loss_sum,
