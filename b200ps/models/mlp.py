@@ -78,7 +78,7 @@ class SigmoidMLP:
         k = (batch, key)
         if k not in self._bufs:
             self._bufs[k] = dict(
-                z2=torch.empty(batch, self.hidden, device=device),
+                z2=torch.zeros(batch, self.hidden, device=device),
                 dz2=torch.empty(batch, self.hidden, device=device),
                 loss=torch.zeros(1, device=device),
                 correct=torch.zeros(1, device=device, dtype=torch.int32))
@@ -86,24 +86,29 @@ class SigmoidMLP:
 
     # -- GPU path -------------------------------------------------------------------------
     def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
-                         global_batch: Optional[int] = None):
+                         global_batch: Optional[int] = None, row_offset: Optional[torch.Tensor] = None,
+                         batch: Optional[int] = None):
         """Forward + backward of one worker's batch; gradients land in ``store.grad(...)``.
-        Returns the (device) loss tensor accumulator and the correct-count tensor."""
-        B = x.shape[0]
+        Returns the (device) loss tensor and the correct-count tensor (both overwritten per step).
+
+        With ``row_offset`` (int32 device scalar) ``x``/``labels`` are a whole resident dataset and
+        the batch is rows ``[*row_offset, *row_offset + batch)`` — read on the device, no copies."""
+        B = x.shape[0] if row_offset is None else batch
         bufs = self._buffers(B, x.device, 0 if rank is None else rank)
         z2, dz2, loss, correct = bufs["z2"], bufs["dz2"], bufs["loss"], bufs["correct"]
         w1 = store.var(self.W1, rank)
-        loss.zero_(); correct.zero_()
+        off = dict(a_row_offset=row_offset, a_rows=B) if row_offset is not None else {}
         if self.split_k > 1:
-            z2.zero_()
-            ops.gemm(x, w1, z2, b_mn_major=True, epilogue=ops.EPI_ATOMIC_ADD, split_k=self.split_k)
+            # z2 starts at zero (allocation) and the head kernel re-zeroes it after reading it
+            ops.gemm(x, w1, z2, b_mn_major=True, epilogue=ops.EPI_ATOMIC_ADD, split_k=self.split_k, **off)
         else:
-            ops.gemm(x, w1, z2, b_mn_major=True)
+            ops.gemm(x, w1, z2, b_mn_major=True, **off)
         ops.mlp_tail(z2, store.var(self.B1, rank), store.var(self.W2, rank), store.var(self.B2, rank),
                      labels, loss_sum=loss, correct=correct, dz2=dz2, dw2=store.grad(self.W2, rank),
                      db2=store.grad(self.B2, rank), db1=store.grad(self.B1, rank), train=True,
-                     grad_scale=1.0 / B, loss_scale=1.0 / B)
-        ops.gemm(x, dz2, store.grad(self.W1, rank), a_mn_major=True, b_mn_major=True)
+                     grad_scale=1.0 / B, loss_scale=1.0 / B, overwrite_stats=True,
+                     clear_z2=self.split_k > 1, label_offset=row_offset)
+        ops.gemm(x, dz2, store.grad(self.W1, rank), a_mn_major=True, b_mn_major=True, **off)
         return loss, correct
 
     def evaluate(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None):

@@ -49,6 +49,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          dsigmoid_of: Optional[torch.Tensor] = None, epilogue: int = EPI_STORE, split_k: int = 1,
          sgd_master: Optional[torch.Tensor] = None, sgd_lowp: Optional[torch.Tensor] = None,
          sgd_lr: float = 0.0, out_dtype: Optional[torch.dtype] = None, max_ctas: int = 0,
+         a_row_offset: Optional[torch.Tensor] = None, a_rows: Optional[int] = None,
          stream=None) -> Optional[torch.Tensor]:
     """tcgen05/TMA GEMM  ``out[M,N] = epilogue(alpha * op(a) @ op(b))``.
 
@@ -56,11 +57,25 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     ``b`` is ``[N,K]`` (K-major) or, with ``b_mn_major``, stored ``[K,N]``.
     fp32 operands run on the tensor cores as tf32.  Replaces tf.matmul and its gradients
     (example.py:95,97,118).
+
+    Resident datasets: with ``a_row_offset`` (int32 device scalar) and ``a_rows`` (rows this call
+    consumes), ``a`` is the WHOLE stored array and the kernel reads rows
+    ``[*a_row_offset, *a_row_offset + a_rows)`` of it — the offset is dereferenced on the device,
+    so a CUDA graph can walk a dataset without per-step copies.
     """
     _cuda(a, b, out, bias, dsigmoid_of, sgd_master, sgd_lowp)
     if a.dtype != b.dtype:
         raise TypeError("gemm: A and B dtypes differ")
     M, K = (a.shape[1], a.shape[0]) if a_mn_major else (a.shape[0], a.shape[1])
+    a_rows_total = 0
+    if a_row_offset is not None:
+        if a_rows is None or a_row_offset.dtype != torch.int32:
+            raise ValueError("gemm: a_row_offset needs a_rows and an int32 device scalar")
+        a_rows_total = a.shape[0]
+        if a_mn_major:
+            K = a_rows
+        else:
+            M = a_rows
     N, Kb = (b.shape[1], b.shape[0]) if b_mn_major else (b.shape[0], b.shape[1])
     if K != Kb:
         raise ValueError(f"gemm: reduction dims differ ({K} vs {Kb})")
@@ -98,24 +113,29 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     args.split_k = split_k
     args.sgd_master, args.sgd_lowp, args.sgd_lr = ptr(sgd_master), ptr(sgd_lowp), sgd_lr
     args.max_ctas = max_ctas
+    args.a_row_offset, args.a_rows_total = ptr(a_row_offset), a_rows_total
     check(native.load().b200ps_gemm(C.byref(args), stream_ptr(stream)), "gemm")
     return out
 
 
 def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=None, db2=None,
              db1=None, a2_out=None, probs_out=None, train=True, grad_scale=None, loss_scale=None,
-             stream=None):
+             overwrite_stats=False, clear_z2=False, label_offset=None, stream=None):
     """Fused narrow MLP head (K6): see include/b200ps.h b200ps_mlp_tail."""
     _cuda(z2, b1, w2, b2, labels)
     B, H = z2.shape
     Cn = w2.shape[1]
     if labels.dtype != torch.int32:
         raise TypeError("mlp_tail: labels must be int32 class ids")
+    if label_offset is not None and label_offset.dtype != torch.int32:
+        raise TypeError("mlp_tail: label_offset must be an int32 device scalar")
     gs = (1.0 / B) if grad_scale is None else grad_scale
     ls = (1.0 / B) if loss_scale is None else loss_scale
     check(native.load().b200ps_mlp_tail(ptr(z2), ptr(b1), ptr(w2), ptr(b2), ptr(labels), ptr(a2_out),
                                         ptr(dz2), ptr(dw2), ptr(db2), ptr(db1), ptr(loss_sum),
                                         ptr(correct), ptr(probs_out), B, H, Cn, int(train), gs, ls,
+                                        (native.TAIL_OVERWRITE_STATS if overwrite_stats else 0) |
+                                        (native.TAIL_CLEAR_Z2 if clear_z2 else 0), ptr(label_offset),
                                         stream_ptr(stream)), "mlp_tail")
 
 
@@ -232,11 +252,13 @@ def signal_pad_words() -> int:
 
 
 def push_sync_sgd(pads, masters, outs, grads, bounds, global_steps, *, world, rank_base, local_ranks=1,
-                  max_shard_elems, dtype, replicas_to_aggregate, lr, max_ctas=0, stream=None):
+                  max_shard_elems, dtype, replicas_to_aggregate, lr, max_ctas=0, cursor=None, cursor_step=0,
+                  cursor_wrap=1, stream=None):
     d = DT_BF16 if dtype == torch.bfloat16 else DT_F32
     check(native.load().b200ps_push_sync_sgd(ptr(pads), ptr(masters), ptr(outs), ptr(grads), ptr(bounds),
                                              ptr(global_steps), world, rank_base, local_ranks,
                                              max_shard_elems, d, d, replicas_to_aggregate, lr, max_ctas,
+                                             ptr(cursor), cursor_step, cursor_wrap,
                                              stream_ptr(stream)), "push_sync_sgd")
 
 

@@ -37,12 +37,14 @@ class GemmArgs(C.Structure):
         ("sgd_master", C.c_void_p), ("sgd_lowp", C.c_void_p),
         ("sgd_lr", C.c_float),
         ("max_ctas", C.c_int32),
+        ("a_row_offset", C.c_void_p), ("a_rows_total", C.c_int64),
     ]
 
 
 DT_BF16, DT_F32 = 0, 1
 ACT_NONE, ACT_SIGMOID = 0, 1
 EPI_STORE, EPI_ATOMIC_ADD, EPI_SGD = 0, 1, 2
+TAIL_OVERWRITE_STATS, TAIL_CLEAR_Z2 = 1, 2
 
 
 def lib_path() -> str:

@@ -38,8 +38,8 @@ class SyncReplicasSGD:
     def prepare(self, store, rank: Optional[int] = None) -> None:
         pass   # push_sync broadcast the fresh values already: the pull is fused into the push
 
-    def apply(self, store, rank: Optional[int] = None) -> None:
+    def apply(self, store, rank: Optional[int] = None, **cursor_kw) -> None:
         total = self.total_num_replicas or store.world
         if total != store.world:
             raise ValueError(f"total_num_replicas={total} but {store.world} workers are running")
-        store.push_sync(self.learning_rate, self.replicas_to_aggregate or total)
+        store.push_sync(self.learning_rate, self.replicas_to_aggregate or total, **cursor_kw)

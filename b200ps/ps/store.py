@@ -352,7 +352,7 @@ class ParameterStore:
                      include_self=include_self or g.master is not None)
 
     def push_sync(self, lr: float, replicas_to_aggregate: Optional[int] = None, groups=None,
-                  count_step: bool = True) -> None:
+                  count_step: bool = True, cursor=None, cursor_step: int = 0, cursor_wrap: int = 1) -> None:
         base, n = self._ranks()
         R = replicas_to_aggregate or self.world
         gl = list(self._iter_groups(groups))
@@ -362,7 +362,9 @@ class ParameterStore:
             ops.push_sync_sgd(self.t_pads, g.t_masters, g.t_outs, g.t_grads, g.bounds, gs,
                               world=self.world, rank_base=base, local_ranks=n,
                               max_shard_elems=g.layout.max_shard, dtype=g.dtype,
-                              replicas_to_aggregate=R, lr=lr)
+                              replicas_to_aggregate=R, lr=lr,
+                              cursor=cursor if i == len(gl) - 1 else None, cursor_step=cursor_step,
+                              cursor_wrap=cursor_wrap)
 
     def push_async(self, lr: float, rank: Optional[int] = None, groups=None, count_step: bool = True) -> None:
         """Hogwild push of ONE worker's gradients (fp32 groups only)."""

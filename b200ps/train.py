@@ -114,6 +114,32 @@ class MLPTrainer(_TrainerBase):
         if self.mode == "sync":
             self.opt.apply(st)
 
+    # -- resident dataset: the whole (per-worker) epoch lives on the device and the captured step
+    #    walks it through a device-side cursor — no per-step input copies, no host work but the
+    #    graph launch (the on-device replacement of mnist.train.next_batch, example.py:165)
+    def attach_dataset(self, data: torch.Tensor, labels: torch.Tensor) -> None:
+        if self.mode != "sync" or len(self.local_ranks) != 1:
+            raise NotImplementedError("resident datasets are implemented for the sync trainer, one rank per process")
+        n = (data.shape[0] // self.batch_size) * self.batch_size
+        if n == 0 or labels.dtype != torch.int32 or labels.shape[0] < n:
+            raise ValueError("attach_dataset: need >= batch_size rows and int32 labels")
+        self._ds = (data, labels, n)
+        self._cursor = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._step_res = _GraphedStep(self._body_resident, self.device, self._step.use_graph)
+
+    def _body_resident(self):
+        data, labels, n = self._ds
+        r = self.local_ranks[0]
+        loss, correct = self.model.forward_backward(self.store, data, labels, rank=r, row_offset=self._cursor,
+                                                    batch=self.batch_size)
+        self._losses[r], self._corrects[r] = loss, correct
+        self.opt.apply(self.store, cursor=self._cursor, cursor_step=self.batch_size, cursor_wrap=n)
+
+    def step_resident(self) -> None:
+        """One step on the next batch of the attached dataset."""
+        self._step_res()
+        self.local_step += 1
+
     @property
     def last_loss(self) -> torch.Tensor:
         return self._losses[self.local_ranks[0]]

@@ -163,9 +163,19 @@ def bench_mnist(ctx, args, sampler, mode):
         tr.step(xs[2 + i], ys[2 + i])
     loss0 = tr.read_loss()
 
+    resident = mode == "sync" and not args.no_resident
+    if resident:
+        # the epoch stays on the device; each captured step reads its batch through a device cursor
+        tr.attach_dataset(data, labels)
+        for _ in range(4):
+            tr.step_resident()
+
     def dev_step(i):
-        j = i % n_batches
-        tr.step(xs[j], ys[j])
+        if resident:
+            tr.step_resident()
+        else:
+            j = i % n_batches
+            tr.step(xs[j], ys[j])
 
     for i in range(max(args.warmup, 3)):
         dev_step(i)
@@ -196,7 +206,8 @@ def bench_mnist(ctx, args, sampler, mode):
                    "per_gpu_batch": B, "seq_len": None, "mode": mode,
                    "parallelism": f"dp{ctx.world}+ps_shard{ctx.world}", "lr": 0.0005,
                    "inputs": "device-resident synthetic epoch 55000x784 fp32 (172 MB > 126 MB L2), "
-                             "streamed sequentially; no explicit L2 flush",
+                             "streamed sequentially" + (" through a device-side cursor (no per-step copy)" if resident
+                                                        else " (per-step device copy)") + "; no explicit L2 flush",
                    "cuda_graph": not args.no_graph},
     }
     tr.store  # keep alive until here
@@ -325,6 +336,8 @@ def main():
     ap.add_argument("--config", default="all",
                     choices=["all", "mnist_mlp_sync", "mnist_mlp_async", "wide_mlp", "sparse_lr"])
     ap.add_argument("--no-graph", dest="no_graph", action="store_true")
+    ap.add_argument("--no-resident", dest="no_resident", action="store_true",
+                    help="copy each batch into a static buffer instead of walking the device-resident epoch")
     ap.add_argument("--wide-batch", dest="wide_batch", type=int, default=4096)
     ap.add_argument("--wide-layers", dest="wide_layers", type=int, default=8)
     ap.add_argument("--wide-hidden", dest="wide_hidden", type=int, default=8192)

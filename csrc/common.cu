@@ -29,6 +29,15 @@ int sm_count() {
   return cached[dev];
 }
 
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("B200PS_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 tensormap_encode_fn get_tensormap_encode() {
   static tensormap_encode_fn fn = nullptr;
   static std::once_flag once;

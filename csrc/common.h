@@ -6,6 +6,8 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <utility>
 
 #include "../include/b200ps.h"
 
@@ -49,5 +51,27 @@ typedef CUresult (*tensormap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuin
 tensormap_encode_fn get_tensormap_encode();
 
 inline cudaStream_t as_stream(b200ps_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// Is programmatic dependent launch enabled?  (B200PS_PDL=0 in the environment turns it off.)
+bool pdl_enabled();
+
+// Launch `kernel` with the programmatic-stream-serialization attribute (when enabled), so its
+// prologue can overlap the tail of the previous kernel in the stream.  The kernel must execute
+// griddepcontrol.wait (pdl_wait()) before touching anything its predecessor produced.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
 
 }  // namespace b200ps

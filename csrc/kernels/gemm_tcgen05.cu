@@ -38,6 +38,7 @@ struct GemmParams {
   long long ldaux;
   float* master;
   void* lowp;
+  const int* a_row_offset;   // device scalar added to A's stored-row coordinate (resident datasets)
 };
 
 __device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
@@ -90,6 +91,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_smem;
 
+  // Everything above overlapped the previous kernel (programmatic dependent launch); from here
+  // on we read what it produced.  Let our own successor start its prologue right away.
+  pdl_wait();
+  pdl_trigger();
+  const int a_row0 = p.a_row_offset ? __ldg(p.a_row_offset) : 0;
+
   const int tiles_mn = p.num_m_blocks * p.num_n_blocks;
   const int total_tiles = tiles_mn * p.split_k;
 
@@ -111,12 +118,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
           uint8_t* sB = sA + kABytes;
           mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
           if (!p.a_mn) {
-            tma_load_2d(&tmA, &full_bar[stage], sA, kb * BLOCK_K, m_blk * kBlockM);
+            tma_load_2d(&tmA, &full_bar[stage], sA, kb * BLOCK_K, a_row0 + m_blk * kBlockM);
           } else {
 #pragma unroll
             for (int j = 0; j < kBlockM / ATOM_MN; ++j)
               tma_load_2d(&tmA, &full_bar[stage], sA + j * (BLOCK_K * kRowBytes),
-                          m_blk * kBlockM + j * ATOM_MN, kb * BLOCK_K);
+                          m_blk * kBlockM + j * ATOM_MN, a_row0 + kb * BLOCK_K);
           }
           if (!p.b_mn) {
             tma_load_2d(&tmB, &full_bar[stage], sB, kb * BLOCK_K, n_blk * BLOCK_N);
@@ -377,8 +384,11 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
 
   CUtensorMap tmA, tmB;
   int rc;
-  if (!a.a_mn_major) rc = encode_map(&tmA, a.A, kTf32, a.K, a.M, a.lda, BLOCK_K, kBlockM);
-  else               rc = encode_map(&tmA, a.A, kTf32, a.M, a.K, a.lda, ATOM_MN, BLOCK_K, kTf32);
+  // a_rows_total widens the stored-row extent of A beyond this call's M (or K): the GEMM then
+  // reads rows [*a_row_offset, ...) of a larger resident array; rows past the array are zero-filled
+  const uint64_t a_rows = a.a_rows_total > 0 ? (uint64_t)a.a_rows_total : (uint64_t)(a.a_mn_major ? a.K : a.M);
+  if (!a.a_mn_major) rc = encode_map(&tmA, a.A, kTf32, a.K, a_rows, a.lda, BLOCK_K, kBlockM);
+  else               rc = encode_map(&tmA, a.A, kTf32, a.M, a_rows, a.lda, ATOM_MN, BLOCK_K, kTf32);
   if (rc) return rc;
   if (!a.b_mn_major) rc = encode_map(&tmB, a.B, kTf32, a.K, a.N, a.ldb, BLOCK_K, BLOCK_N);
   else               rc = encode_map(&tmB, a.B, kTf32, a.N, a.K, a.ldb, ATOM_MN, BLOCK_K, kTf32);
@@ -407,6 +417,7 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   p.ldaux = a.ldaux;
   p.master = a.sgd_master;
   p.lowp = a.sgd_lowp;
+  p.a_row_offset = a.a_row_offset;
   // 16-byte vector path: every row start and every 32-column chunk start must be 16 B aligned
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
   const int c_esz = (a.epilogue == B200PS_EPI_SGD) ? 2 : (p.c_is_f32 ? 4 : 2);
@@ -425,7 +436,7 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   const int total_tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
   int ctas = a.max_ctas > 0 ? a.max_ctas : sm_count();
   if (ctas > total_tiles) ctas = total_tiles;
-  kern<<<ctas, kGemmThreads, kSmem, stream>>>(tmA, tmB, p);
+  B200PS_CUDA_CHECK(launch_pdl(kern, dim3(ctas), dim3(kGemmThreads), kSmem, stream, tmA, tmB, p));
   B200PS_LAUNCH_CHECK();
   return 0;
 }

@@ -35,7 +35,9 @@ struct TailParams {
   int rows_per_cta;
   float grad_scale;    // 1/B_global for the mean loss
   float loss_scale;    // 1/B for a mean, 1 for a sum
-  int atomic_out;      // unused (kept for ABI stability of the struct)
+  int flags;           // B200PS_TAIL_*
+  const int* label_offset;   // device scalar added to the label row index, or null
+  float* z2_clear;     // == z2 when B200PS_TAIL_CLEAR_Z2
 };
 
 // ------------------------------------------------------------------------------------
@@ -77,7 +79,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
   const int row_begin = blockIdx.x * p.rows_per_cta;
   const int row_end = min(p.B, row_begin + p.rows_per_cta);
   const int HK = (H + 31) >> 5;   // hidden units per lane (<= 4)
-  const int P = H * C + C + H + 1;
+  const int P = H * C + C + H + 2;   // dW2 | db2 | db1 | loss | correct
 
   // gradient outputs owned by this thread (fixed ownership => fixed summation order)
   int eh[kT2MaxPer], ec[kT2MaxPer];
@@ -92,18 +94,30 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
   float acc_b2 = 0.f, acc_b1a = 0.f, acc_b1b = 0.f;   // thread c < C ; threads h = tid, tid + 256 < H
   float loss_w = 0.f;
   int corr_w = 0;
+  // W2/b1/b2 were last written by the previous step's push, which every kernel between it and
+  // us has already waited on; only z2 comes from our immediate predecessor.
+  pdl_wait();
+  pdl_trigger();
+  const int label0 = p.label_offset ? __ldg(p.label_offset) : 0;
   __syncthreads();
 
   for (int r0 = row_begin; r0 < row_end; r0 += kT2Rows) {
     const int r = r0 + warp;
     const bool row_ok = r < row_end;
     // (a) a = sigmoid(z2 + b1) for this lane's hidden units (label fetched in the same batch of loads)
-    const int label = row_ok ? __ldg(p.labels + r) : 0;
+    const int label = row_ok ? __ldg(p.labels + label0 + r) : 0;
     float zk[4], ak[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int h = lane + 32 * k;
-      zk[k] = (row_ok && k < HK && h < H) ? __ldg(p.z2 + (size_t)r * H + h) : 0.f;
+      zk[k] = (row_ok && k < HK && h < H) ? __ldcg(p.z2 + (size_t)r * H + h) : 0.f;
+    }
+    if (p.z2_clear) {   // leave z2 zeroed for the next step's split-K accumulation
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int h = lane + 32 * k;
+        if (row_ok && k < HK && h < H) p.z2_clear[(size_t)r * H + h] = 0.f;
+      }
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -242,14 +256,16 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
   if (lane == 0) { s_loss[warp] = loss_w; s_corr[warp] = corr_w; }
   __syncthreads();
   float loss_cta = 0.f;
-  if (tid == 0) {
-    int corr = 0;
-    for (int w8 = 0; w8 < kT2Rows; ++w8) { loss_cta += s_loss[w8]; corr += s_corr[w8]; }
-    if (p.correct && corr) atomicAdd(p.correct, corr);   // integer: order-independent
-  }
+  int corr_cta = 0;
+  if (tid == 0)
+    for (int w8 = 0; w8 < kT2Rows; ++w8) { loss_cta += s_loss[w8]; corr_cta += s_corr[w8]; }
+  const bool overwrite = (p.flags & B200PS_TAIL_OVERWRITE_STATS) != 0;
 
   if (gridDim.x == 1) {
-    if (tid == 0 && p.loss_sum) *p.loss_sum += loss_cta * p.loss_scale;
+    if (tid == 0) {
+      if (p.loss_sum) *p.loss_sum = (overwrite ? 0.f : *p.loss_sum) + loss_cta * p.loss_scale;
+      if (p.correct) *p.correct = (overwrite ? 0 : *p.correct) + corr_cta;
+    }
     if (p.train) {
 #pragma unroll
       for (int j = 0; j < kT2MaxPer; ++j)
@@ -271,7 +287,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
     if (tid < H) mine[H * C + C + tid] = acc_b1a;
     if (tid + kT2Threads < H) mine[H * C + C + tid + kT2Threads] = acc_b1b;
   }
-  if (tid == 0) mine[P - 1] = loss_cta;
+  if (tid == 0) { mine[P - 2] = loss_cta; mine[P - 1] = (float)corr_cta; }   // counts < 2^24: exact
   __syncthreads();
   if (tid == 0) {
     __threadfence();
@@ -280,7 +296,7 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  const int first = p.train ? 0 : P - 1;
+  const int first = p.train ? 0 : P - 2;
   // 4 outputs x 8 partials = 32 independent loads in flight per thread; sums stay in CTA order
   for (int o0 = first + tid; o0 < P; o0 += 4 * kT2Threads) {
     float t[4] = {0.f, 0.f, 0.f, 0.f};
@@ -304,8 +320,9 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
       if (o >= P) continue;
       if (o < H * C) p.dw2[o] = t[q];
       else if (o < H * C + C) p.db2[o - H * C] = t[q];
-      else if (o < P - 1) p.db1[o - H * C - C] = t[q];
-      else if (p.loss_sum) *p.loss_sum += t[q] * p.loss_scale;
+      else if (o < P - 2) p.db1[o - H * C - C] = t[q];
+      else if (o == P - 2) { if (p.loss_sum) *p.loss_sum = (overwrite ? 0.f : *p.loss_sum) + t[q] * p.loss_scale; }
+      else if (p.correct) *p.correct = (overwrite ? 0 : *p.correct) + (int)(t[q] + 0.5f);
     }
   }
   if (tid == 0) *counter = 0;   // self-resetting for the next launch
@@ -524,7 +541,8 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
                                const int32_t* labels, float* a2_out, float* dz2, float* dw2,
                                float* db2, float* db1, float* loss_sum, int32_t* correct,
                                float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
-                               float grad_scale, float loss_scale, b200ps_stream_t stream) {
+                               float grad_scale, float loss_scale, int32_t flags,
+                               const int32_t* label_offset, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail: bad shape");
   B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail: C=%d > %d (use gemm + softmax_ce)", C, kMaxClasses);
   B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail: H=%d too wide for the fused head (<= 128)", H);
@@ -534,23 +552,26 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
   p.dw2 = dw2; p.db2 = db2; p.db1 = db1; p.loss_sum = loss_sum; p.correct = correct;
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
+  p.flags = flags; p.label_offset = label_offset;
+  p.z2_clear = (flags & B200PS_TAIL_CLEAR_Z2) ? const_cast<float*>(z2) : nullptr;
   // rows are dealt to CTAs in tiles of 8; at most one CTA per SM so the merge stays short
   int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
   p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;
   ctas = (B + p.rows_per_cta - 1) / p.rows_per_cta;
-  p.atomic_out = 0;
   cudaStream_t s = as_stream(stream);
   const int CP = C <= 16 ? 16 : 32;
-  const int P = H * C + C + H + 1;
+  const int P = H * C + C + H + 2;
   Workspace ws;
   int rc = get_workspace(sizeof(float) * (size_t)ctas * P, &ws);
   if (rc) return rc;
   const size_t smem = sizeof(float) * ((size_t)H * (CP + 4) + CP + ((H + 3) & ~3) + 2 * (size_t)kT2Rows * H +
                                        (size_t)kT2Rows * CP);
   if (CP == 16)
-    mlp_tail2_kernel<16><<<ctas, kT2Threads, smem, s>>>(p, reinterpret_cast<float*>(ws.data), ws.counters);
+    B200PS_CUDA_CHECK(launch_pdl(mlp_tail2_kernel<16>, dim3(ctas), dim3(kT2Threads), smem, s, p,
+                                 reinterpret_cast<float*>(ws.data), ws.counters));
   else
-    mlp_tail2_kernel<32><<<ctas, kT2Threads, smem, s>>>(p, reinterpret_cast<float*>(ws.data), ws.counters);
+    B200PS_CUDA_CHECK(launch_pdl(mlp_tail2_kernel<32>, dim3(ctas), dim3(kT2Threads), smem, s, p,
+                                 reinterpret_cast<float*>(ws.data), ws.counters));
   B200PS_LAUNCH_CHECK();
   return 0;
 }
@@ -568,7 +589,7 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
 //
 //   * capacity: kTailStaticFloats floats (1 MiB) of partials + one arrival counter, resident
 //     on every GPU that loads libb200ps.so until the process exits;
-//   * a launch needs ctas * (H*C + C + H + 1) floats (ctas = row tiles, at most one per SM);
+//   * a launch needs ctas * (H*C + C + H + 2) floats (ctas = row tiles, at most one per SM);
 //     larger problems are refused with B200PS_ERR_INVALID — use b200ps_mlp_tail for those;
 //   * the array is shared by every call and keeps the previous call's contents: the counter
 //     is cleared on the stream before each launch, the partials are always fully rewritten
@@ -589,7 +610,8 @@ extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const fl
                                       const int32_t* labels, float* a2_out, float* dz2, float* dw2,
                                       float* db2, float* db1, float* loss_sum, int32_t* correct,
                                       float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
-                                      float grad_scale, float loss_scale, b200ps_stream_t stream) {
+                                      float grad_scale, float loss_scale, int32_t flags,
+                                      const int32_t* label_offset, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail_static: bad shape");
   B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail_static: C=%d > %d", C, kMaxClasses);
   B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail_static: H=%d too wide for the fused head (<= 128)", H);
@@ -599,12 +621,13 @@ extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const fl
   p.dw2 = dw2; p.db2 = db2; p.db1 = db1; p.loss_sum = loss_sum; p.correct = correct;
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
+  p.flags = flags; p.label_offset = label_offset;
+  p.z2_clear = (flags & B200PS_TAIL_CLEAR_Z2) ? const_cast<float*>(z2) : nullptr;
   int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
   p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;
   ctas = (B + p.rows_per_cta - 1) / p.rows_per_cta;
-  p.atomic_out = 0;
   const int CP = C <= 16 ? 16 : 32;
-  const size_t P = (size_t)H * C + C + H + 1;
+  const size_t P = (size_t)H * C + C + H + 2;
   const size_t need = (size_t)ctas * P;
   B200PS_REQUIRE(need <= kTailStaticFloats,
                  "mlp_tail_static: B=%d H=%d C=%d needs %zu bytes of static scratch, the built-in maximum is "

@@ -48,6 +48,8 @@ struct CommArgs {
   int world, rank_base;
   int replicas_to_aggregate;
   float lr;
+  int* cursor;                // resident-dataset batch pointer advanced at the end of the step
+  int cursor_step, cursor_wrap;
 };
 
 template <typename T> struct Vec4;
@@ -91,6 +93,8 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   const int world = a.world;
   const int tid = threadIdx.x;
   uint32_t* pad = a.pads[rank];
+  pdl_wait();      // the gradients come from the kernels just before us
+  pdl_trigger();
   const uint32_t epoch = pad[kSlotEpoch] + 1;
 
   // -- phase 0: my gradients (written by earlier kernels of this stream) are ready
@@ -164,6 +168,7 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
       pad[kSlotCtaDone] = 0;
       pad[kSlotEpoch] = epoch;
       if (a.global_steps) *a.global_steps[rank] += 1ull;  // one step per aggregated update
+      if (a.cursor && blockIdx.y == 0) *a.cursor = (*a.cursor + a.cursor_step) % a.cursor_wrap;
     }
   }
 }
@@ -234,7 +239,8 @@ extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters
                                     uint64_t* const* global_steps, int32_t world, int32_t rank_base,
                                     int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
                                     int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
-                                    int32_t max_ctas, b200ps_stream_t stream) {
+                                    int32_t max_ctas, int32_t* cursor, int32_t cursor_step,
+                                    int32_t cursor_wrap, b200ps_stream_t stream) {
   B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "push_sync: world=%d out of range", world);
   B200PS_REQUIRE(local_ranks >= 1 && rank_base >= 0 && rank_base + local_ranks <= world, "push_sync: bad ranks");
   B200PS_REQUIRE(grad_dtype == out_dtype, "push_sync: gradient and working-copy dtypes must match");
@@ -244,11 +250,14 @@ extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters
   a.bounds = reinterpret_cast<const long long*>(bounds);
   a.global_steps = reinterpret_cast<unsigned long long* const*>(global_steps);
   a.world = world; a.rank_base = rank_base; a.replicas_to_aggregate = replicas_to_aggregate; a.lr = lr;
+  a.cursor = cursor; a.cursor_step = cursor_step; a.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
   const int want = max_ctas > 0 ? max_ctas : sm_count();
   dim3 grid(comm_grid(max_shard_elems, local_ranks, want), local_ranks);
   cudaStream_t s = as_stream(stream);
-  if (grad_dtype == B200PS_DT_F32) push_sync_sgd_kernel<float, float><<<grid, 256, 0, s>>>(a);
-  else push_sync_sgd_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>(a);
+  if (grad_dtype == B200PS_DT_F32)
+    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<float, float>, grid, dim3(256), 0, s, a));
+  else
+    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<__nv_bfloat16, __nv_bfloat16>, grid, dim3(256), 0, s, a));
   B200PS_LAUNCH_CHECK();
   return 0;
 }

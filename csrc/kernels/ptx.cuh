@@ -31,6 +31,14 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// Programmatic dependent launch: a kernel launched with the "programmatic stream serialization"
+// attribute may start while its predecessor is still running; griddepcontrol.wait then blocks
+// until the predecessor grid has completed and its memory is visible.  Everything before the
+// wait (barrier init, TMEM allocation, descriptor prefetch, parameter staging) overlaps the
+// predecessor's execution.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Every in-kernel wait in this library is bounded: a protocol bug must become a trap
 // (which the host sees as an error) instead of a hung GPU.
 #ifndef B200PS_WAIT_TIMEOUT_NS

@@ -74,6 +74,11 @@ typedef struct b200ps_gemm_args {
   void* sgd_lowp;      /* [M,N] bf16 shadow, row stride ldc, or NULL (EPI_SGD) */
   float sgd_lr;
   int32_t max_ctas;    /* 0 = one CTA per SM */
+  /* Resident-dataset addressing: A is rows [*a_row_offset, +M) (K-major) or [*a_row_offset, +K)
+   * (MN-major) of a stored array with a_rows_total rows; the offset is read ON THE DEVICE at run
+   * time, so one captured launch can walk a dataset.  NULL / 0 = plain A. */
+  const int32_t* a_row_offset;
+  int64_t a_rows_total;
 } b200ps_gemm_args;
 
 int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);
@@ -83,13 +88,19 @@ int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);
  * head GEMM, stable log-softmax cross-entropy, accuracy count and, when train != 0,
  * dZ2 (for the first-layer wgrad GEMM), dW2, db2, db1.  (example.py:96-103,127-128)
  *   z2 [B,H] is the first-layer pre-activation WITHOUT bias.  loss_sum and correct are
- *   accumulated into (+=).  grad_scale multiplies dZ3 (1/global_batch for a mean loss).
+ *   accumulated into (+=) unless B200PS_TAIL_OVERWRITE_STATS.  grad_scale multiplies dZ3
+ *   (1/global_batch for a mean loss).  labels are read at labels[*label_offset + row] when
+ *   label_offset != NULL (device scalar, resident datasets).
  * ---------------------------------------------------------------------------------- */
+enum {
+  B200PS_TAIL_OVERWRITE_STATS = 1, /* *loss_sum = loss, *correct = count (no += , no zeroing pass) */
+  B200PS_TAIL_CLEAR_Z2 = 2         /* zero z2 after reading it (ready for the next split-K GEMM)  */
+};
 int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const float* b2,
                     const int32_t* labels, float* a2_out, float* dz2, float* dw2, float* db2,
                     float* db1, float* loss_sum, int32_t* correct, float* probs_out, int32_t B,
                     int32_t H, int32_t C, int32_t train, float grad_scale, float loss_scale,
-                    b200ps_stream_t stream);
+                    int32_t flags, const int32_t* label_offset, b200ps_stream_t stream);
 
 /* The same head computation, for callers that may not allocate (no counterpart in the
  * reference, which has no device code at all).  b200ps_mlp_tail draws its cross-CTA scratch
@@ -98,7 +109,7 @@ int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const flo
  * device-wide synchronisation, can call this variant instead: the scratch is a fixed 1 MiB
  * array inside the library's device image (held by every GPU that loads the library).
  * Same arguments and results as b200ps_mlp_tail.  Limits and rules:
- *   - ctas * (H*C + C + H + 1) * 4 bytes must fit in 1 MiB (ctas = ceil(B/8) capped at the SM
+ *   - ctas * (H*C + C + H + 2) * 4 bytes must fit in 1 MiB (ctas = ceil(B/8) capped at the SM
  *     count); otherwise B200PS_ERR_INVALID is returned and nothing is launched;
  *   - the array is shared by all calls: launches that could overlap on the GPU must be
  *     serialised by the caller;
@@ -109,7 +120,8 @@ int b200ps_mlp_tail_static(const float* z2, const float* b1, const float* w2, co
                            const int32_t* labels, float* a2_out, float* dz2, float* dw2,
                            float* db2, float* db1, float* loss_sum, int32_t* correct,
                            float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
-                           float grad_scale, float loss_scale, b200ps_stream_t stream);
+                           float grad_scale, float loss_scale, int32_t flags,
+                           const int32_t* label_offset, b200ps_stream_t stream);
 
 /* Wide-head softmax cross-entropy: logits [B,C] (ld = row stride) -> dlogits (same dtype,
  * may alias logits, may be NULL), loss_sum += , correct += .  C <= 16384. */
@@ -190,7 +202,10 @@ int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* con
                          uint64_t* const* global_steps, int32_t world, int32_t rank_base,
                          int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
                          int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
-                         int32_t max_ctas, b200ps_stream_t stream);
+                         int32_t max_ctas, int32_t* cursor, int32_t cursor_step, int32_t cursor_wrap,
+                         b200ps_stream_t stream);
+/* cursor (device int32, may be NULL): after the update has landed, *cursor = (*cursor + cursor_step)
+ * % cursor_wrap — the batch pointer of a resident dataset, advanced inside the captured step. */
 /* async (Hogwild): red.add of -lr*g into every owner's master; no barrier (example.py:118). */
 int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
                       uint64_t* const* global_steps, int32_t world, int32_t rank_base,

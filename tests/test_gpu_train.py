@@ -52,6 +52,25 @@ def test_mlp_trains_and_graph_matches_eager(native_lib, use_graph):
     assert tr.global_step == 150
 
 
+def test_resident_dataset_cursor_matches_copy_path(native_lib):
+    """Walking a device-resident epoch through the in-graph cursor == feeding the same batches by copy."""
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    xs, ys = _mnist_batches(7)
+    a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    a.attach_dataset(xs.reshape(-1, 784), ys.reshape(-1))
+    for i in range(17):                       # wraps around the 7-batch epoch twice
+        a.step_resident()
+        b.step(xs[i % 7], ys[i % 7])
+    torch.cuda.synchronize()
+    assert a._cursor.item() == (17 * 100) % 700
+    sa, sb = a.store.state_dict(), b.store.state_dict()
+    for name in a.model.names():
+        assert torch.equal(sa[name], sb[name]), name
+    assert a.read_loss() == b.read_loss() and a.global_step == b.global_step == 17
+
+
 def test_sync_virtual_ranks_equal_big_batch(native_lib):
     """4 sync replicas x batch 100 == 1 worker x batch 400 (mean of means), up to fp32 rounding."""
     from b200ps.parallel.context import init_from_env

@@ -37,7 +37,7 @@ def _call(fn, inp, out, B, H, Cn, train=1):
     return fn(inp["z2"].data_ptr(), inp["b1"].data_ptr(), inp["w2"].data_ptr(), inp["b2"].data_ptr(),
               inp["labels"].data_ptr(), out["a2"].data_ptr(), out["dz2"].data_ptr(), out["dw2"].data_ptr(),
               out["db2"].data_ptr(), out["db1"].data_ptr(), out["loss"].data_ptr(), out["correct"].data_ptr(),
-              out["probs"].data_ptr(), B, H, Cn, train, 1.0 / B, 1.0 / B, stream)
+              out["probs"].data_ptr(), B, H, Cn, train, 1.0 / B, 1.0 / B, 0, None, stream)
 
 
 def test_static_scratch_entry_point_matches_allocating_one(native_lib):
@@ -59,7 +59,7 @@ def test_static_scratch_entry_point_matches_allocating_one(native_lib):
 
 def test_static_scratch_entry_point_refuses_oversize(native_lib):
     lib = native_lib
-    B, H, Cn = 4096, 128, 32            # 148 CTAs x 4257 floats = 2.4 MiB > the 1 MiB array
+    B, H, Cn = 4096, 128, 32            # 148 CTAs x 4258 floats = 2.4 MiB > the 1 MiB array
     inp, out = _problem(B, H, Cn, 2), _outputs(B, H, Cn)
     before = out["dw2"].clone()
     rc = _call(lib.b200ps_mlp_tail_static, inp, out, B, H, Cn)
