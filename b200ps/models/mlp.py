@@ -78,7 +78,7 @@ class SigmoidMLP:
         k = (batch, key)
         if k not in self._bufs:
             self._bufs[k] = dict(
-                z2=torch.zeros(batch, self.hidden, device=device),
+                z2=torch.zeros(max(self.split_k, 1), batch, self.hidden, device=device),
                 dz2=torch.empty(batch, self.hidden, device=device),
                 loss=torch.zeros(1, device=device),
                 correct=torch.zeros(1, device=device, dtype=torch.int32))
@@ -98,16 +98,15 @@ class SigmoidMLP:
         z2, dz2, loss, correct = bufs["z2"], bufs["dz2"], bufs["loss"], bufs["correct"]
         w1 = store.var(self.W1, rank)
         off = dict(a_row_offset=row_offset, a_rows=B) if row_offset is not None else {}
-        if self.split_k > 1:
-            # z2 starts at zero (allocation) and the head kernel re-zeroes it after reading it
-            ops.gemm(x, w1, z2, b_mn_major=True, epilogue=ops.EPI_ATOMIC_ADD, split_k=self.split_k, **off)
-        else:
-            ops.gemm(x, w1, z2, b_mn_major=True, **off)
-        ops.mlp_tail(z2, store.var(self.B1, rank), store.var(self.W2, rank), store.var(self.B2, rank),
+        # split-K over CTAs, each writing its own slab of z2; the head kernel sums the slabs in a
+        # fixed order (an atomic split-K would make the step irreproducible bit for bit)
+        ksplits = min(max(self.split_k, 1), -(-self.in_dim // 32))
+        ops.gemm(x, w1, z2[0], b_mn_major=True, split_k=ksplits, c_split_stride=z2.stride(0), **off)
+        ops.mlp_tail(z2[0], store.var(self.B1, rank), store.var(self.W2, rank), store.var(self.B2, rank),
                      labels, loss_sum=loss, correct=correct, dz2=dz2, dw2=store.grad(self.W2, rank),
                      db2=store.grad(self.B2, rank), db1=store.grad(self.B1, rank), train=True,
-                     grad_scale=1.0 / B, loss_scale=1.0 / B, overwrite_stats=True,
-                     clear_z2=self.split_k > 1, label_offset=row_offset)
+                     grad_scale=1.0 / B, loss_scale=1.0 / B, overwrite_stats=True, label_offset=row_offset,
+                     z2_splits=ksplits, z2_split_stride=z2.stride(0))
         ops.gemm(x, dz2, store.grad(self.W1, rank), a_mn_major=True, b_mn_major=True, **off)
         return loss, correct
 

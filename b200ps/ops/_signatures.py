@@ -4,8 +4,8 @@ import ctypes as C
 vp, i32, i64, u32, u64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64, C.c_float
 
 SIGNATURES = {
-    "b200ps_mlp_tail": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, i32, vp, vp],
-    "b200ps_mlp_tail_static": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, i32, vp, vp],
+    "b200ps_mlp_tail": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, i32, vp, i32, i64, vp],
+    "b200ps_mlp_tail_static": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, i32, vp, i32, i64, vp],
     "b200ps_softmax_ce": [vp, vp, vp, vp, vp, i32, i32, i64, i32, f32, f32, vp],
     "b200ps_colsum": [vp, vp, i32, i32, i64, i32, f32, vp],
     "b200ps_sgd_apply": [vp, vp, i32, vp, u64, f32, f32, vp],

@@ -50,7 +50,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          sgd_master: Optional[torch.Tensor] = None, sgd_lowp: Optional[torch.Tensor] = None,
          sgd_lr: float = 0.0, out_dtype: Optional[torch.dtype] = None, max_ctas: int = 0,
          a_row_offset: Optional[torch.Tensor] = None, a_rows: Optional[int] = None,
-         stream=None) -> Optional[torch.Tensor]:
+         c_split_stride: int = 0, stream=None) -> Optional[torch.Tensor]:
     """tcgen05/TMA GEMM  ``out[M,N] = epilogue(alpha * op(a) @ op(b))``.
 
     ``a`` is ``[M,K]`` (K-major) or, with ``a_mn_major``, stored ``[K,M]``;
@@ -114,13 +114,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     args.sgd_master, args.sgd_lowp, args.sgd_lr = ptr(sgd_master), ptr(sgd_lowp), sgd_lr
     args.max_ctas = max_ctas
     args.a_row_offset, args.a_rows_total = ptr(a_row_offset), a_rows_total
+    args.c_split_stride = c_split_stride
     check(native.load().b200ps_gemm(C.byref(args), stream_ptr(stream)), "gemm")
     return out
 
 
 def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=None, db2=None,
              db1=None, a2_out=None, probs_out=None, train=True, grad_scale=None, loss_scale=None,
-             overwrite_stats=False, clear_z2=False, label_offset=None, stream=None):
+             overwrite_stats=False, clear_z2=False, label_offset=None, z2_splits=1, z2_split_stride=0,
+             stream=None):
     """Fused narrow MLP head (K6): see include/b200ps.h b200ps_mlp_tail."""
     _cuda(z2, b1, w2, b2, labels)
     B, H = z2.shape
@@ -135,7 +137,8 @@ def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=No
                                         ptr(dz2), ptr(dw2), ptr(db2), ptr(db1), ptr(loss_sum),
                                         ptr(correct), ptr(probs_out), B, H, Cn, int(train), gs, ls,
                                         (native.TAIL_OVERWRITE_STATS if overwrite_stats else 0) |
-                                        (native.TAIL_CLEAR_Z2 if clear_z2 else 0), ptr(label_offset),
+                                        (native.TAIL_CLEAR_Z2 if clear_z2 else 0), ptr(label_offset), z2_splits,
+                                        z2_split_stride,
                                         stream_ptr(stream)), "mlp_tail")
 
 

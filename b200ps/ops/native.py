@@ -37,7 +37,7 @@ class GemmArgs(C.Structure):
         ("sgd_master", C.c_void_p), ("sgd_lowp", C.c_void_p),
         ("sgd_lr", C.c_float),
         ("max_ctas", C.c_int32),
-        ("a_row_offset", C.c_void_p), ("a_rows_total", C.c_int64),
+        ("a_row_offset", C.c_void_p), ("a_rows_total", C.c_int64), ("c_split_stride", C.c_int64),
     ]
 
 

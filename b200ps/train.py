@@ -117,7 +117,7 @@ class MLPTrainer(_TrainerBase):
     # -- resident dataset: the whole (per-worker) epoch lives on the device and the captured step
     #    walks it through a device-side cursor — no per-step input copies, no host work but the
     #    graph launch (the on-device replacement of mnist.train.next_batch, example.py:165)
-    def attach_dataset(self, data: torch.Tensor, labels: torch.Tensor) -> None:
+    def attach_dataset(self, data: torch.Tensor, labels: torch.Tensor, steps_per_graph: int = 8) -> None:
         if self.mode != "sync" or len(self.local_ranks) != 1:
             raise NotImplementedError("resident datasets are implemented for the sync trainer, one rank per process")
         n = (data.shape[0] // self.batch_size) * self.batch_size
@@ -126,6 +126,10 @@ class MLPTrainer(_TrainerBase):
         self._ds = (data, labels, n)
         self._cursor = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._step_res = _GraphedStep(self._body_resident, self.device, self._step.use_graph)
+        # the cursor lives on the device, so consecutive steps chain inside ONE graph: a replay of
+        # `steps_per_graph` steps costs one host launch
+        self._spg = max(1, steps_per_graph)
+        self._step_res_multi = _GraphedStep(self._body_resident_multi, self.device, self._step.use_graph)
 
     def _body_resident(self):
         data, labels, n = self._ds
@@ -135,10 +139,24 @@ class MLPTrainer(_TrainerBase):
         self._losses[r], self._corrects[r] = loss, correct
         self.opt.apply(self.store, cursor=self._cursor, cursor_step=self.batch_size, cursor_wrap=n)
 
+    def _body_resident_multi(self):
+        for _ in range(self._spg):
+            self._body_resident()
+
     def step_resident(self) -> None:
         """One step on the next batch of the attached dataset."""
         self._step_res()
         self.local_step += 1
+
+    def run_resident(self, steps: int) -> None:
+        """``steps`` consecutive steps over the attached dataset (multi-step graph replays + remainder)."""
+        n = steps
+        while n >= self._spg and self._spg > 1:
+            self._step_res_multi()
+            n -= self._spg
+        for _ in range(n):
+            self._step_res()
+        self.local_step += steps
 
     @property
     def last_loss(self) -> torch.Tensor:

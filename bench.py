@@ -166,9 +166,10 @@ def bench_mnist(ctx, args, sampler, mode):
     resident = mode == "sync" and not args.no_resident
     if resident:
         # the epoch stays on the device; each captured step reads its batch through a device cursor
-        tr.attach_dataset(data, labels)
+        tr.attach_dataset(data, labels, steps_per_graph=args.steps_per_graph)
         for _ in range(4):
             tr.step_resident()
+        tr.run_resident(4 * args.steps_per_graph)       # warm-up + capture of the multi-step graph
 
     def dev_step(i):
         if resident:
@@ -179,7 +180,10 @@ def bench_mnist(ctx, args, sampler, mode):
 
     for i in range(max(args.warmup, 3)):
         dev_step(i)
-    ms = timed_region(ctx, torch, sampler, args.steps, dev_step)
+    if resident:
+        ms = timed_region(ctx, torch, sampler, 1, lambda i: tr.run_resident(args.steps))   # exactly K steps
+    else:
+        ms = timed_region(ctx, torch, sampler, args.steps, dev_step)
     loss1 = tr.read_loss()
 
     # ---- end to end: pinned host batch -> H2D -> step -> loss D2H, every step
@@ -208,7 +212,7 @@ def bench_mnist(ctx, args, sampler, mode):
                    "inputs": "device-resident synthetic epoch 55000x784 fp32 (172 MB > 126 MB L2), "
                              "streamed sequentially" + (" through a device-side cursor (no per-step copy)" if resident
                                                         else " (per-step device copy)") + "; no explicit L2 flush",
-                   "cuda_graph": not args.no_graph},
+                   "cuda_graph": not args.no_graph, "steps_per_graph_replay": args.steps_per_graph if resident else 1},
     }
     tr.store  # keep alive until here
     return out
@@ -336,6 +340,8 @@ def main():
     ap.add_argument("--config", default="all",
                     choices=["all", "mnist_mlp_sync", "mnist_mlp_async", "wide_mlp", "sparse_lr"])
     ap.add_argument("--no-graph", dest="no_graph", action="store_true")
+    ap.add_argument("--steps-per-graph", dest="steps_per_graph", type=int, default=8,
+                    help="training steps chained inside one CUDA-graph replay (device-side batch cursor)")
     ap.add_argument("--no-resident", dest="no_resident", action="store_true",
                     help="copy each batch into a static buffer instead of walking the device-resident epoch")
     ap.add_argument("--wide-batch", dest="wide_batch", type=int, default=4096)

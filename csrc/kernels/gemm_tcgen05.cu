@@ -39,6 +39,7 @@ struct GemmParams {
   float* master;
   void* lowp;
   const int* a_row_offset;   // device scalar added to A's stored-row coordinate (resident datasets)
+  long long c_split_stride;  // EPI_STORE with split_k > 1: split s writes its partial to C + s*stride
 };
 
 __device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
@@ -190,6 +191,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int tmn = t / p.split_k;
+      const int split = t % p.split_k;
       const int m_blk = tmn % p.num_m_blocks;
       const int n_blk = tmn / p.num_m_blocks;
       const int row = m_blk * kBlockM + quarter * 32 + lane;
@@ -255,7 +257,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             }
           }
           if (p.c_is_f32) {
-            float* cp = reinterpret_cast<float*>(p.C) + row * p.ldc + col0;
+            float* cp = reinterpret_cast<float*>(p.C) + split * p.c_split_stride + row * p.ldc + col0;
             if (p.vec_ok && ncols == 32) {
 #pragma unroll
               for (int q = 0; q < 8; ++q)
@@ -267,7 +269,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                 if (j < ncols) cp[j] = v[j];
             }
           } else {
-            __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + row * p.ldc + col0;
+            __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + split * p.c_split_stride + row * p.ldc + col0;
             if (p.vec_ok && ncols == 32) {
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
@@ -418,6 +420,7 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   p.master = a.sgd_master;
   p.lowp = a.sgd_lowp;
   p.a_row_offset = a.a_row_offset;
+  p.c_split_stride = a.c_split_stride;
   // 16-byte vector path: every row start and every 32-column chunk start must be 16 B aligned
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
   const int c_esz = (a.epilogue == B200PS_EPI_SGD) ? 2 : (p.c_is_f32 ? 4 : 2);
@@ -464,7 +467,12 @@ extern "C" int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream)
   switch (a.epilogue) {
     case B200PS_EPI_STORE:
       B200PS_REQUIRE(a.C != nullptr, "gemm: null C");
-      B200PS_REQUIRE(a.split_k <= 1, "gemm: split_k > 1 needs B200PS_EPI_ATOMIC_ADD");
+      B200PS_REQUIRE(a.split_k <= 1 || (a.c_split_stride >= (int64_t)a.M * a.ldc && !a.bias && !a.aux &&
+                                        a.act == B200PS_ACT_NONE),
+                     "gemm: split_k > 1 needs B200PS_EPI_ATOMIC_ADD, or a plain store into per-split slabs "
+                     "(c_split_stride >= M*ldc)");
+      B200PS_REQUIRE(a.split_k <= 1 || (a.c_split_stride * (a.c_dtype == B200PS_DT_F32 ? 4 : 2)) % 16 == 0,
+                     "gemm: c_split_stride must keep slabs 16-byte aligned");
       break;
     case B200PS_EPI_ATOMIC_ADD:
       B200PS_REQUIRE(a.C != nullptr && a.c_dtype == B200PS_DT_F32, "gemm: atomic epilogue needs fp32 C");

@@ -38,6 +38,8 @@ struct TailParams {
   int flags;           // B200PS_TAIL_*
   const int* label_offset;   // device scalar added to the label row index, or null
   float* z2_clear;     // == z2 when B200PS_TAIL_CLEAR_Z2
+  int z2_splits;       // >= 1: number of split-K slabs stacked in z2
+  long long z2_split_stride;
 };
 
 // ------------------------------------------------------------------------------------
@@ -111,6 +113,16 @@ __global__ void __launch_bounds__(kT2Threads) mlp_tail2_kernel(const TailParams 
     for (int k = 0; k < 4; ++k) {
       const int h = lane + 32 * k;
       zk[k] = (row_ok && k < HK && h < H) ? __ldcg(p.z2 + (size_t)r * H + h) : 0.f;
+    }
+    for (int sp = 1; sp < p.z2_splits; ++sp) {   // split-K slabs, summed in slab order
+      float part[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int h = lane + 32 * k;
+        part[k] = (row_ok && k < HK && h < H) ? __ldcg(p.z2 + sp * p.z2_split_stride + (size_t)r * H + h) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) zk[k] += part[k];
     }
     if (p.z2_clear) {   // leave z2 zeroed for the next step's split-K accumulation
 #pragma unroll
@@ -542,7 +554,8 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
                                float* db2, float* db1, float* loss_sum, int32_t* correct,
                                float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
                                float grad_scale, float loss_scale, int32_t flags,
-                               const int32_t* label_offset, b200ps_stream_t stream) {
+                               const int32_t* label_offset, int32_t z2_splits, int64_t z2_split_stride,
+                               b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail: bad shape");
   B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail: C=%d > %d (use gemm + softmax_ce)", C, kMaxClasses);
   B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail: H=%d too wide for the fused head (<= 128)", H);
@@ -553,6 +566,7 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
   p.flags = flags; p.label_offset = label_offset;
+  p.z2_splits = z2_splits < 1 ? 1 : z2_splits; p.z2_split_stride = z2_split_stride;
   p.z2_clear = (flags & B200PS_TAIL_CLEAR_Z2) ? const_cast<float*>(z2) : nullptr;
   // rows are dealt to CTAs in tiles of 8; at most one CTA per SM so the merge stays short
   int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
@@ -611,7 +625,8 @@ extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const fl
                                       float* db2, float* db1, float* loss_sum, int32_t* correct,
                                       float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
                                       float grad_scale, float loss_scale, int32_t flags,
-                                      const int32_t* label_offset, b200ps_stream_t stream) {
+                                      const int32_t* label_offset, int32_t z2_splits,
+                                      int64_t z2_split_stride, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && H > 0 && C > 0, "mlp_tail_static: bad shape");
   B200PS_REQUIRE(C <= kMaxClasses, "mlp_tail_static: C=%d > %d", C, kMaxClasses);
   B200PS_REQUIRE(H <= 128 && H * C <= 4096, "mlp_tail_static: H=%d too wide for the fused head (<= 128)", H);
@@ -622,6 +637,7 @@ extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const fl
   p.probs_out = probs_out; p.B = B; p.H = H; p.C = C; p.train = train;
   p.grad_scale = grad_scale; p.loss_scale = loss_scale;
   p.flags = flags; p.label_offset = label_offset;
+  p.z2_splits = z2_splits < 1 ? 1 : z2_splits; p.z2_split_stride = z2_split_stride;
   p.z2_clear = (flags & B200PS_TAIL_CLEAR_Z2) ? const_cast<float*>(z2) : nullptr;
   int ctas = std::min((B + kT2Rows - 1) / kT2Rows, sm_count());
   p.rows_per_cta = ((B + ctas - 1) / ctas + kT2Rows - 1) / kT2Rows * kT2Rows;

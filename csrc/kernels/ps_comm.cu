@@ -97,11 +97,16 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   pdl_trigger();
   const uint32_t epoch = pad[kSlotEpoch] + 1;
 
+  // A single shard has nobody to wait for: no flags, no system-scope fences, no arrival count.
+  const bool solo = (world == 1);
+
   // -- phase 0: my gradients (written by earlier kernels of this stream) are ready
   // (relaxed store: the gradients were written by EARLIER kernels, i.e. are already visible)
-  if (blockIdx.x == 0 && tid < world) st_relaxed_sys(a.pads[tid] + kFlagGradsReady + rank, epoch);
-  if (tid < world) wait_flag_geq(pad + kFlagGradsReady + tid, epoch);
-  __syncthreads();
+  if (!solo) {
+    if (blockIdx.x == 0 && tid < world) st_relaxed_sys(a.pads[tid] + kFlagGradsReady + rank, epoch);
+    if (tid < world) wait_flag_geq(pad + kFlagGradsReady + tid, epoch);
+    __syncthreads();
+  }
 
   // -- phase 1: reduce my slice over the replicas, apply, broadcast
   const long long lo = a.bounds[rank], hi = a.bounds[rank + 1];
@@ -146,6 +151,16 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
         if (reinterpret_cast<void*>(dst) != reinterpret_cast<void*>(master + i)) Vec4<O>::store(dst, x);
       }
     }
+  }
+
+  if (solo) {
+    // the step counters are only read by later kernels / the host: any one thread may bump them
+    if (blockIdx.x == 0 && tid == 0) {
+      pad[kSlotEpoch] = epoch;
+      if (a.global_steps) *a.global_steps[rank] += 1ull;
+      if (a.cursor) *a.cursor = (*a.cursor + a.cursor_step) % a.cursor_wrap;
+    }
+    return;
   }
 
   // -- phase 2: when every CTA of this rank is done, tell the peers and wait for theirs.

@@ -79,6 +79,10 @@ typedef struct b200ps_gemm_args {
    * time, so one captured launch can walk a dataset.  NULL / 0 = plain A. */
   const int32_t* a_row_offset;
   int64_t a_rows_total;
+  /* Deterministic split-K: with B200PS_EPI_STORE and split_k > 1, split s stores its partial
+   * product to C + s*c_split_stride (elements); the consumer sums the slabs in a fixed order
+   * (b200ps_mlp_tail does).  The actual number of splits is min(split_k, ceil(K / block_k)). */
+  int64_t c_split_stride;
 } b200ps_gemm_args;
 
 int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);
@@ -100,7 +104,10 @@ int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2, const flo
                     const int32_t* labels, float* a2_out, float* dz2, float* dw2, float* db2,
                     float* db1, float* loss_sum, int32_t* correct, float* probs_out, int32_t B,
                     int32_t H, int32_t C, int32_t train, float grad_scale, float loss_scale,
-                    int32_t flags, const int32_t* label_offset, b200ps_stream_t stream);
+                    int32_t flags, const int32_t* label_offset, int32_t z2_splits,
+                    int64_t z2_split_stride, b200ps_stream_t stream);
+/* z2_splits > 1: z2 is a stack of split-K partial slabs, z2_split_stride elements apart, summed
+ * here in slab order (bitwise reproducible, unlike an atomic split-K). */
 
 /* The same head computation, for callers that may not allocate (no counterpart in the
  * reference, which has no device code at all).  b200ps_mlp_tail draws its cross-CTA scratch
@@ -121,7 +128,8 @@ int b200ps_mlp_tail_static(const float* z2, const float* b1, const float* w2, co
                            float* db2, float* db1, float* loss_sum, int32_t* correct,
                            float* probs_out, int32_t B, int32_t H, int32_t C, int32_t train,
                            float grad_scale, float loss_scale, int32_t flags,
-                           const int32_t* label_offset, b200ps_stream_t stream);
+                           const int32_t* label_offset, int32_t z2_splits, int64_t z2_split_stride,
+                           b200ps_stream_t stream);
 
 /* Wide-head softmax cross-entropy: logits [B,C] (ld = row stride) -> dlogits (same dtype,
  * may alias logits, may be NULL), loss_sum += , correct += .  C <= 16384. */

@@ -60,8 +60,10 @@ def test_resident_dataset_cursor_matches_copy_path(native_lib):
     a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
     b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
     a.attach_dataset(xs.reshape(-1, 784), ys.reshape(-1))
-    for i in range(17):                       # wraps around the 7-batch epoch twice
+    a.run_resident(11)                        # one 8-step graph replay + 3 single steps
+    for i in range(11, 17):
         a.step_resident()
+    for i in range(17):                       # wraps around the 7-batch epoch twice
         b.step(xs[i % 7], ys[i % 7])
     torch.cuda.synchronize()
     assert a._cursor.item() == (17 * 100) % 700

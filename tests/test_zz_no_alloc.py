@@ -37,7 +37,7 @@ def _call(fn, inp, out, B, H, Cn, train=1):
     return fn(inp["z2"].data_ptr(), inp["b1"].data_ptr(), inp["w2"].data_ptr(), inp["b2"].data_ptr(),
               inp["labels"].data_ptr(), out["a2"].data_ptr(), out["dz2"].data_ptr(), out["dw2"].data_ptr(),
               out["db2"].data_ptr(), out["db1"].data_ptr(), out["loss"].data_ptr(), out["correct"].data_ptr(),
-              out["probs"].data_ptr(), B, H, Cn, train, 1.0 / B, 1.0 / B, 0, None, stream)
+              out["probs"].data_ptr(), B, H, Cn, train, 1.0 / B, 1.0 / B, 0, None, 1, 0, stream)
 
 
 def test_static_scratch_entry_point_matches_allocating_one(native_lib):
