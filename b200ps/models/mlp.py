@@ -125,7 +125,16 @@ class SigmoidMLP:
 
 class WideMLP:
     """``layers`` dense layers of ``hidden x hidden`` (bf16 working copy, fp32 master), sigmoid
-    between layers, softmax cross-entropy over the last layer's ``hidden`` outputs."""
+    between layers, softmax cross-entropy over the last layer's ``hidden`` outputs.
+
+    Every weight matrix is a parameter-server bucket of its own (group ``bf16:<l>``), row-sharded
+    over the ranks, which is what lets the multi-GPU step overlap its traffic with its math:
+
+    * forward: layer l's GEMM pulls the other ranks' row shards of W_l *inside the launch* (K2,
+      gather CTAs next to the GEMM CTAs) — no separate all-gather, no broadcast in the push;
+    * backward: as soon as dW_l is written, its reduce-scatter + SGD (K1, ``broadcast=False``) is
+      queued on a side stream and runs under the remaining backward GEMMs.
+    """
 
     def __init__(self, layers: int = 8, hidden: int = 8192, fuse_sgd_in_wgrad: bool = True):
         self.layers, self.hidden = layers, hidden
@@ -138,12 +147,15 @@ class WideMLP:
     def bname(self, l: int) -> str:
         return "biases/Variable" + (f"_{l}" if l else "")
 
+    def wgroup(self, l: int) -> str:
+        return f"bf16:{l}"
+
     def register(self, store) -> None:
         if hasattr(store, "note_untracked_variable"):
             store.note_untracked_variable("global_step")
         std = 4.0 / (self.hidden ** 0.5)   # keeps sigmoid layers away from saturation
         for l in range(self.layers):
-            store.register(self.wname(l), (self.hidden, self.hidden), group="bf16", init="normal", stddev=std)
+            store.register(self.wname(l), (self.hidden, self.hidden), group=self.wgroup(l), init="normal", stddev=std)
         for l in range(self.layers):
             store.register(self.bname(l), (self.hidden,), group="fp32", init="zeros")
 
@@ -163,10 +175,15 @@ class WideMLP:
         return self._acts[k]
 
     def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
-                         lr: float = 0.0, local_sgd: bool = False):
-        """One worker's forward/backward.  With ``local_sgd`` (world == 1) the weight update is
-        fused into the wgrad GEMM's epilogue (master -= lr*dW, bf16 copy refreshed) so the
-        1 GB gradient never touches HBM; otherwise gradients go to the symmetric push buffer."""
+                         lr: float = 0.0, local_sgd: bool = False, fused_pull: bool = False,
+                         on_wgrad_done=None):
+        """One worker's forward/backward.
+
+        ``local_sgd`` (world == 1): the weight update is fused into the wgrad GEMM's epilogue
+        (master -= lr*dW, bf16 copy refreshed) so the 1 GB gradient never touches HBM.
+        ``fused_pull`` (world > 1): forward GEMMs gather their weights from the shard owners in
+        the same launch.  ``on_wgrad_done(l)`` is called right after layer l's gradients (weights
+        and bias) have been queued, so the caller can start that layer's push."""
         B, L = x.shape[0], self.layers
         bufs = self._buffers(B, x.device, 0 if rank is None else rank)
         acts, dzs, loss, correct = bufs["acts"], bufs["dz"], bufs["loss"], bufs["correct"]
@@ -176,7 +193,8 @@ class WideMLP:
             out = acts[l + 1]
             ops.gemm(a, store.var(self.wname(l), rank), out, b_mn_major=True,
                      bias=store.var(self.bname(l), rank),
-                     act=ops.ACT_SIGMOID if l < L - 1 else ops.ACT_NONE)
+                     act=ops.ACT_SIGMOID if l < L - 1 else ops.ACT_NONE,
+                     gather=store.gather_info(self.wname(l), rank) if fused_pull else None)
             a = out
         dz = dzs[0]
         ops.softmax_ce(acts[L], labels, dlogits=dz, loss_sum=loss, correct=correct,
@@ -190,12 +208,15 @@ class WideMLP:
                 dz_prev = dzs[1] if dz is dzs[0] else dzs[0]
                 ops.gemm(dz, w, dz_prev, dsigmoid_of=acts[l])
             if local_sgd:
-                g = store.groups["bf16"]
-                lo = g.layout.offsets[self.wname(l)] - g.layout.bounds[store.pool.local_ranks[0]]
-                master = g.master.view(store.pool.local_ranks[0], torch.float32)[lo: lo + w.numel()].view_as(w)
+                g = store.groups[self.wgroup(l)]
+                r0 = store.pool.local_ranks[0]
+                lo = g.layout.offsets[self.wname(l)] - g.layout.bounds[r0]
+                master = g.master.view(r0, torch.float32)[lo: lo + w.numel()].view_as(w)
                 ops.gemm(a_in, dz, a_mn_major=True, b_mn_major=True, epilogue=ops.EPI_SGD,
                          sgd_master=master, sgd_lowp=w, sgd_lr=lr)
             else:
                 ops.gemm(a_in, dz, store.grad(self.wname(l), rank), a_mn_major=True, b_mn_major=True)
+            if on_wgrad_done is not None:
+                on_wgrad_done(l)
             dz = dz_prev
         return loss, correct

@@ -50,7 +50,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          sgd_master: Optional[torch.Tensor] = None, sgd_lowp: Optional[torch.Tensor] = None,
          sgd_lr: float = 0.0, out_dtype: Optional[torch.dtype] = None, max_ctas: int = 0,
          a_row_offset: Optional[torch.Tensor] = None, a_rows: Optional[int] = None,
-         c_split_stride: int = 0, stream=None) -> Optional[torch.Tensor]:
+         c_split_stride: int = 0, gather: Optional[dict] = None, stream=None) -> Optional[torch.Tensor]:
     """tcgen05/TMA GEMM  ``out[M,N] = epilogue(alpha * op(a) @ op(b))``.
 
     ``a`` is ``[M,K]`` (K-major) or, with ``a_mn_major``, stored ``[K,M]``;
@@ -115,6 +115,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     args.max_ctas = max_ctas
     args.a_row_offset, args.a_rows_total = ptr(a_row_offset), a_rows_total
     args.c_split_stride = c_split_stride
+    if gather is not None:
+        # K2: pull fused into the GEMM — gather = dict(src_table, flags, world, rank[, ctas])
+        args.gather_src, args.gather_flags = ptr(gather["src_table"]), ptr(gather["flags"])
+        args.gather_world, args.gather_rank = gather["world"], gather["rank"]
+        args.gather_ctas = gather.get("ctas", 0)
     check(native.load().b200ps_gemm(C.byref(args), stream_ptr(stream)), "gemm")
     return out
 
@@ -256,12 +261,12 @@ def signal_pad_words() -> int:
 
 def push_sync_sgd(pads, masters, outs, grads, bounds, global_steps, *, world, rank_base, local_ranks=1,
                   max_shard_elems, dtype, replicas_to_aggregate, lr, max_ctas=0, cursor=None, cursor_step=0,
-                  cursor_wrap=1, stream=None):
+                  cursor_wrap=1, broadcast=True, stream=None):
     d = DT_BF16 if dtype == torch.bfloat16 else DT_F32
     check(native.load().b200ps_push_sync_sgd(ptr(pads), ptr(masters), ptr(outs), ptr(grads), ptr(bounds),
                                              ptr(global_steps), world, rank_base, local_ranks,
                                              max_shard_elems, d, d, replicas_to_aggregate, lr, max_ctas,
-                                             ptr(cursor), cursor_step, cursor_wrap,
+                                             ptr(cursor), cursor_step, cursor_wrap, int(broadcast),
                                              stream_ptr(stream)), "push_sync_sgd")
 
 

@@ -88,7 +88,7 @@ class ParameterStore:
             raise RuntimeError("register() after build()")
         if name in self._order:
             raise ValueError(f"variable {name!r} registered twice")
-        if group not in _DT and group != "sparse":
+        if group.split(":")[0] not in _DT and group != "sparse":
             raise ValueError(f"unknown group {group!r}")
         if group == "sparse" and not (len(shape) == 2 and int(shape[1]) == 1):
             raise ValueError("sparse variables are [rows, 1] (lr2.py:384)")
@@ -115,7 +115,12 @@ class ParameterStore:
         self.gstep = pool.alloc("global_step", 8)
         self.t_pads = ops.device_ptr_table(self.pads.ptrs, dev)
         self.t_gsteps = ops.device_ptr_table(self.gstep.ptrs, dev)
-        for gname, dtype in _DT.items():
+        gnames = []
+        for s in self._specs:          # "bf16:<tag>" = a bucket of its own (per-layer push / fused pull)
+            if s.group != "sparse" and s.group not in gnames:
+                gnames.append(s.group)
+        for gname in gnames:
+            dtype = _DT[gname.split(":")[0]]
             specs = [s for s in self._specs if s.group == gname and s.trainable]
             if not specs:
                 continue
@@ -123,7 +128,7 @@ class ParameterStore:
             esz = 4 if dtype == torch.float32 else 2
             work = pool.alloc(f"{gname}.work", layout.total * esz)
             grads = pool.alloc(f"{gname}.grads", layout.total * esz)
-            if gname == "bf16":
+            if dtype == torch.bfloat16:
                 master = pool.alloc(f"{gname}.master", max(layout.max_shard, 8) * 4)
                 master_ptrs = [master.ptrs[r] - 4 * layout.bounds[r] for r in range(self.world)]
             else:
@@ -352,7 +357,8 @@ class ParameterStore:
                      include_self=include_self or g.master is not None)
 
     def push_sync(self, lr: float, replicas_to_aggregate: Optional[int] = None, groups=None,
-                  count_step: bool = True, cursor=None, cursor_step: int = 0, cursor_wrap: int = 1) -> None:
+                  count_step: bool = True, cursor=None, cursor_step: int = 0, cursor_wrap: int = 1,
+                  broadcast: bool = True) -> None:
         base, n = self._ranks()
         R = replicas_to_aggregate or self.world
         gl = list(self._iter_groups(groups))
@@ -364,7 +370,7 @@ class ParameterStore:
                               max_shard_elems=g.layout.max_shard, dtype=g.dtype,
                               replicas_to_aggregate=R, lr=lr,
                               cursor=cursor if i == len(gl) - 1 else None, cursor_step=cursor_step,
-                              cursor_wrap=cursor_wrap)
+                              cursor_wrap=cursor_wrap, broadcast=broadcast)
 
     def push_async(self, lr: float, rank: Optional[int] = None, groups=None, count_step: bool = True) -> None:
         """Hogwild push of ONE worker's gradients (fp32 groups only)."""
@@ -376,6 +382,21 @@ class ParameterStore:
             gs = self.t_gsteps if (count_step and i == len(gl) - 1) else None
             ops.push_async(g.t_masters, g.t_grads, g.bounds, gs, world=self.world, rank_base=r,
                            total_elems=g.layout.total, lr=lr)
+
+    def gather_info(self, name: str, rank: Optional[int] = None, ctas: int = 0) -> dict:
+        """Arguments of the fused pull (``ops.gemm(..., gather=...)``) for a [K,N] bf16 variable that
+        is the only member of its group: every rank's working copy + the local panel flags."""
+        g = self._group_of(name)
+        s = self._spec(name)
+        if g.dtype != torch.bfloat16 or len(g.specs) != 1 or len(s.shape) != 2:
+            raise ValueError("fused pull needs a 2-D bf16 variable in a group of its own")
+        rank = self.pool.local_ranks[0] if rank is None else rank
+        key = (name, rank)
+        if not hasattr(self, "_gather"):
+            self._gather = {}
+        if key not in self._gather:
+            self._gather[key] = torch.zeros(s.shape[0] // 64 + 1, dtype=torch.int32, device=self.device)
+        return dict(src_table=g.t_outs, flags=self._gather[key], world=self.world, rank=rank, ctas=ctas)
 
     def barrier(self) -> None:
         base, n = self._ranks()

@@ -188,7 +188,8 @@ class WideMLPTrainer(_TrainerBase):
     """BASELINE.json config 4: 8 x 8192 x 8192 bf16 sigmoid MLP, synchronous PS."""
 
     def __init__(self, ctx, batch_size: int = 4096, layers: int = 8, hidden: int = 8192, lr: float = 0.01,
-                 replicas_to_aggregate: Optional[int] = None, seed: int = 1, use_graph: bool = True):
+                 replicas_to_aggregate: Optional[int] = None, seed: int = 1, use_graph: bool = True,
+                 fused_pull: bool = True, overlap: bool = True):
         super().__init__(ctx, "sync", lr, replicas_to_aggregate, "flat_shard", seed)
         self.model = WideMLP(layers, hidden)
         self.batch_size = batch_size
@@ -200,20 +201,49 @@ class WideMLPTrainer(_TrainerBase):
         self.labels = {r: torch.zeros(batch_size, device=dev, dtype=torch.int32) for r in self.local_ranks}
         self._losses, self._corrects = {}, {}
         self.local_sgd = ctx.world == 1
+        # K2 needs the row shards to be whole 64-row panels
+        self.fused_pull = fused_pull and ctx.world > 1 and hidden % (64 * ctx.world) == 0
+        self.overlap = overlap
+        self._side = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
         self._step = _GraphedStep(self._body, dev, use_graph)
         if ctx.group is not None:
             ctx.control_barrier()
 
     def _body(self):
-        st = self.store
-        for r in self.local_ranks:
-            loss, correct = self.model.forward_backward(st, self.x[r], self.labels[r], rank=r, lr=self.lr,
-                                                        local_sgd=self.local_sgd)
-            self._losses[r], self._corrects[r] = loss, correct
+        st, m = self.store, self.model
         if self.local_sgd:
+            for r in self.local_ranks:
+                loss, correct = m.forward_backward(st, self.x[r], self.labels[r], rank=r, lr=self.lr, local_sgd=True)
+                self._losses[r], self._corrects[r] = loss, correct
             st.push_sync(self.lr, groups=("fp32",))            # biases; weights were fused into wgrad
-        else:
-            st.push_sync(self.lr, self.opt.replicas_to_aggregate)
+            return
+        R = self.opt.replicas_to_aggregate
+        if len(self.local_ranks) > 1 or not self.overlap:
+            # virtual ranks (tests) / overlap off: same kernels, pushes after the whole backward
+            for r in self.local_ranks:
+                loss, correct = m.forward_backward(st, self.x[r], self.labels[r], rank=r, fused_pull=self.fused_pull)
+                self._losses[r], self._corrects[r] = loss, correct
+            for l in range(m.layers - 1, -1, -1):
+                st.push_sync(self.lr, R, groups=(m.wgroup(l),), count_step=False, broadcast=not self.fused_pull)
+            st.push_sync(self.lr, R, groups=("fp32",))
+            return
+        # one rank per process: layer l's push runs on the side stream under the rest of the backward
+        main = torch.cuda.current_stream(self.device)
+        side = self._side
+        r = self.local_ranks[0]
+
+        def on_wgrad_done(l):
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                st.push_sync(self.lr, R, groups=(m.wgroup(l),), count_step=False, broadcast=not self.fused_pull)
+
+        loss, correct = m.forward_backward(st, self.x[r], self.labels[r], rank=r, fused_pull=self.fused_pull,
+                                           on_wgrad_done=on_wgrad_done)
+        self._losses[r], self._corrects[r] = loss, correct
+        side.wait_stream(main)
+        with torch.cuda.stream(side):                           # all pushes share the signal pads:
+            st.push_sync(self.lr, R, groups=("fp32",))          # keep them on ONE stream, in order
+        main.wait_stream(side)
 
     @property
     def last_loss(self) -> torch.Tensor:

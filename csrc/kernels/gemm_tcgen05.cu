@@ -40,6 +40,13 @@ struct GemmParams {
   void* lowp;
   const int* a_row_offset;   // device scalar added to A's stored-row coordinate (resident datasets)
   long long c_split_stride;  // EPI_STORE with split_k > 1: split s writes its partial to C + s*stride
+  // ---- K2: pull (all-gather of the weight shards) fused into this GEMM.  B is [K,N] row-major
+  // bf16, row-sharded over `gather_world` ranks; `gather_src[r]` is rank r's copy (valid in its own
+  // row range, peer-mapped), `gather_dst` the local copy the TMA descriptor of B points at.
+  const void* const* gather_src;
+  void* gather_dst;
+  unsigned int* gather_flags;   // [num_k_blocks + 1]: panel-landed flags + CTA arrival counter
+  int gather_world, gather_rank, gather_ctas, gather_kb_per_rank;
 };
 
 __device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
@@ -100,20 +107,95 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 
   const int tiles_mn = p.num_m_blocks * p.num_n_blocks;
   const int total_tiles = tiles_mn * p.split_k;
+  // With the gather role active the first `gather_ctas` CTAs move weight panels and the remaining
+  // ones are the GEMM; the k loop starts at this rank's own (already local) panels.
+  const int G = p.gather_src ? p.gather_ctas : 0;
+  const int gemm_cta = (int)blockIdx.x - G;
+  const int gemm_ctas = (int)gridDim.x - G;
+  const int k_rot = p.gather_src ? p.gather_rank * p.gather_kb_per_rank : 0;
 
-  if (warp_idx == 0) {
+  if (gemm_cta < 0) {
+    // ===================== gather role (K2) =====================
+    // One thread streams remote panels  peer HBM -> smem ring -> local HBM  with 1-D bulk copies
+    // (cp.async.bulk): kStages * 32 KiB in flight per CTA, no registers, no other threads needed.
+    // A panel = BLOCK_K consecutive rows of B = one contiguous run of BLOCK_K*N elements.
+    if (warp_idx == 0 && elect_one()) {
+      constexpr uint32_t kChunk = 32768;
+      constexpr int kRingMem = (kStages * kStageBytes) / kChunk;
+      constexpr int kRing = kRingMem < 2 * kStages ? kRingMem : 2 * kStages;   // slots (smem) vs barriers
+      constexpr int kDepth = kRing - 1;                                         // loads kept in flight
+      uint64_t* ring_bar = full_bar;   // full_bar[kStages] ++ empty_bar[kStages]: unused by this CTA otherwise
+      const size_t panel_bytes = (size_t)BLOCK_K * p.N * kElemBytes;
+      const int chunks_per_panel = (int)((panel_bytes + kChunk - 1) / kChunk);
+      const int nkb = p.num_k_blocks;
+      const int remote_panels = nkb - p.gather_kb_per_rank;
+      // job list: remote panels in ring order after our own range, dealt round-robin to the gather CTAs
+      const int my_jobs = max((remote_panels - (int)blockIdx.x + G - 1) / G, 0);
+      const int total_chunks = my_jobs * chunks_per_panel;
+      for (int i = 0; i < total_chunks + kDepth; ++i) {
+        if (i >= kDepth) {   // retire chunk j: it has landed in smem -> store it to local HBM
+          const int j = i - kDepth;
+          const int job = j / chunks_per_panel, ci = j % chunks_per_panel;
+          const int kb = (k_rot + p.gather_kb_per_rank + (int)blockIdx.x + job * G) % nkb;
+          const size_t off = (size_t)kb * panel_bytes + (size_t)ci * kChunk;
+          const uint32_t bytes = (uint32_t)min((size_t)kChunk, panel_bytes - (size_t)ci * kChunk);
+          const int slot = j % kRing;
+          mbar_wait(&ring_bar[slot], (uint32_t)(j / kRing) & 1u);
+          bulk_store_s2g(reinterpret_cast<uint8_t*>(p.gather_dst) + off, smem + (size_t)slot * kChunk, bytes);
+          bulk_commit();
+          if (ci == chunks_per_panel - 1) {
+            // the whole panel is on its way: wait until it is IN local memory, then publish it to
+            // the GEMM CTAs (they read it through TMA, i.e. the async proxy)
+            bulk_wait_all<0>();
+            fence_proxy_async_all();
+            __threadfence();
+            st_release_gpu(p.gather_flags + kb, 1u);
+          }
+        }
+        if (i < total_chunks) {   // issue the load of chunk i from the owner's HBM (over NVLink)
+          const int job = i / chunks_per_panel, ci = i % chunks_per_panel;
+          const int kb = (k_rot + p.gather_kb_per_rank + (int)blockIdx.x + job * G) % nkb;
+          const int owner = kb / p.gather_kb_per_rank;
+          const size_t off = (size_t)kb * panel_bytes + (size_t)ci * kChunk;
+          const uint32_t bytes = (uint32_t)min((size_t)kChunk, panel_bytes - (size_t)ci * kChunk);
+          const int slot = i % kRing;
+          if (i >= kRing) bulk_wait_read<0>();   // the store that last used this slot has drained its smem
+          mbar_arrive_expect_tx(&ring_bar[slot], bytes);
+          bulk_load_g2s(smem + (size_t)slot * kChunk, reinterpret_cast<const uint8_t*>(p.gather_src[owner]) + off,
+                        bytes, &ring_bar[slot]);
+        }
+      }
+      bulk_wait_all<0>();
+    }
+  } else if (warp_idx == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      uint32_t seen[16] = {0};   // panels already observed as landed (<= 512 k-blocks)
+      for (int t = gemm_cta; t < total_tiles; t += gemm_ctas) {
         const int split = t % p.split_k;
         const int tmn = t / p.split_k;
         const int m_blk = tmn % p.num_m_blocks;
         const int n_blk = tmn / p.num_m_blocks;
         const int kb0 = split * p.k_blocks_per_split;
         const int kb1 = min(kb0 + p.k_blocks_per_split, p.num_k_blocks);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int ki = kb0; ki < kb1; ++ki) {
+          int kb = ki;
+          if (p.gather_src) {   // own panels first; a remote panel must have landed locally
+            kb = (ki + k_rot) % p.num_k_blocks;
+            if (kb / p.gather_kb_per_rank != p.gather_rank && !((seen[kb >> 5] >> (kb & 31)) & 1u)) {
+              const uint64_t t0 = globaltimer_ns();
+              while (ld_acquire_gpu(p.gather_flags + kb) == 0u) {
+                if (globaltimer_ns() - t0 > B200PS_WAIT_TIMEOUT_NS) {
+                  printf("b200ps: gather panel %d never landed (block %d)\n", kb, blockIdx.x);
+                  __trap();
+                }
+              }
+              fence_proxy_async_all();
+              seen[kb >> 5] |= 1u << (kb & 31);
+            }
+          }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = smem + stage * kStageBytes;
           uint8_t* sB = sA + kABytes;
@@ -138,7 +220,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         }
       }
     }
-  } else if (warp_idx == 1) {
+  } else if (warp_idx == 1 && gemm_cta >= 0) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc(kTf32 ? 2u : 1u, p.a_mn, p.b_mn, kBlockM, BLOCK_N);
     // K-major SW128: 8-row groups 1024 B apart (SBO); LBO unused.  MN-major SW128: atoms of
@@ -155,7 +237,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int t = gemm_cta; t < total_tiles; t += gemm_ctas) {
       const int split = t % p.split_k;
       const int kb0 = split * p.k_blocks_per_split;
       const int kb1 = min(kb0 + p.k_blocks_per_split, p.num_k_blocks);
@@ -184,12 +266,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp_idx >= 4) {
+  } else if (warp_idx >= 4 && gemm_cta >= 0) {
     // ===================== epilogue =====================
     const int quarter = warp_idx & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int t = gemm_cta; t < total_tiles; t += gemm_ctas) {
       const int tmn = t / p.split_k;
       const int split = t % p.split_k;
       const int m_blk = tmn % p.num_m_blocks;
@@ -346,6 +428,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     tcgen05_fence_after();
     tmem_dealloc<kTmemCols>(tmem_base);
   }
+  if (p.gather_src && threadIdx.x == 0) {
+    // last CTA out re-arms the panel flags for the next launch (nobody can still be reading them)
+    __threadfence();
+    if (atomicAdd(p.gather_flags + p.num_k_blocks, 1u) == gridDim.x - 1) {
+      for (int kb = 0; kb <= p.num_k_blocks; ++kb) p.gather_flags[kb] = 0u;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------
@@ -396,7 +485,7 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   else               rc = encode_map(&tmB, a.B, kTf32, a.N, a.K, a.ldb, ATOM_MN, BLOCK_K, kTf32);
   if (rc) return rc;
 
-  GemmParams p;
+  GemmParams p{};
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.a_mn = a.a_mn_major ? 1 : 0;
   p.b_mn = a.b_mn_major ? 1 : 0;
@@ -421,6 +510,25 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   p.lowp = a.sgd_lowp;
   p.a_row_offset = a.a_row_offset;
   p.c_split_stride = a.c_split_stride;
+  int gather_ctas = 0;
+  if (a.gather_src) {
+    const bool is_bf16 = !kTf32;   // (a runtime value keeps the tf32 instantiations free of dead-code warnings)
+    B200PS_REQUIRE(is_bf16 && a.b_mn_major && a.ldb == a.N && p.split_k == 1 && a.epilogue == B200PS_EPI_STORE,
+                   "gemm: the fused pull needs bf16, B stored [K,N] densely (ldb == N), split_k == 1 and a store epilogue");
+    B200PS_REQUIRE(a.gather_world >= 1 && a.gather_rank >= 0 && a.gather_rank < a.gather_world && a.gather_flags,
+                   "gemm: bad gather rank/world/flags");
+    B200PS_REQUIRE(a.K % (a.gather_world * BLOCK_K) == 0 && p.num_k_blocks <= 512,
+                   "gemm: fused pull needs K (%d) divisible by world*%d and at most 512 k-blocks", a.K, BLOCK_K);
+    p.gather_src = a.gather_src;
+    p.gather_dst = const_cast<void*>(a.B);
+    p.gather_flags = a.gather_flags;
+    p.gather_world = a.gather_world;
+    p.gather_rank = a.gather_rank;
+    p.gather_kb_per_rank = p.num_k_blocks / a.gather_world;
+    gather_ctas = a.gather_world == 1 ? 0 : (a.gather_ctas > 0 ? a.gather_ctas : 8);
+    p.gather_ctas = gather_ctas;
+    if (a.gather_world == 1) p.gather_src = nullptr;   // nothing to pull: plain GEMM
+  }
   // 16-byte vector path: every row start and every 32-column chunk start must be 16 B aligned
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
   const int c_esz = (a.epilogue == B200PS_EPI_SGD) ? 2 : (p.c_is_f32 ? 4 : 2);
@@ -438,7 +546,12 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   }
   const int total_tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
   int ctas = a.max_ctas > 0 ? a.max_ctas : sm_count();
-  if (ctas > total_tiles) ctas = total_tiles;
+  if (p.gather_src) {
+    // gather CTAs + GEMM CTAs must be co-resident (the GEMM waits on panels the gather role lands)
+    ctas = std::min(ctas, sm_count());
+    B200PS_REQUIRE(ctas > gather_ctas, "gemm: no CTAs left for the GEMM next to %d gather CTAs", gather_ctas);
+    ctas = std::min(ctas - gather_ctas, total_tiles) + gather_ctas;
+  } else if (ctas > total_tiles) ctas = total_tiles;
   B200PS_CUDA_CHECK(launch_pdl(kern, dim3(ctas), dim3(kGemmThreads), kSmem, stream, tmA, tmB, p));
   B200PS_LAUNCH_CHECK();
   return 0;

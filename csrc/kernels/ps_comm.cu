@@ -49,6 +49,7 @@ struct CommArgs {
   int replicas_to_aggregate;
   float lr;
   int* cursor;                // resident-dataset batch pointer advanced at the end of the step
+  int broadcast;              // 1: write fresh values into every replica; 0: owner's copy only (pull is fused elsewhere)
   int cursor_step, cursor_wrap;
 };
 
@@ -147,6 +148,7 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
       x.x -= step * s[u].x; x.y -= step * s[u].y; x.z -= step * s[u].z; x.w -= step * s[u].w;
       *reinterpret_cast<float4*>(master + i) = x;
       for (int r = 0; r < world; ++r) {
+        if (!a.broadcast && r != rank) continue;
         O* dst = reinterpret_cast<O*>(a.outs[r]) + i;
         if (reinterpret_cast<void*>(dst) != reinterpret_cast<void*>(master + i)) Vec4<O>::store(dst, x);
       }
@@ -217,11 +219,21 @@ __global__ void __launch_bounds__(256) pull_kernel(const CommArgs a, int include
     const long long lo = a.bounds[r], hi = a.bounds[r + 1];
     const float* src = a.masters[r];
     const long long nvec = (hi - lo) >> 2;
-    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
-         v += (long long)gridDim.x * blockDim.x) {
-      const long long i = lo + (v << 2);
-      if (reinterpret_cast<const void*>(dst + i) == reinterpret_cast<const void*>(src + i)) continue;
-      Vec4<O>::store(dst + i, ld_relaxed_sys_v4(reinterpret_cast<const float4*>(src + i)));
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (reinterpret_cast<const void*>(dst + lo) == reinterpret_cast<const void*>(src + lo)) continue;
+    constexpr int kU = 8;   // independent 16-byte loads in flight per thread (peer latency is ~2 us)
+    for (long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += kU * stride) {
+      float4 x[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long v = v0 + u * stride;
+        if (v < nvec) x[u] = __ldcg(reinterpret_cast<const float4*>(src + lo + (v << 2)));
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long v = v0 + u * stride;
+        if (v < nvec) Vec4<O>::store(dst + lo + (v << 2), x[u]);
+      }
     }
   }
 }
@@ -255,7 +267,7 @@ extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters
                                     int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
                                     int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
                                     int32_t max_ctas, int32_t* cursor, int32_t cursor_step,
-                                    int32_t cursor_wrap, b200ps_stream_t stream) {
+                                    int32_t cursor_wrap, int32_t broadcast, b200ps_stream_t stream) {
   B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "push_sync: world=%d out of range", world);
   B200PS_REQUIRE(local_ranks >= 1 && rank_base >= 0 && rank_base + local_ranks <= world, "push_sync: bad ranks");
   B200PS_REQUIRE(grad_dtype == out_dtype, "push_sync: gradient and working-copy dtypes must match");
@@ -266,6 +278,7 @@ extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters
   a.global_steps = reinterpret_cast<unsigned long long* const*>(global_steps);
   a.world = world; a.rank_base = rank_base; a.replicas_to_aggregate = replicas_to_aggregate; a.lr = lr;
   a.cursor = cursor; a.cursor_step = cursor_step; a.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
+  a.broadcast = broadcast ? 1 : 0;
   const int want = max_ctas > 0 ? max_ctas : sm_count();
   dim3 grid(comm_grid(max_shard_elems, local_ranks, want), local_ranks);
   cudaStream_t s = as_stream(stream);

@@ -18,13 +18,12 @@ int get_workspace(size_t bytes, Workspace* out) {
     B200PS_CUDA_CHECK(cudaMemset(w.counters, 0, 64 * sizeof(unsigned int)));
   }
   if (bytes > w.capacity) {
-    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-    // growing allocates: refuse while any capture is active on the legacy/per-thread default check
+    // growing allocates, which is illegal inside a stream capture: cudaMalloc fails there and the
+    // error text below tells the caller what to do
     size_t want = (bytes + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
     void* p = nullptr;
     cudaError_t e = cudaMalloc(&p, want);
     if (e != cudaSuccess) {
-      (void)st;
       return set_error(B200PS_ERR_CUDA,
                        "workspace: cudaMalloc(%zu) failed: %s (size the workspace with an eager call "
                        "before CUDA-graph capture)", want, cudaGetErrorString(e));

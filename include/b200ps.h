@@ -83,6 +83,18 @@ typedef struct b200ps_gemm_args {
    * product to C + s*c_split_stride (elements); the consumer sums the slabs in a fixed order
    * (b200ps_mlp_tail does).  The actual number of splits is min(split_k, ceil(K / block_k)). */
   int64_t c_split_stride;
+  /* K2 — parameter pull fused into the GEMM that consumes the weights.  B ([K,N] row-major bf16,
+   * ldb == N) is row-sharded over gather_world ranks: gather_src[r] (DEVICE array of gather_world
+   * pointers) is rank r's copy of B, valid in rows [r*K/world, (r+1)*K/world) and peer-mapped;
+   * args->B is the local copy.  gather_ctas CTAs (default 8) of the same launch stream the remote
+   * row panels into the local copy with bulk-async copies over NVLink and publish them panel by
+   * panel; the GEMM CTAs start on the local panels and consume remote ones as they land.  On
+   * return of the kernel the local copy is complete (the all-gather happened as a side effect).
+   * gather_flags: (K/64 + 1) zero-initialised uint32 in local memory, re-armed by the kernel.
+   * The owners' slices must be final before the launch (b200ps_push_sync_sgd's flag round does it). */
+  const void* const* gather_src;
+  uint32_t* gather_flags;
+  int32_t gather_world, gather_rank, gather_ctas;
 } b200ps_gemm_args;
 
 int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);
@@ -211,7 +223,10 @@ int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* con
                          int32_t local_ranks, int64_t max_shard_elems, int32_t grad_dtype,
                          int32_t out_dtype, int32_t replicas_to_aggregate, float lr,
                          int32_t max_ctas, int32_t* cursor, int32_t cursor_step, int32_t cursor_wrap,
-                         b200ps_stream_t stream);
+                         int32_t broadcast, b200ps_stream_t stream);
+/* broadcast = 1: the owner also writes the fresh values into every replica's working copy (the
+ * next pull is already done).  broadcast = 0: only the owner's own copy is refreshed — use it when
+ * the consumers pull inside their GEMM (b200ps_gemm gather_src, K2). */
 /* cursor (device int32, may be NULL): after the update has landed, *cursor = (*cursor + cursor_step)
  * % cursor_wrap — the batch pointer of a resident dataset, advanced inside the captured step. */
 /* async (Hogwild): red.add of -lr*g into every owner's master; no barrier (example.py:118). */

@@ -74,7 +74,11 @@ def main():
         if i in (0, 11):
             lw.append(tw.read_loss())
     torch.cuda.synchronize()
-    res["wide_digests_equal"] = len(set(gather(ctx, digest(tw.store.flat_work("bf16"))))) == 1
+    tw.store.pull()                                   # refresh every replica from the owners' masters
+    torch.cuda.synchronize()
+    ctx.control_barrier()
+    res["wide_fused_pull"] = bool(tw.fused_pull)
+    res["wide_digests_equal"] = len(set(gather(ctx, digest(tw.store.flat_work("bf16:1"))))) == 1
     res["wide_loss"] = lw
     ctx.control_barrier()
 

@@ -95,3 +95,34 @@ def test_gemm_rejects_bad_args(native_lib):
     a = torch.zeros(10, 10, device="cuda")
     with pytest.raises(ops.native.NativeError):
         ops.gemm(a[:, :7].contiguous(), a[:, :7].contiguous())  # 28-byte rows: not TMA-able
+
+
+@pytest.mark.parametrize("world,rank", [(1, 0), (2, 1), (4, 0), (4, 2), (8, 5)])
+def test_fused_pull_gemm_virtual_ranks(native_lib, world, rank):
+    """K2: the weight all-gather runs inside the GEMM launch (gather CTAs + GEMM CTAs)."""
+    from b200ps import ops
+    g = torch.Generator(device="cuda").manual_seed(world * 10 + rank)
+    M, K, N = 384, 1024, 512
+    x = (torch.randn(M, K, device="cuda", generator=g) * 0.3).bfloat16()
+    w_full = (torch.randn(K, N, device="cuda", generator=g) * 0.3).bfloat16()
+    rows = K // world
+    # every "rank" holds a full-size buffer that is only valid in its own row range
+    copies = []
+    for r in range(world):
+        c = torch.full((K, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+        c[r * rows:(r + 1) * rows] = w_full[r * rows:(r + 1) * rows]
+        copies.append(c)
+    table = ops.device_ptr_table([c.data_ptr() for c in copies], "cuda")
+    flags = torch.zeros(K // 64 + 1, device="cuda", dtype=torch.int32)
+    bias = torch.randn(N, device="cuda", generator=g)
+    ref = torch.sigmoid(x.float() @ w_full.float() + bias)
+    for _ in range(2):                                   # second launch: flags were re-armed by the first
+        out = ops.gemm(x, copies[rank], b_mn_major=True, bias=bias, act=ops.ACT_SIGMOID,
+                       gather=dict(src_table=table, flags=flags, world=world, rank=rank, ctas=3))
+        torch.cuda.synchronize()
+        assert (out.float() - ref).abs().max().item() < 1.5e-2
+        assert torch.equal(copies[rank], w_full)         # the all-gather happened as a side effect
+        assert int(flags.abs().sum().item()) == 0
+        if world > 1:                                     # invalidate the gathered part again
+            keep = copies[rank][rank * rows:(rank + 1) * rows].clone()
+            copies[rank].fill_(float("nan")); copies[rank][rank * rows:(rank + 1) * rows] = keep

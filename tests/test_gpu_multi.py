@@ -30,6 +30,7 @@ def test_multi_gpu_trainers(native_lib, tmp_path):
     assert res["sync_loss"][1] < res["sync_loss"][0] and res["sync_acc"] > 0.2
     assert res["async_global_step"] == 40 * n and res["async_loss"][1] < res["async_loss"][0]
     assert res["wide_digests_equal"] and res["wide_loss"][1] < res["wide_loss"][0]
+    assert res["wide_fused_pull"] == (512 % (64 * n) == 0)
     assert res["sparse_async_global_step"] == 10 * n and res["sparse_sync_global_step"] == 10
     assert res["barrier_epoch"] == 5
     # a checkpoint taken on n GPUs restores on one (P25)

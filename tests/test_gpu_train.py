@@ -153,8 +153,17 @@ def test_wide_mlp_small_matches_autograd(native_lib):
             scale_w = (0.5 * ws[l].grad).abs().max().item()
             assert ew < 0.05 * scale_w + 1e-5, (world, l, ew, scale_w)
             assert eb < 0.05 * (0.5 * bs[l].grad).abs().max().item() + 1e-5, (world, l, eb)
-            w_dev = tr.store.var(tr.model.wname(l), 0)
-            assert torch.equal(w_dev.cpu(), after[tr.model.wname(l)].bfloat16())
+            # every rank's bf16 working copy agrees with the master on the rows it owns (the other
+            # rows are re-pulled inside the next forward GEMM when the pull is fused)
+            rows = D // world
+            for r in range(world):
+                w_dev = tr.store.var(tr.model.wname(l), r)[r * rows:(r + 1) * rows]
+                assert torch.equal(w_dev.cpu(), after[tr.model.wname(l)][r * rows:(r + 1) * rows].bfloat16())
+        if world > 1:
+            assert tr.fused_pull
+            tr.step()                                  # a second step consumes the fused pull of fresh weights
+            torch.cuda.synchronize()
+            assert tr.read_loss() == tr.read_loss() and tr.global_step == 2
 
 
 def test_sparse_lr_trainer_learns(native_lib):
