@@ -25,6 +25,26 @@ from .optim.sgd import AsyncSGD, SyncReplicasSGD
 from .ps.store import ParameterStore
 
 
+def _capture(body, device):
+    """Capture ``body`` into a CUDA graph.  The cyclic garbage collector is parked for the duration:
+    a collection that happened to run mid-capture could destroy unrelated CUDA objects (older
+    graphs, their memory pools), and freeing device memory is illegal while a stream is capturing
+    — it invalidates the capture."""
+    import gc
+    gc.collect()
+    torch.cuda.synchronize(device)
+    was_enabled = gc.isenabled()
+    gc.disable()
+    try:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            body()
+    finally:
+        if was_enabled:
+            gc.enable()
+    return g
+
+
 class _GraphedStep:
     """Warm up eagerly, then capture ``body`` into a CUDA graph and replay it."""
 
@@ -42,11 +62,7 @@ class _GraphedStep:
                 self.calls += 1
                 self.body()
                 return
-            torch.cuda.synchronize(self.device)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self.body()
-            self.graph = g
+            self.graph = _capture(self.body, self.device)
         self.graph.replay()
 
 
@@ -301,10 +317,7 @@ class SparseLRTrainer(_TrainerBase):
             if self.use_graph:
                 self._graphs[key] = 1 if key not in self._graphs else self._graphs[key]
         elif ent == 1:
-            torch.cuda.synchronize(self.device)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._eager(batch, rank)
+            g = _capture(lambda: self._eager(batch, rank), self.device)
             self._graphs[key] = (g, batch)          # keep the batch tensors alive with the graph
             g.replay()
         else:

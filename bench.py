@@ -224,7 +224,9 @@ def bench_wide(ctx, args, sampler):
     from b200ps.ops import native
     from b200ps.train import WideMLPTrainer
     B, L, D = args.wide_batch, args.wide_layers, args.wide_hidden
-    tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.01, use_graph=not args.no_graph)
+    tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.01, use_graph=not args.no_graph,
+                        fused_pull=os.environ.get("B200PS_WIDE_FUSED_PULL", "1") != "0",
+                        overlap=os.environ.get("B200PS_WIDE_OVERLAP", "1") != "0")
     dev = ctx.device
     ring = 4                                   # 4 x 64 MB input batches: inputs + 1 GB weights >> L2
     xs = torch.empty(ring, B, D, device=dev, dtype=torch.bfloat16)
@@ -265,6 +267,7 @@ def bench_wide(ctx, args, sampler):
         "config": {"model": f"wide_sigmoid_mlp_{L}x{D}", "global_batch": B * ctx.world, "per_gpu_batch": B,
                    "dtype": "bf16 (fp32 master, fp32 accumulate)", "mode": "sync",
                    "parallelism": f"dp{ctx.world}+ps_shard{ctx.world}",
+                   "fused_pull_in_gemm": tr.fused_pull, "push_overlapped_with_backward": tr.overlap and ctx.world > 1,
                    "inputs": f"ring of {ring} device batches; 1.07 GB of weights per step >> L2"},
     }
 

@@ -23,6 +23,7 @@ constexpr int kBlockM = 128;
 constexpr int kRowBytes = 128;           // one swizzle-128B row: 64 bf16 or 32 tf32 along K (or MN)
 constexpr int kABytes = kBlockM * kRowBytes;  // 16 KiB per stage
 constexpr int kGemmThreads = 256;
+constexpr int kGatherChunk = 16384;   // bytes per bulk copy of the fused pull; ring of 2 per CTA
 
 struct GemmParams {
   int M, N, K;
@@ -90,6 +91,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full_bar[s], 1);
       mbar_init(&tmem_empty_bar[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty_bar[3 + s], 1);  // gather ring (K2)
     }
     fence_mbar_init();
   }
@@ -107,65 +109,59 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
 
   const int tiles_mn = p.num_m_blocks * p.num_n_blocks;
   const int total_tiles = tiles_mn * p.split_k;
-  // With the gather role active the first `gather_ctas` CTAs move weight panels and the remaining
-  // ones are the GEMM; the k loop starts at this rank's own (already local) panels.
-  const int G = p.gather_src ? p.gather_ctas : 0;
-  const int gemm_cta = (int)blockIdx.x - G;
-  const int gemm_ctas = (int)gridDim.x - G;
+  // K2: with a fused pull every CTA's otherwise idle warp 3 streams remote weight panels into the
+  // local copy; the k loop starts at this rank's own (already local) panels.
+  const int gemm_cta = (int)blockIdx.x;
+  const int gemm_ctas = (int)gridDim.x;
   const int k_rot = p.gather_src ? p.gather_rank * p.gather_kb_per_rank : 0;
 
-  if (gemm_cta < 0) {
+  if (warp_idx == 3) {
     // ===================== gather role (K2) =====================
-    // One thread streams remote panels  peer HBM -> smem ring -> local HBM  with 1-D bulk copies
-    // (cp.async.bulk): kStages * 32 KiB in flight per CTA, no registers, no other threads needed.
-    // A panel = BLOCK_K consecutive rows of B = one contiguous run of BLOCK_K*N elements.
-    if (warp_idx == 0 && elect_one()) {
-      constexpr uint32_t kChunk = 32768;
-      constexpr int kRingMem = (kStages * kStageBytes) / kChunk;
-      constexpr int kRing = kRingMem < 2 * kStages ? kRingMem : 2 * kStages;   // slots (smem) vs barriers
-      constexpr int kDepth = kRing - 1;                                         // loads kept in flight
-      uint64_t* ring_bar = full_bar;   // full_bar[kStages] ++ empty_bar[kStages]: unused by this CTA otherwise
+    // One thread per CTA moves 16 KiB chunks  peer HBM -> smem ring -> local HBM  with 1-D bulk
+    // copies (cp.async.bulk).  Chunks of the remote panels, in ring order after our own range, are
+    // dealt round-robin over ALL CTAs of the launch, so ~gridDim x 32 KiB are in flight over NVLink
+    // without giving up a single SM.  A panel (BLOCK_K rows of B, contiguous) is published by
+    // counting its landed chunks in gather_flags[kb].
+    if (p.gather_src && elect_one()) {
+      constexpr uint32_t kChunk = kGatherChunk;
+      uint8_t* ring = smem + kStages * kStageBytes + 256;
+      uint64_t* gbar = tmem_empty_bar + 3;            // two spare mbarriers after the tmem pointer slot
       const size_t panel_bytes = (size_t)BLOCK_K * p.N * kElemBytes;
-      const int chunks_per_panel = (int)((panel_bytes + kChunk - 1) / kChunk);
+      const int cpp = (int)(panel_bytes / kChunk);    // chunks per panel (host guarantees divisibility)
       const int nkb = p.num_k_blocks;
-      const int remote_panels = nkb - p.gather_kb_per_rank;
-      // job list: remote panels in ring order after our own range, dealt round-robin to the gather CTAs
-      const int my_jobs = max((remote_panels - (int)blockIdx.x + G - 1) / G, 0);
-      const int total_chunks = my_jobs * chunks_per_panel;
-      for (int i = 0; i < total_chunks + kDepth; ++i) {
-        if (i >= kDepth) {   // retire chunk j: it has landed in smem -> store it to local HBM
-          const int j = i - kDepth;
-          const int job = j / chunks_per_panel, ci = j % chunks_per_panel;
-          const int kb = (k_rot + p.gather_kb_per_rank + (int)blockIdx.x + job * G) % nkb;
-          const size_t off = (size_t)kb * panel_bytes + (size_t)ci * kChunk;
-          const uint32_t bytes = (uint32_t)min((size_t)kChunk, panel_bytes - (size_t)ci * kChunk);
-          const int slot = j % kRing;
-          mbar_wait(&ring_bar[slot], (uint32_t)(j / kRing) & 1u);
-          bulk_store_s2g(reinterpret_cast<uint8_t*>(p.gather_dst) + off, smem + (size_t)slot * kChunk, bytes);
-          bulk_commit();
-          if (ci == chunks_per_panel - 1) {
-            // the whole panel is on its way: wait until it is IN local memory, then publish it to
-            // the GEMM CTAs (they read it through TMA, i.e. the async proxy)
-            bulk_wait_all<0>();
-            fence_proxy_async_all();
-            __threadfence();
-            st_release_gpu(p.gather_flags + kb, 1u);
-          }
+      const long long total = (long long)(nkb - p.gather_kb_per_rank) * cpp;   // remote chunks, whole launch
+      // software pipeline, two loads in flight: load(n+1) is issued before load(n) is consumed
+      auto chunk_kb = [&](long long c) { return (k_rot + p.gather_kb_per_rank + (int)(c / cpp)) % nkb; };
+      auto issue_load = [&](long long c, int n) {
+        const int slot = n & 1;
+        const int kb = chunk_kb(c);
+        const size_t off = (size_t)kb * panel_bytes + (size_t)(c % cpp) * kChunk;
+        mbar_arrive_expect_tx(&gbar[slot], kChunk);
+        bulk_load_g2s(ring + slot * kChunk,
+                      reinterpret_cast<const uint8_t*>(p.gather_src[kb / p.gather_kb_per_rank]) + off, kChunk, &gbar[slot]);
+      };
+      auto publish = [&](long long c) {   // chunk c is completely in local memory
+        fence_proxy_async_all();
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.gather_flags + chunk_kb(c)) : "memory");
+      };
+      long long c = blockIdx.x;
+      if (c < total) issue_load(c, 0);
+      long long prev = -1;   // chunk whose store is committed but not yet known complete
+      for (int n = 0; c < total; c += gridDim.x, ++n) {
+        const long long cn = c + gridDim.x;
+        if (cn < total) {
+          if (n >= 1) bulk_wait_read<0>();            // slot (n+1)&1 was read by the store of chunk n-1
+          issue_load(cn, n + 1);
         }
-        if (i < total_chunks) {   // issue the load of chunk i from the owner's HBM (over NVLink)
-          const int job = i / chunks_per_panel, ci = i % chunks_per_panel;
-          const int kb = (k_rot + p.gather_kb_per_rank + (int)blockIdx.x + job * G) % nkb;
-          const int owner = kb / p.gather_kb_per_rank;
-          const size_t off = (size_t)kb * panel_bytes + (size_t)ci * kChunk;
-          const uint32_t bytes = (uint32_t)min((size_t)kChunk, panel_bytes - (size_t)ci * kChunk);
-          const int slot = i % kRing;
-          if (i >= kRing) bulk_wait_read<0>();   // the store that last used this slot has drained its smem
-          mbar_arrive_expect_tx(&ring_bar[slot], bytes);
-          bulk_load_g2s(smem + (size_t)slot * kChunk, reinterpret_cast<const uint8_t*>(p.gather_src[owner]) + off,
-                        bytes, &ring_bar[slot]);
-        }
+        const int slot = n & 1;
+        const size_t off = (size_t)chunk_kb(c) * panel_bytes + (size_t)(c % cpp) * kChunk;
+        mbar_wait(&gbar[slot], (uint32_t)(n >> 1) & 1u);
+        bulk_store_s2g(reinterpret_cast<uint8_t*>(p.gather_dst) + off, ring + slot * kChunk, kChunk);
+        bulk_commit();
+        if (prev >= 0) { bulk_wait_all<1>(); publish(prev); }
+        prev = c;
       }
-      bulk_wait_all<0>();
+      if (prev >= 0) { bulk_wait_all<0>(); publish(prev); }
     }
   } else if (warp_idx == 0) {
     // ===================== TMA producer =====================
@@ -173,6 +169,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       int stage = 0;
       uint32_t phase = 0;
       uint32_t seen[16] = {0};   // panels already observed as landed (<= 512 k-blocks)
+      const uint32_t gather_cpp = p.gather_src ? (uint32_t)(((size_t)BLOCK_K * p.N * kElemBytes) / kGatherChunk) : 0u;
       for (int t = gemm_cta; t < total_tiles; t += gemm_ctas) {
         const int split = t % p.split_k;
         const int tmn = t / p.split_k;
@@ -186,13 +183,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
             kb = (ki + k_rot) % p.num_k_blocks;
             if (kb / p.gather_kb_per_rank != p.gather_rank && !((seen[kb >> 5] >> (kb & 31)) & 1u)) {
               const uint64_t t0 = globaltimer_ns();
-              while (ld_acquire_gpu(p.gather_flags + kb) == 0u) {
+              while (ld_acquire_gpu(p.gather_flags + kb) < gather_cpp) {
                 if (globaltimer_ns() - t0 > B200PS_WAIT_TIMEOUT_NS) {
                   printf("b200ps: gather panel %d never landed (block %d)\n", kb, blockIdx.x);
                   __trap();
                 }
               }
-              fence_proxy_async_all();
+              // (the panel was written by bulk-async stores and is read by TMA: same proxy, so the
+              //  acquire on the flag is all the ordering the consumer side needs)
               seen[kb >> 5] |= 1u << (kb & 31);
             }
           }
@@ -220,7 +218,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
         }
       }
     }
-  } else if (warp_idx == 1 && gemm_cta >= 0) {
+  } else if (warp_idx == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc(kTf32 ? 2u : 1u, p.a_mn, p.b_mn, kBlockM, BLOCK_N);
     // K-major SW128: 8-row groups 1024 B apart (SBO); LBO unused.  MN-major SW128: atoms of
@@ -266,7 +264,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp_idx >= 4 && gemm_cta >= 0) {
+  } else if (warp_idx >= 4) {
     // ===================== epilogue =====================
     const int quarter = warp_idx & 3;
     int acc = 0;
@@ -470,7 +468,7 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   constexpr int BLOCK_K = kRowBytes / esz;
   constexpr int ATOM_MN = kRowBytes / esz;
   constexpr int kStageBytes = kABytes + BLOCK_N * kRowBytes;
-  constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + 2 * kGatherChunk /*K2 ring*/;
   static_assert(kSmem <= 232448, "shared memory budget");
 
   CUtensorMap tmA, tmB;
@@ -525,8 +523,10 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
     p.gather_world = a.gather_world;
     p.gather_rank = a.gather_rank;
     p.gather_kb_per_rank = p.num_k_blocks / a.gather_world;
-    gather_ctas = a.gather_world == 1 ? 0 : (a.gather_ctas > 0 ? a.gather_ctas : 8);
-    p.gather_ctas = gather_ctas;
+    B200PS_REQUIRE(((size_t)BLOCK_K * a.N * 2) % kGatherChunk == 0,
+                   "gemm: fused pull needs 64*N*2 bytes (one row panel) to be a multiple of %d", kGatherChunk);
+    gather_ctas = 0;
+    p.gather_ctas = 0;
     if (a.gather_world == 1) p.gather_src = nullptr;   // nothing to pull: plain GEMM
   }
   // 16-byte vector path: every row start and every 32-column chunk start must be 16 B aligned
@@ -546,12 +546,8 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   }
   const int total_tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
   int ctas = a.max_ctas > 0 ? a.max_ctas : sm_count();
-  if (p.gather_src) {
-    // gather CTAs + GEMM CTAs must be co-resident (the GEMM waits on panels the gather role lands)
-    ctas = std::min(ctas, sm_count());
-    B200PS_REQUIRE(ctas > gather_ctas, "gemm: no CTAs left for the GEMM next to %d gather CTAs", gather_ctas);
-    ctas = std::min(ctas - gather_ctas, total_tiles) + gather_ctas;
-  } else if (ctas > total_tiles) ctas = total_tiles;
+  if (p.gather_src) ctas = std::min(ctas, sm_count());   // all CTAs co-resident: they wait on each other's gather work
+  if (ctas > total_tiles) ctas = total_tiles;
   B200PS_CUDA_CHECK(launch_pdl(kern, dim3(ctas), dim3(kGemmThreads), kSmem, stream, tmA, tmB, p));
   B200PS_LAUNCH_CHECK();
   return 0;
