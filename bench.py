@@ -196,7 +196,23 @@ def bench_mnist(ctx, args, sampler, mode):
 
     for i in range(max(args.warmup, 3)):
         e2e_step(i)
-    ms_e2e = wall_region(ctx, torch, sampler, args.steps, e2e_step)
+    ms_e2e_blocking = wall_region(ctx, torch, sampler, args.steps, e2e_step)
+    # pipelined form of the same API: step t+1 is queued before the host blocks on the loss of step t
+    pending = []
+
+    def e2e_pipelined(i):
+        pending.append(tr.step_from_host_async(hx[i % ring], hy[i % ring]))
+        if len(pending) > 2:
+            pending.pop(0).result()
+        if i == args.steps - 1:
+            while pending:
+                pending.pop(0).result()
+
+    for i in range(3):
+        e2e_pipelined(-1)
+    while pending:
+        pending.pop(0).result()
+    ms_e2e = wall_region(ctx, torch, sampler, args.steps, e2e_pipelined)
     acc, test_loss = tr.evaluate(data[:10000], labels[:10000])
     gstep = tr.global_step
     out = {
@@ -204,7 +220,10 @@ def bench_mnist(ctx, args, sampler, mode):
         "gpu_launches": per_step * args.steps, "launches_per_step": per_step,
         "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
                 "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 4,
+                "api": "MLPTrainer.step_from_host_async (loss of step t read after step t+2 is queued)",
+                "blocking_value": B * ctx.world * args.steps / (ms_e2e_blocking / 1e3),
+                "blocking_api": "MLPTrainer.step_from_host (host blocks on every step's loss)"},
         "loss_first": loss0, "loss_last": loss1, "train_subset_accuracy": acc, "global_step": gstep,
         "config": {"model": "mnist_sigmoid_mlp_784_100_10", "global_batch": B * ctx.world,
                    "per_gpu_batch": B, "seq_len": None, "mode": mode,
@@ -225,7 +244,7 @@ def bench_wide(ctx, args, sampler):
     from b200ps.train import WideMLPTrainer
     B, L, D = args.wide_batch, args.wide_layers, args.wide_hidden
     tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.01, use_graph=not args.no_graph,
-                        fused_pull=os.environ.get("B200PS_WIDE_FUSED_PULL", "1") != "0",
+                        fused_pull=os.environ.get("B200PS_WIDE_FUSED_PULL", "0") != "0",
                         overlap=os.environ.get("B200PS_WIDE_OVERLAP", "1") != "0")
     dev = ctx.device
     ring = 4                                   # 4 x 64 MB input batches: inputs + 1 GB weights >> L2

@@ -89,7 +89,7 @@ __device__ __forceinline__ bool replica_counts(int r, uint32_t epoch, int world,
 }
 
 template <typename G, typename O>
-__global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
+__global__ void __launch_bounds__(1024) push_sync_sgd_kernel(const CommArgs a) {
   const int rank = a.rank_base + blockIdx.y;
   const int world = a.world;
   const int tid = threadIdx.x;
@@ -171,8 +171,12 @@ __global__ void __launch_bounds__(256) push_sync_sgd_kernel(const CommArgs a) {
   __syncthreads();
   __shared__ bool s_last;
   if (tid == 0) {
-    __threadfence();   // gpu scope here; the last CTA issues the one system-scope fence
-    s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
+    if (gridDim.x == 1) {
+      s_last = true;   // a small shard is handled by ONE wide CTA: no arrival counting at all
+    } else {
+      __threadfence();   // gpu scope here; the last CTA issues the one system-scope fence
+      s_last = (atomicAdd(pad + kSlotCtaDone, 1u) == gridDim.x - 1);
+    }
   }
   __syncthreads();
   if (s_last) {
@@ -280,12 +284,16 @@ extern "C" int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters
   a.cursor = cursor; a.cursor_step = cursor_step; a.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
   a.broadcast = broadcast ? 1 : 0;
   const int want = max_ctas > 0 ? max_ctas : sm_count();
-  dim3 grid(comm_grid(max_shard_elems, local_ranks, want), local_ranks);
+  // latency-bound regime (small shards, several ranks): one 1024-thread CTA per rank does the whole
+  // shard in one trip of 4 float4 per thread, and the per-CTA fence/atomic/last-CTA machinery vanishes
+  const bool one_cta = world > 1 && max_shard_elems <= 16384;
+  dim3 grid(one_cta ? 1 : comm_grid(max_shard_elems, local_ranks, want), local_ranks);
+  dim3 block(one_cta ? 1024 : 256);
   cudaStream_t s = as_stream(stream);
   if (grad_dtype == B200PS_DT_F32)
-    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<float, float>, grid, dim3(256), 0, s, a));
+    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<float, float>, grid, block, 0, s, a));
   else
-    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<__nv_bfloat16, __nv_bfloat16>, grid, dim3(256), 0, s, a));
+    B200PS_CUDA_CHECK(launch_pdl(push_sync_sgd_kernel<__nv_bfloat16, __nv_bfloat16>, grid, block, 0, s, a));
   B200PS_LAUNCH_CHECK();
   return 0;
 }

@@ -65,7 +65,7 @@ def main():
     res["async_loss"] = l2
 
     # ---- wide MLP (bf16 group + fp32 group) at a small size
-    tw = WideMLPTrainer(ctx, batch_size=256, layers=3, hidden=512, lr=0.5, use_graph=False)
+    tw = WideMLPTrainer(ctx, batch_size=256, layers=3, hidden=512, lr=0.5, use_graph=True, fused_pull=True)
     xb = torch.empty(256, 512, device=dev, dtype=torch.bfloat16); yb = torch.empty(256, device=dev, dtype=torch.int32)
     ops.synth_dense_bf16(xb, yb, classes=512, seed=3, offset=rank * 256)
     lw = []

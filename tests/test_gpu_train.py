@@ -124,7 +124,7 @@ def test_wide_mlp_small_matches_autograd(native_lib):
     B, L, D = 256, 3, 512
     for world in (1, 2):
         ctx = init_from_env(virtual_world=world)
-        tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.5, use_graph=False)
+        tr = WideMLPTrainer(ctx, batch_size=B, layers=L, hidden=D, lr=0.5, use_graph=False, fused_pull=True)
         xs = torch.empty(world, B, D, device=DEV, dtype=torch.bfloat16)
         ys = torch.empty(world, B, device=DEV, dtype=torch.int32)
         for r in range(world):

@@ -1,0 +1,111 @@
+"""Turn gpurun_out/*.ncu-rep and launch lists into the tracked summaries under profiles/."""
+import collections
+import csv
+import json
+import os
+import re
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "profiles")
+GP = os.path.join(ROOT, "gpurun_out")
+KEYS = [
+    ("gpu__time_duration.sum", "duration_us"),
+    ("sm__cycles_elapsed.max", "sm_cycles"),
+    ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor_pipe_active_pct"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm_throughput_pct"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram_throughput_pct"),
+    ("dram__bytes_read.sum", "dram_read"),
+    ("dram__bytes_write.sum", "dram_write"),
+    ("launch__registers_per_thread", "regs_per_thread"),
+    ("launch__grid_size", "grid"),
+    ("launch__block_size", "block"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps_active_pct"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue_active_pct"),
+    ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem_bank_conflicts"),
+    ("lts__t_sector_hit_rate.pct", "l2_hit_pct"),
+]
+
+
+def ncu_raw(rep):
+    r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
+    rows = list(csv.reader(r.stdout.splitlines()))
+    hdr, units = rows[0], rows[1]
+    out = []
+    for row in rows[2:]:
+        d = {"kernel": re.sub(r"\(.*", "", row[hdr.index("Kernel Name")])[:90]}
+        for k, name in KEYS:
+            if k in hdr and row[hdr.index(k)] not in ("", "n/a"):
+                d[name] = row[hdr.index(k)] + (" " + units[hdr.index(k)] if units[hdr.index(k)] not in ("", "%") else "")
+        out.append(d)
+    return out
+
+
+def launch_list(path):
+    lines = [l for l in open(path) if not l.startswith("==")]
+    agg = collections.OrderedDict()
+    rows = list(csv.DictReader(lines))
+    n = len(rows)
+    for r in rows[-(n // 4):]:                     # last of the 4 profiled steps
+        name = re.sub(r"\(.*", "", r["Kernel Name"])[:80]
+        a = agg.setdefault(name, [0.0, 0])
+        a[0] += float(r["Metric Value"].replace(",", "")) / 1e3
+        a[1] += 1
+    return agg
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    md = ["# Profiles (B200, sm_100a)", "",
+          "All captures: `ncu --set full --clock-control none --import-source on` on ONE GPU, after the same command "
+          "had exited 0 without ncu (`tools/gpu_profiles.sh`).  Durations under ncu are cold-cache and serialised: "
+          "compare shares, not absolutes; the timed numbers are the CUDA-event ones in `bench_*.json`.",
+          "`compute-sanitizer` is closed on this pool (the tool answered so; `gpurun_out/sanitizer_memcheck.log`), "
+          "so memory safety rests on the bounded-wait traps, shape/alignment checks and the reference-comparison tests.", ""]
+    for cfg in ("mnist", "wide", "sparse"):
+        rep = os.path.join(GP, f"prof_{cfg}.ncu-rep")
+        if os.path.exists(rep):
+            rows = ncu_raw(rep)
+            json.dump(rows, open(os.path.join(OUT, f"ncu_{cfg}.json"), "w"), indent=1)
+            md += [f"## ncu --set full: {cfg} step kernels", "",
+                   "| kernel | duration | tensor pipe active % | SM throughput % | DRAM throughput % | DRAM read | DRAM write | regs | grid |",
+                   "|---|---|---|---|---|---|---|---|---|"]
+            for d in rows:
+                md.append("| `{}` | {} | {} | {} | {} | {} | {} | {} | {} |".format(
+                    d["kernel"], d.get("duration_us", ""), d.get("tensor_pipe_active_pct", ""), d.get("sm_throughput_pct", ""),
+                    d.get("dram_throughput_pct", ""), d.get("dram_read", ""), d.get("dram_write", ""),
+                    d.get("regs_per_thread", ""), d.get("grid", "")))
+            md.append("")
+        ll = os.path.join(GP, f"launches_{cfg}.csv")
+        if os.path.exists(ll):
+            agg = launch_list(ll)
+            tot = sum(v[0] for v in agg.values())
+            md += [f"### launch list of one {cfg} step (gpu__time_duration, eager, under ncu)", "",
+                   "| kernel | launches | total us | share |", "|---|---|---|---|"]
+            for name, (t, c) in agg.items():
+                md.append(f"| `{name}` | {c} | {t:.1f} | {100 * t / tot:.1f}% |")
+            md += [f"| **sum** | | {tot:.1f} | |", ""]
+            os.replace(ll, os.path.join(OUT, f"launches_{cfg}.csv")) if False else None
+            open(os.path.join(OUT, f"launches_{cfg}.csv"), "w").write(open(ll).read())
+    for f in sorted(os.listdir(GP)):
+        if f.startswith("pushpull_sweep_n") and f.endswith(".json"):
+            rows = json.load(open(os.path.join(GP, f)))
+            json.dump(rows, open(os.path.join(OUT, f), "w"), indent=1)
+            n = rows[0]["n_gpus"]
+            md += [f"## push/pull sweep, {n} GPUs (`bench/pushpull_sweep.py`; us = CUDA events, max over ranks)", "",
+                   "| bytes | push_sync us | NCCL rs+add+ag us | pull us | NCCL all_gather us | push_async us | NCCL rs+add us | "
+                   "push_sync GB/s/dir | fraction of 770 GB/s |", "|---|---|---|---|---|---|---|---|---|"]
+            for r in rows:
+                md.append(f"| {r['bytes']} | {r['push_sync_us']} | {r['nccl_push_us']} | {r['pull_us']} | {r['nccl_allgather_us']} | "
+                          f"{r['push_async_us']} | {r['nccl_rs_apply_us']} | {r['push_sync_GBs_per_dir']} | {r['push_sync_frac_of_link']} |")
+            md.append("")
+    md += ["## SASS evidence", "",
+           "`profiles/sass_mnemonics.txt` (from `tools/sass_summary.sh`, cuobjdump of libb200ps.so) lists per kernel the "
+           "Blackwell instructions present: `UTCHMMA` (tcgen05.mma), `LDTM` (tcgen05.ld), `UTMALDG` (TMA tensor loads), "
+           "`UBLKCP` (cp.async.bulk of the fused pull), `SYNCS.*` (mbarrier), `REDG.E.ADD.F32...SYS` (peer reductions).", ""]
+    open(os.path.join(OUT, "README.md"), "w").write("\n".join(md))
+    print("\n".join(md)[:6000])
+
+
+if __name__ == "__main__":
+    main()
