@@ -29,6 +29,10 @@ SIGNATURES = {
     "b200ps_symm_free": [vp],
     "b200ps_device_count": [C.POINTER(i32)],
     "b200ps_can_access_peer": [i32, i32, C.POINTER(i32)],
+    "b200ps_host_step": [vp, vp, u64, vp, vp, u64, vp, vp, vp, u64, vp, vp],
+    "b200ps_event_create": [C.POINTER(vp)],
+    "b200ps_event_synchronize": [vp],
+    "b200ps_event_destroy": [vp],
     "b200ps_libsvm_count": [C.c_char_p, u64, C.POINTER(u64), C.POINTER(u64)],
 }
 

@@ -112,6 +112,15 @@ class _TrainerBase:
         self.ctx.close()
 
 
+class _NativeLossHandle:
+    def __init__(self, view, event, lib):
+        self._view, self._event, self._lib = view, event, lib
+
+    def result(self) -> float:
+        self._lib.b200ps_event_synchronize(self._event)
+        return float(self._view[0])
+
+
 class _LossHandle:
     """Result of ``step_from_host_async``: ``result()`` blocks until that step's loss is on the host."""
 
@@ -218,8 +227,35 @@ class MLPTrainer(_TrainerBase):
 
     def step_from_host(self, x_pinned: torch.Tensor, labels_pinned: torch.Tensor) -> float:
         """The end-to-end call: pinned host batch in, loss (python float) out."""
-        self.step(x_pinned, labels_pinned)
-        return self.read_loss()
+        return self.step_from_host_async(x_pinned, labels_pinned).result()
+
+    def step_from_host_async(self, x_pinned: torch.Tensor, labels_pinned: torch.Tensor):
+        """Queue one end-to-end step and return a handle whose ``result()`` is that step's loss.
+        Once the step graph exists the whole host side (2 H2D copies, graph launch, loss D2H copy,
+        completion event) is ONE native call (``b200ps_host_step``)."""
+        g = self._step.graph
+        if g is None or len(self.local_ranks) != 1:
+            return super().step_from_host_async(x_pinned, labels_pinned)
+        import ctypes as C
+        from .ops import native
+        lib = native.load()
+        if not hasattr(self, "_nring"):
+            self._nring, self._nring_i = [], 0
+            for _ in range(4):
+                ev = C.c_void_p()
+                native.check(lib.b200ps_event_create(C.byref(ev)), "event_create")
+                slot = torch.zeros(1).pin_memory()
+                self._nring.append((slot, slot.numpy(), ev))
+            self._gexec = g.raw_cuda_graph_exec()
+        r = self.local_ranks[0]
+        slot, view, ev = self._nring[self._nring_i % 4]
+        self._nring_i += 1
+        x, y, loss = self.x[r], self.labels[r], self._losses[r]
+        native.check(lib.b200ps_host_step(
+            x.data_ptr(), x_pinned.data_ptr(), x.numel() * 4, y.data_ptr(), labels_pinned.data_ptr(), y.numel() * 4,
+            self._gexec, slot.data_ptr(), loss.data_ptr(), 4, ev, native.stream_ptr()), "host_step")
+        self.local_step += 1
+        return _NativeLossHandle(view, ev, lib)
 
     def evaluate(self, x: torch.Tensor, labels: torch.Tensor):
         return self.model.evaluate(self.store, x, labels, rank=self.local_ranks[0])

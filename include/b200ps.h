@@ -253,6 +253,18 @@ int b200ps_device_count(int32_t* n);
 int b200ps_can_access_peer(int32_t dev, int32_t peer, int32_t* ok);
 
 /* ------------------------------------------------------------------------------------
+ * Runtime: the host side of one end-to-end step in a single call — two optional H2D copies from
+ * pinned memory, replay of a captured step graph (cudaGraphExec_t), D2H copy of the result, and
+ * an event record.  Replaces the per-step sess.run(feed_dict=...) round trip (example.py:168-170).
+ * ---------------------------------------------------------------------------------- */
+int b200ps_host_step(void* dst0, const void* src0, uint64_t bytes0, void* dst1, const void* src1,
+                     uint64_t bytes1, void* graph_exec, void* result_host, const void* result_dev,
+                     uint64_t result_bytes, void* done_event, b200ps_stream_t stream);
+int b200ps_event_create(void** ev);
+int b200ps_event_synchronize(void* ev);
+int b200ps_event_destroy(void* ev);
+
+/* ------------------------------------------------------------------------------------
  * Host-side native helpers (no GPU needed).
  * ---------------------------------------------------------------------------------- */
 /* CRC-32C used by tfevents / tensor-bundle files (example.py:154, model_export.py:53). */

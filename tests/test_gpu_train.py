@@ -73,6 +73,25 @@ def test_resident_dataset_cursor_matches_copy_path(native_lib):
     assert a.read_loss() == b.read_loss() and a.global_step == b.global_step == 17
 
 
+def test_native_host_step_matches_python_path(native_lib):
+    """The one-call native e2e step (H2D + graph + D2H) gives the same losses as copy_/replay/item."""
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    xs, ys = _mnist_batches(6)
+    hx, hy = xs.cpu().pin_memory(), ys.cpu().pin_memory()
+    a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    la, lb, pending = [], [], []
+    for i in range(12):
+        pending.append(a.step_from_host_async(hx[i % 6], hy[i % 6]))     # native once the graph exists
+        if len(pending) > 2:
+            la.append(pending.pop(0).result())
+        b.step(xs[i % 6], ys[i % 6])
+        lb.append(b.read_loss())
+    la += [h.result() for h in pending]
+    assert hasattr(a, "_gexec") and la == lb and a.global_step == b.global_step == 12
+
+
 def test_sync_virtual_ranks_equal_big_batch(native_lib):
     """4 sync replicas x batch 100 == 1 worker x batch 400 (mean of means), up to fp32 rounding."""
     from b200ps.parallel.context import init_from_env
