@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "auc_hist", "push_sync_sgd", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words",
 ]
 
@@ -268,6 +268,15 @@ def push_sync_sgd(pads, masters, outs, grads, bounds, global_steps, *, world, ra
                                              max_shard_elems, d, d, replicas_to_aggregate, lr, max_ctas,
                                              ptr(cursor), cursor_step, cursor_wrap, int(broadcast),
                                              stream_ptr(stream)), "push_sync_sgd")
+
+
+def push_sync_ll(pads, masters, grads, bounds, global_steps, ll_grads, ll_params, *, world, rank_base, local_ranks=1,
+                 max_shard_elems, total_elems, lr, cursor=None, cursor_step=0, cursor_wrap=1, stream=None):
+    """Low-latency synchronous push for small fp32 groups (see include/b200ps.h)."""
+    check(native.load().b200ps_push_sync_ll(ptr(pads), ptr(masters), ptr(grads), ptr(bounds), ptr(global_steps),
+                                            ptr(ll_grads), ptr(ll_params), world, rank_base, local_ranks,
+                                            max_shard_elems, total_elems, lr, ptr(cursor), cursor_step, cursor_wrap,
+                                            stream_ptr(stream)), "push_sync_ll")
 
 
 def push_async(masters, grads, bounds, global_steps, *, world, rank_base, local_ranks=1, total_elems, lr,

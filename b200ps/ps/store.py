@@ -45,6 +45,8 @@ class _Group:
     t_masters: torch.Tensor
     t_outs: torch.Tensor
     t_grads: torch.Tensor
+    t_ll_grads: Optional[torch.Tensor] = None     # low-latency packet landing buffers (small fp32 groups)
+    t_ll_params: Optional[torch.Tensor] = None
 
 
 @dataclass
@@ -63,6 +65,8 @@ def _stream_id(name: str) -> int:
 
 
 class ParameterStore:
+    LL_MAX_ELEMS = 1 << 19     # fp32 groups up to 2 MB use the low-latency packet push
+
     def __init__(self, pool: SymmPool, placement: str = "flat_shard", seed: int = 1,
                  num_shards: Optional[int] = None):
         self.pool = pool
@@ -79,6 +83,8 @@ class ParameterStore:
         self.groups: Dict[str, _Group] = {}
         self.sparse: Dict[str, _SparseVar] = {}
         self._built = False
+        import os
+        self.use_ll = os.environ.get("B200PS_LL_PUSH", "1") != "0"
 
     # ------------------------------------------------------------------ registration
     def register(self, name: str, shape, *, group: str = "fp32", init: str = "zeros",
@@ -134,11 +140,18 @@ class ParameterStore:
             else:
                 master = None
                 master_ptrs = list(work.ptrs)
-            self.groups[gname] = _Group(
+            grp = _Group(
                 gname, dtype, specs, layout, work, grads, master,
                 torch.tensor(layout.bounds, dtype=torch.int64, device=dev),
                 ops.device_ptr_table(master_ptrs, dev), ops.device_ptr_table(work.ptrs, dev),
                 ops.device_ptr_table(grads.ptrs, dev))
+            if dtype == torch.float32 and self.world > 1 and layout.total <= self.LL_MAX_ELEMS:
+                llg = pool.alloc(f"{gname}.ll_grads", self.world * max(layout.max_shard, 8) * 8)
+                llp = pool.alloc(f"{gname}.ll_params", layout.total * 8)
+                grp.t_ll_grads = ops.device_ptr_table(llg.ptrs, dev)
+                grp.t_ll_params = ops.device_ptr_table(llp.ptrs, dev)
+                grp._ll_bufs = (llg, llp)
+            self.groups[gname] = grp
         for s in self._specs:
             if s.group != "sparse":
                 continue
@@ -365,6 +378,13 @@ class ParameterStore:
         for i, g in enumerate(gl):
             # one global_step per aggregated update: only the last group's launch counts it
             gs = self.t_gsteps if (count_step and i == len(gl) - 1) else None
+            if g.t_ll_grads is not None and R >= self.world and broadcast and self.use_ll:
+                ops.push_sync_ll(self.t_pads, g.t_masters, g.t_grads, g.bounds, gs, g.t_ll_grads, g.t_ll_params,
+                                 world=self.world, rank_base=base, local_ranks=n,
+                                 max_shard_elems=max(g.layout.max_shard, 8), total_elems=g.layout.total, lr=lr,
+                                 cursor=cursor if i == len(gl) - 1 else None, cursor_step=cursor_step,
+                                 cursor_wrap=cursor_wrap)
+                continue
             ops.push_sync_sgd(self.t_pads, g.t_masters, g.t_outs, g.t_grads, g.bounds, gs,
                               world=self.world, rank_base=base, local_ranks=n,
                               max_shard_elems=g.layout.max_shard, dtype=g.dtype,

@@ -229,6 +229,16 @@ int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* con
  * the consumers pull inside their GEMM (b200ps_gemm gather_src, K2). */
 /* cursor (device int32, may be NULL): after the update has landed, *cursor = (*cursor + cursor_step)
  * % cursor_wrap — the batch pointer of a resident dataset, advanced inside the captured step. */
+/* The same synchronous update for SMALL fp32 models, latency-optimised: values cross NVLink as
+ * 8-byte {value, epoch} packets that the receiver polls, so there is no flag round trip, no remote
+ * read round trip and no fence (2 one-way hops instead of ~5).  ll_grads[r]: world*max_shard_elems
+ * uint2 per rank; ll_params[r]: total_elems uint2 per rank (both symmetric, zero-initialised).
+ * All replicas are aggregated (replicas_to_aggregate == world). */
+int b200ps_push_sync_ll(uint32_t* const* pads, float* const* masters, const void* const* grads,
+                        const int64_t* bounds, uint64_t* const* global_steps, void* const* ll_grads,
+                        void* const* ll_params, int32_t world, int32_t rank_base, int32_t local_ranks,
+                        int64_t max_shard_elems, int64_t total_elems, float lr, int32_t* cursor,
+                        int32_t cursor_step, int32_t cursor_wrap, b200ps_stream_t stream);
 /* async (Hogwild): red.add of -lr*g into every owner's master; no barrier (example.py:118). */
 int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
                       uint64_t* const* global_steps, int32_t world, int32_t rank_base,

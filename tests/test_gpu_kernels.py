@@ -291,6 +291,36 @@ def test_push_sync_virtual_ranks(native_lib, dtype, world, R):
             assert torch.equal(v["work"][0], got.bfloat16())
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_push_sync_ll_matches_flag_protocol(native_lib, world):
+    """The low-latency packet push gives bit-identical parameters to the flag-based push."""
+    from b200ps import ops
+    res = []
+    for ll in (False, True):
+        v = _virtual_ranks(world, 79510, torch.float32)
+        llg = [torch.zeros(world * v["shard"], 2, device=DEV, dtype=torch.int32) for _ in range(world)]
+        llp = [torch.zeros(v["total"], 2, device=DEV, dtype=torch.int32) for _ in range(world)]
+        T = lambda ts: ops.device_ptr_table([t.data_ptr() for t in ts], DEV)
+        t_llg, t_llp = T(llg), T(llp)
+        for step in range(3):
+            for g in v["grads"]:
+                g.mul_(0.5).add_(0.01 * (step + 1))
+            if ll:
+                ops.push_sync_ll(v["t_pads"], v["t_masters"], v["t_grads"], v["bounds"], v["t_gsteps"], t_llg, t_llp,
+                                 world=world, rank_base=0, local_ranks=world, max_shard_elems=v["shard"],
+                                 total_elems=v["total"], lr=0.1)
+            else:
+                ops.push_sync_sgd(v["t_pads"], v["t_masters"], v["t_outs"], v["t_grads"], v["bounds"], v["t_gsteps"],
+                                  world=world, rank_base=0, local_ranks=world, max_shard_elems=v["shard"],
+                                  dtype=torch.float32, replicas_to_aggregate=world, lr=0.1)
+        torch.cuda.synchronize()
+        for r in range(1, world):
+            assert torch.equal(v["work"][r], v["work"][0])
+        assert all(gs.item() == 3 for gs in v["gsteps"])
+        res.append(v["work"][0].clone())
+    assert torch.equal(res[0], res[1])
+
+
 def test_push_sync_is_bitwise_reproducible(native_lib):
     from b200ps import ops
     outs = []
