@@ -50,7 +50,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          sgd_master: Optional[torch.Tensor] = None, sgd_lowp: Optional[torch.Tensor] = None,
          sgd_lr: float = 0.0, out_dtype: Optional[torch.dtype] = None, max_ctas: int = 0,
          a_row_offset: Optional[torch.Tensor] = None, a_rows: Optional[int] = None,
-         c_split_stride: int = 0, gather: Optional[dict] = None, stream=None) -> Optional[torch.Tensor]:
+         c_split_stride: int = 0, gather: Optional[dict] = None,
+         colsum_out: Optional[torch.Tensor] = None, stream=None) -> Optional[torch.Tensor]:
     """tcgen05/TMA GEMM  ``out[M,N] = epilogue(alpha * op(a) @ op(b))``.
 
     ``a`` is ``[M,K]`` (K-major) or, with ``a_mn_major``, stored ``[K,M]``;
@@ -115,6 +116,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     args.max_ctas = max_ctas
     args.a_row_offset, args.a_rows_total = ptr(a_row_offset), a_rows_total
     args.c_split_stride = c_split_stride
+    args.colsum_out = ptr(colsum_out)          # fused bias gradient (column sums of the stored tile)
     if gather is not None:
         # K2: pull fused into the GEMM — gather = dict(src_table, flags, world, rank[, ctas])
         args.gather_src, args.gather_flags = ptr(gather["src_table"]), ptr(gather["flags"])

@@ -40,6 +40,7 @@ class GemmArgs(C.Structure):
         ("a_row_offset", C.c_void_p), ("a_rows_total", C.c_int64), ("c_split_stride", C.c_int64),
         ("gather_src", C.c_void_p), ("gather_flags", C.c_void_p),
         ("gather_world", C.c_int32), ("gather_rank", C.c_int32), ("gather_ctas", C.c_int32),
+        ("colsum_out", C.c_void_p),
     ]
 
 

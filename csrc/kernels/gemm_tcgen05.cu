@@ -12,8 +12,9 @@
 // * epilogue warps read TMEM with tcgen05.ld and apply bias / sigmoid / sigmoid' / SGD
 //   directly from registers.
 //
-// Warp roles (256 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w3 idle,
-// w4..w7 epilogue (TMEM lane quarter = warp_idx % 4).
+// Warp roles (384 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w3 K2 gather,
+// w4..w11 epilogue (TMEM lane quarter = warp_idx % 4; the two warps of a quarter take alternate
+// 32-column chunks).
 #include "../common.h"
 #include "ptx.cuh"
 
@@ -22,7 +23,7 @@ namespace b200ps {
 constexpr int kBlockM = 128;
 constexpr int kRowBytes = 128;           // one swizzle-128B row: 64 bf16 or 32 tf32 along K (or MN)
 constexpr int kABytes = kBlockM * kRowBytes;  // 16 KiB per stage
-constexpr int kGemmThreads = 256;
+constexpr int kGemmThreads = 384;   // 4 role warps + 8 epilogue warps
 constexpr int kGatherChunk = 16384;   // bytes per bulk copy of the fused pull; ring of 2 per CTA
 
 struct GemmParams {
@@ -48,6 +49,7 @@ struct GemmParams {
   void* gather_dst;
   unsigned int* gather_flags;   // [num_k_blocks + 1]: panel-landed flags + CTA arrival counter
   int gather_world, gather_rank, gather_ctas, gather_kb_per_rank;
+  float* colsum;   // [N] += column sums of the stored tile (fused bias gradient), or null
 };
 
 __device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
@@ -90,7 +92,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full_bar[s], 1);
-      mbar_init(&tmem_empty_bar[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty_bar[s], 8);  // one arrive per epilogue warp
       mbar_init(&tmem_empty_bar[3 + s], 1);  // gather ring (K2)
     }
     fence_mbar_init();
@@ -267,6 +269,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
   } else if (warp_idx >= 4) {
     // ===================== epilogue =====================
     const int quarter = warp_idx & 3;
+    const int half = (warp_idx - 4) >> 2;     // which of the quarter's two warps: chunks half, half+2, ...
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = gemm_cta; t < total_tiles; t += gemm_ctas) {
@@ -281,11 +284,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N;
       const int n_valid = min(BLOCK_N, p.N - n_blk * BLOCK_N);
       const int n_chunks = (n_valid + 31) / 32;
-      for (int c = 0; c < n_chunks; ++c) {
+      if (half >= n_chunks) {   // nothing for this warp in a narrow tile: just hand the stage back
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+      }
+      for (int c = half; c < n_chunks; c += 2) {
         uint32_t r[32];
         tmem_ld_32x32(t_addr + c * 32, r);
         tmem_ld_wait();
-        if (c == n_chunks - 1) {
+        if (c + 2 >= n_chunks) {
           // all of this warp's TMEM reads for the tile are done: hand the stage back
           tcgen05_fence_before();
           __syncwarp();
@@ -336,6 +344,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
               }
             }
           }
+          if (p.colsum != nullptr) {   // bias gradient: column sums of the tile rows, one red per column per warp
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float cs = warp_sum(v[j]);
+              if (lane == 0 && j < ncols) red_add_f32_gpu(p.colsum + col0 + j, cs);
+            }
+          }
           if (p.c_is_f32) {
             float* cp = reinterpret_cast<float*>(p.C) + split * p.c_split_stride + row * p.ldc + col0;
             if (p.vec_ok && ncols == 32) {
@@ -384,13 +399,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
           __nv_bfloat16* lp =
               p.lowp ? reinterpret_cast<__nv_bfloat16*>(p.lowp) + row * p.ldc + col0 : nullptr;
           if (p.vec_ok && ncols == 32) {
+            // The master is touched exactly once per step: stream it (evict-first loads and stores)
+            // so that 0.67 GB of read-modify-write per layer does not push the GEMM operands out of L2.
+            float4 w[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) w[q] = __ldcs(reinterpret_cast<const float4*>(mp + q * 4));
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
-              float4 w = *reinterpret_cast<float4*>(mp + q * 4);
-              w.x -= p.lr * v[q * 4]; w.y -= p.lr * v[q * 4 + 1];
-              w.z -= p.lr * v[q * 4 + 2]; w.w -= p.lr * v[q * 4 + 3];
-              *reinterpret_cast<float4*>(mp + q * 4) = w;
-              v[q * 4] = w.x; v[q * 4 + 1] = w.y; v[q * 4 + 2] = w.z; v[q * 4 + 3] = w.w;
+              w[q].x -= p.lr * v[q * 4]; w[q].y -= p.lr * v[q * 4 + 1];
+              w[q].z -= p.lr * v[q * 4 + 2]; w[q].w -= p.lr * v[q * 4 + 3];
+              __stcs(reinterpret_cast<float4*>(mp + q * 4), w[q]);
+              v[q * 4] = w[q].x; v[q * 4 + 1] = w[q].y; v[q * 4 + 2] = w[q].z; v[q * 4 + 3] = w[q].w;
             }
             if (lp) {
 #pragma unroll
@@ -508,6 +527,12 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   p.lowp = a.sgd_lowp;
   p.a_row_offset = a.a_row_offset;
   p.c_split_stride = a.c_split_stride;
+  p.colsum = a.colsum_out;
+  if (a.colsum_out) {
+    B200PS_REQUIRE(a.epilogue == B200PS_EPI_STORE && p.split_k == 1 && a.M % kBlockM == 0,
+                   "gemm: colsum_out needs a plain store epilogue and M a multiple of %d (whole warps of valid rows)", kBlockM);
+    B200PS_CUDA_CHECK(cudaMemsetAsync(a.colsum_out, 0, sizeof(float) * a.N, stream));
+  }
   int gather_ctas = 0;
   if (a.gather_src) {
     const bool is_bf16 = !kTf32;   // (a runtime value keeps the tf32 instantiations free of dead-code warnings)

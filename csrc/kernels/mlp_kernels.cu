@@ -434,6 +434,100 @@ __global__ void __launch_bounds__(kCeThreads) softmax_ce_kernel(const T* __restr
   }
 }
 
+// bf16 rows with C a multiple of 8 and 16-byte aligned rows: every thread owns 8-element (16 B)
+// vectors, so a warp reads 512 contiguous bytes per instruction instead of 64.
+constexpr int kCeVecMax = 8;   // vectors per thread: C <= 256 * 8 * 8 = 16384
+__global__ void __launch_bounds__(kCeThreads) softmax_ce_bf16_vec_kernel(const __nv_bfloat16* __restrict__ logits,
+                                                                        const int* __restrict__ labels,
+                                                                        __nv_bfloat16* dlogits, float* loss_sum,
+                                                                        int* correct, int B, int C, long long ld,
+                                                                        float grad_scale, float loss_scale) {
+  __shared__ float s_val[kCeThreads / 32];
+  __shared__ int s_idx[kCeThreads / 32];
+  __shared__ float s_bcast[2];
+  const int row = blockIdx.x, tid = threadIdx.x;
+  const uint4* z = reinterpret_cast<const uint4*>(logits + (size_t)row * ld);
+  const int nvec = C >> 3;
+  float v[kCeVecMax][8];
+  float m = -INFINITY;
+  int arg = 0;
+#pragma unroll
+  for (int k = 0; k < kCeVecMax; ++k) {
+    const int i = tid + k * kCeThreads;
+    if (i < nvec) {
+      const uint4 u = z[i];
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        v[k][2 * e] = f.x; v[k][2 * e + 1] = f.y;
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (v[k][e] > m) { m = v[k][e]; arg = i * 8 + e; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  if ((tid & 31) == 0) { s_val[tid >> 5] = m; s_idx[tid >> 5] = arg; }
+  __syncthreads();
+  if (tid == 0) {
+    float bm = s_val[0]; int ba = s_idx[0];
+    for (int w = 1; w < kCeThreads / 32; ++w)
+      if (s_val[w] > bm || (s_val[w] == bm && s_idx[w] < ba)) { bm = s_val[w]; ba = s_idx[w]; }
+    s_bcast[0] = bm; s_idx[0] = ba;
+  }
+  __syncthreads();
+  m = s_bcast[0];
+  const int amax = s_idx[0];
+  __syncthreads();
+  float se = 0.f;
+#pragma unroll
+  for (int k = 0; k < kCeVecMax; ++k)
+    if (tid + k * kCeThreads < nvec)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { v[k][e] = __expf(v[k][e] - m); se += v[k][e]; }
+  se = warp_sum(se);
+  if ((tid & 31) == 0) s_val[tid >> 5] = se;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+    for (int w = 0; w < kCeThreads / 32; ++w) t += s_val[w];
+    s_bcast[1] = t;
+  }
+  __syncthreads();
+  se = s_bcast[1];
+  const int label = labels[row];
+  const float inv = 1.f / se;
+  if (dlogits) {
+    uint4* d = reinterpret_cast<uint4*>(dlogits + (size_t)row * ld);
+#pragma unroll
+    for (int k = 0; k < kCeVecMax; ++k) {
+      const int i = tid + k * kCeThreads;
+      if (i < nvec) {
+        uint4 u;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = i * 8 + 2 * e;
+          h[e] = __floats2bfloat162_rn((v[k][2 * e] * inv - (c == label ? 1.f : 0.f)) * grad_scale,
+                                       (v[k][2 * e + 1] * inv - (c + 1 == label ? 1.f : 0.f)) * grad_scale);
+        }
+        d[i] = u;
+      }
+    }
+  }
+  if (tid == 0) {
+    const float zl = __bfloat162float(logits[(size_t)row * ld + label]);
+    if (loss_sum) atomicAdd(loss_sum, (m + __logf(se) - zl) * loss_scale);
+    if (correct && amax == label) atomicAdd(correct, 1);
+  }
+}
+
 // ------------------------------------------------------------------------------------
 // colsum: out[n] (+)= scale * sum_m x[m,n]   — bias gradients.
 // ------------------------------------------------------------------------------------
@@ -686,6 +780,10 @@ extern "C" int b200ps_softmax_ce(const void* logits, const int32_t* labels, void
   if (dtype == B200PS_DT_F32)
     softmax_ce_kernel<float><<<B, kCeThreads, 0, s>>>((const float*)logits, labels, (float*)dlogits,
                                                      loss_sum, correct, B, C, ld, grad_scale, loss_scale);
+  else if (C % 8 == 0 && C <= kCeThreads * 8 * kCeVecMax && (ld * 2) % 16 == 0 &&
+           (reinterpret_cast<uintptr_t>(logits) & 15) == 0 && (!dlogits || (reinterpret_cast<uintptr_t>(dlogits) & 15) == 0))
+    softmax_ce_bf16_vec_kernel<<<B, kCeThreads, 0, s>>>((const __nv_bfloat16*)logits, labels, (__nv_bfloat16*)dlogits,
+                                                       loss_sum, correct, B, C, ld, grad_scale, loss_scale);
   else
     softmax_ce_kernel<__nv_bfloat16><<<B, kCeThreads, 0, s>>>((const __nv_bfloat16*)logits, labels,
                                                              (__nv_bfloat16*)dlogits, loss_sum, correct,

@@ -95,6 +95,9 @@ typedef struct b200ps_gemm_args {
   const void* const* gather_src;
   uint32_t* gather_flags;
   int32_t gather_world, gather_rank, gather_ctas;
+  /* Fused bias gradient: colsum_out[n] = sum_m C[m,n] of the values this call stores (fp32, overwritten;
+   * B200PS_EPI_STORE, M % 128 == 0).  NULL = off. */
+  float* colsum_out;
 } b200ps_gemm_args;
 
 int b200ps_gemm(const b200ps_gemm_args* args, b200ps_stream_t stream);

@@ -63,6 +63,20 @@ def test_gemm_dsigmoid_epilogue(native_lib):
     assert (out.float() - ref).abs().max().item() < 2e-2 * ref.abs().max().item() + 1e-3
 
 
+def test_gemm_fused_colsum(native_lib):
+    from b200ps import ops
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K = 512, 320, 256
+    dz = (torch.randn(M, K, device="cuda", generator=g) * 0.1).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
+    act = torch.rand(M, N, device="cuda", generator=g).bfloat16()
+    cs = torch.full((N,), 123.0, device="cuda")
+    out = ops.gemm(dz, w, dsigmoid_of=act, colsum_out=cs)
+    ref = (dz.float() @ w.float().t()) * act.float() * (1 - act.float())
+    assert (out.float() - ref).abs().max().item() < 2e-2 * ref.abs().max().item() + 1e-3
+    assert torch.allclose(cs, ref.sum(0), atol=2e-2 * ref.abs().sum(0).max().item())
+
+
 def test_gemm_splitk_atomic(native_lib):
     from b200ps import ops
     g = torch.Generator(device="cuda").manual_seed(2)
