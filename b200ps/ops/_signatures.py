@@ -21,7 +21,7 @@ SIGNATURES = {
     "b200ps_auc_hist": [vp, vp, i32, vp, i32, vp, vp, vp],
     "b200ps_push_sync_sgd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i32, i32, i32, f32, i32, vp, i32, i32, i32, vp],
     "b200ps_push_sync_ll": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64, f32, vp, i32, i32, vp],
-    "b200ps_push_async": [vp, vp, vp, vp, i32, i32, i32, i64, f32, i32, vp],
+    "b200ps_push_async": [vp, vp, vp, vp, i32, i32, i32, i64, f32, i32, vp, i32, i32, vp],
     "b200ps_pull": [vp, vp, vp, i32, i32, i32, i64, i32, i32, i32, vp],
     "b200ps_barrier": [vp, i32, i32, i32, vp],
     "b200ps_symm_alloc": [u64, C.POINTER(vp), vp],

@@ -282,10 +282,10 @@ def push_sync_ll(pads, masters, grads, bounds, global_steps, ll_grads, ll_params
 
 
 def push_async(masters, grads, bounds, global_steps, *, world, rank_base, local_ranks=1, total_elems, lr,
-               max_ctas=0, stream=None):
+               max_ctas=0, cursor=None, cursor_step=0, cursor_wrap=1, stream=None):
     check(native.load().b200ps_push_async(ptr(masters), ptr(grads), ptr(bounds), ptr(global_steps), world,
-                                          rank_base, local_ranks, total_elems, lr, max_ctas,
-                                          stream_ptr(stream)), "push_async")
+                                          rank_base, local_ranks, total_elems, lr, max_ctas, ptr(cursor),
+                                          cursor_step, cursor_wrap, stream_ptr(stream)), "push_async")
 
 
 def pull(masters, outs, bounds, *, world, rank_base, local_ranks=1, max_shard_elems, dtype,

@@ -23,8 +23,8 @@ class AsyncSGD:
         """Refresh the worker's view of peer-owned slices (stale reads are fine)."""
         store.pull()
 
-    def apply(self, store, rank: Optional[int] = None) -> None:
-        store.push_async(self.learning_rate, rank=rank)
+    def apply(self, store, rank: Optional[int] = None, **cursor_kw) -> None:
+        store.push_async(self.learning_rate, rank=rank, **cursor_kw)
 
 
 class SyncReplicasSGD:

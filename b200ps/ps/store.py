@@ -392,7 +392,8 @@ class ParameterStore:
                               cursor=cursor if i == len(gl) - 1 else None, cursor_step=cursor_step,
                               cursor_wrap=cursor_wrap, broadcast=broadcast)
 
-    def push_async(self, lr: float, rank: Optional[int] = None, groups=None, count_step: bool = True) -> None:
+    def push_async(self, lr: float, rank: Optional[int] = None, groups=None, count_step: bool = True,
+                   cursor=None, cursor_step: int = 0, cursor_wrap: int = 1) -> None:
         """Hogwild push of ONE worker's gradients (fp32 groups only)."""
         gl = list(self._iter_groups(groups))
         r = self.pool.local_ranks[0] if rank is None else rank
@@ -401,7 +402,9 @@ class ParameterStore:
                 raise NotImplementedError("async push is defined for fp32 groups")
             gs = self.t_gsteps if (count_step and i == len(gl) - 1) else None
             ops.push_async(g.t_masters, g.t_grads, g.bounds, gs, world=self.world, rank_base=r,
-                           total_elems=g.layout.total, lr=lr)
+                           total_elems=g.layout.total, lr=lr,
+                           cursor=cursor if i == len(gl) - 1 else None, cursor_step=cursor_step,
+                           cursor_wrap=cursor_wrap)
 
     def gather_info(self, name: str, rank: Optional[int] = None, ctas: int = 0) -> dict:
         """Arguments of the fused pull (``ops.gemm(..., gather=...)``) for a [K,N] bf16 variable that

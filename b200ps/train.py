@@ -168,8 +168,8 @@ class MLPTrainer(_TrainerBase):
     #    walks it through a device-side cursor — no per-step input copies, no host work but the
     #    graph launch (the on-device replacement of mnist.train.next_batch, example.py:165)
     def attach_dataset(self, data: torch.Tensor, labels: torch.Tensor, steps_per_graph: int = 8) -> None:
-        if self.mode != "sync" or len(self.local_ranks) != 1:
-            raise NotImplementedError("resident datasets are implemented for the sync trainer, one rank per process")
+        if len(self.local_ranks) != 1:
+            raise NotImplementedError("resident datasets need one rank per process")
         n = (data.shape[0] // self.batch_size) * self.batch_size
         if n == 0 or labels.dtype != torch.int32 or labels.shape[0] < n:
             raise ValueError("attach_dataset: need >= batch_size rows and int32 labels")
@@ -184,6 +184,7 @@ class MLPTrainer(_TrainerBase):
     def _body_resident(self):
         data, labels, n = self._ds
         r = self.local_ranks[0]
+        self.opt.prepare(self.store)             # async: refresh the peer-owned slices (no-op for sync)
         loss, correct = self.model.forward_backward(self.store, data, labels, rank=r, row_offset=self._cursor,
                                                     batch=self.batch_size)
         self._losses[r], self._corrects[r] = loss, correct

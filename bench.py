@@ -163,7 +163,7 @@ def bench_mnist(ctx, args, sampler, mode):
         tr.step(xs[2 + i], ys[2 + i])
     loss0 = tr.read_loss()
 
-    resident = mode == "sync" and not args.no_resident
+    resident = not args.no_resident
     if resident:
         # the epoch stays on the device; each captured step reads its batch through a device cursor
         tr.attach_dataset(data, labels, steps_per_graph=args.steps_per_graph)

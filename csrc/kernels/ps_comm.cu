@@ -288,6 +288,8 @@ __global__ void __launch_bounds__(256) push_sync_ll_kernel(const CommArgs a, uin
 
 __global__ void __launch_bounds__(256) push_async_kernel(const CommArgs a, long long n) {
   const int rank = a.rank_base + blockIdx.y;
+  pdl_wait();      // the gradients come from the kernels just before us
+  pdl_trigger();
   const float* g = reinterpret_cast<const float*>(a.grads[rank]);
   const float nlr = -a.lr;
   for (int r = 0; r < a.world; ++r) {
@@ -301,13 +303,18 @@ __global__ void __launch_bounds__(256) push_async_kernel(const CommArgs a, long 
       red_add_v4f32_sys(master + i, make_float4(nlr * gv.x, nlr * gv.y, nlr * gv.z, nlr * gv.w));
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0 && a.global_steps)
-    atomicAdd_system(a.global_steps[0], 1ull);  // the chief's shard holds global_step
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (a.global_steps) atomicAdd_system(a.global_steps[0], 1ull);  // the chief's shard holds global_step
+    // (safe to advance here: every kernel that reads the cursor in this step has already completed)
+    if (a.cursor) *a.cursor = (*a.cursor + a.cursor_step) % a.cursor_wrap;
+  }
 }
 
 template <typename O>
 __global__ void __launch_bounds__(256) pull_kernel(const CommArgs a, int include_self) {
   const int rank = a.rank_base + blockIdx.y;
+  pdl_wait();
+  pdl_trigger();
   O* dst = reinterpret_cast<O*>(a.outs[rank]);
   for (int rr = 0; rr < a.world; ++rr) {
     const int r = (rank + rr) % a.world;  // start with the local slice, then walk the peers
@@ -415,15 +422,17 @@ extern "C" int b200ps_push_sync_ll(uint32_t* const* pads, float* const* masters,
 extern "C" int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
                                  uint64_t* const* global_steps, int32_t world, int32_t rank_base,
                                  int32_t local_ranks, int64_t total_elems, float lr, int32_t max_ctas,
+                                 int32_t* cursor, int32_t cursor_step, int32_t cursor_wrap,
                                  b200ps_stream_t stream) {
   B200PS_REQUIRE(world >= 1 && world <= kMaxWorld, "push_async: world=%d out of range", world);
   CommArgs a{};
   a.masters = masters; a.grads = grads; a.bounds = reinterpret_cast<const long long*>(bounds);
   a.global_steps = reinterpret_cast<unsigned long long* const*>(global_steps);
   a.world = world; a.rank_base = rank_base; a.lr = lr;
+  a.cursor = cursor; a.cursor_step = cursor_step; a.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
   const int want = max_ctas > 0 ? max_ctas : sm_count();
   dim3 grid(comm_grid(total_elems / std::max(world, 1), 1, want), local_ranks);
-  push_async_kernel<<<grid, 256, 0, as_stream(stream)>>>(a, total_elems);
+  B200PS_CUDA_CHECK(launch_pdl(push_async_kernel, grid, dim3(256), 0, as_stream(stream), a, (long long)total_elems));
   B200PS_LAUNCH_CHECK();
   return 0;
 }
@@ -438,8 +447,10 @@ extern "C" int b200ps_pull(float* const* masters, void* const* outs, const int64
   a.world = world; a.rank_base = rank_base;
   const int want = max_ctas > 0 ? max_ctas : sm_count();
   dim3 grid(comm_grid(max_shard_elems, 1, want), local_ranks);
-  if (out_dtype == B200PS_DT_F32) pull_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(a, include_self);
-  else pull_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(a, include_self);
+  if (out_dtype == B200PS_DT_F32)
+    B200PS_CUDA_CHECK(launch_pdl(pull_kernel<float>, grid, dim3(256), 0, as_stream(stream), a, (int)include_self));
+  else
+    B200PS_CUDA_CHECK(launch_pdl(pull_kernel<__nv_bfloat16>, grid, dim3(256), 0, as_stream(stream), a, (int)include_self));
   B200PS_LAUNCH_CHECK();
   return 0;
 }

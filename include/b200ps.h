@@ -246,7 +246,7 @@ int b200ps_push_sync_ll(uint32_t* const* pads, float* const* masters, const void
 int b200ps_push_async(float* const* masters, const void* const* grads, const int64_t* bounds,
                       uint64_t* const* global_steps, int32_t world, int32_t rank_base,
                       int32_t local_ranks, int64_t total_elems, float lr, int32_t max_ctas,
-                      b200ps_stream_t stream);
+                      int32_t* cursor, int32_t cursor_step, int32_t cursor_wrap, b200ps_stream_t stream);
 /* pull: copy peer-owned slices of the masters into this rank's working copy. */
 int b200ps_pull(float* const* masters, void* const* outs, const int64_t* bounds, int32_t world,
                 int32_t rank_base, int32_t local_ranks, int64_t max_shard_elems,

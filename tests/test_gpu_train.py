@@ -73,6 +73,25 @@ def test_resident_dataset_cursor_matches_copy_path(native_lib):
     assert a.read_loss() == b.read_loss() and a.global_step == b.global_step == 17
 
 
+def test_async_resident_cursor_matches_copy_path(native_lib):
+    """Async mode: the cursor advanced by the push_async kernel walks the same batches as the copy path."""
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    xs, ys = _mnist_batches(5)
+    a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="async", use_graph=True)
+    b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="async", use_graph=True)
+    a.attach_dataset(xs.reshape(-1, 784), ys.reshape(-1))
+    a.run_resident(13)
+    for i in range(13):
+        b.step(xs[i % 5], ys[i % 5])
+    torch.cuda.synchronize()
+    assert a._cursor.item() == (13 * 100) % 500
+    sa, sb = a.store.state_dict(), b.store.state_dict()
+    for name in a.model.names():
+        assert torch.allclose(sa[name], sb[name], rtol=0, atol=1e-6), name
+    assert a.global_step == b.global_step == 13
+
+
 def test_native_host_step_matches_python_path(native_lib):
     """The one-call native e2e step (H2D + graph + D2H) gives the same losses as copy_/replay/item."""
     from b200ps.parallel.context import init_from_env
