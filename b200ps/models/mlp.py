@@ -87,15 +87,18 @@ class SigmoidMLP:
     # -- GPU path -------------------------------------------------------------------------
     def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
                          global_batch: Optional[int] = None, row_offset: Optional[torch.Tensor] = None,
-                         batch: Optional[int] = None):
+                         batch: Optional[int] = None, stats_out=None):
         """Forward + backward of one worker's batch; gradients land in ``store.grad(...)``.
         Returns the (device) loss tensor and the correct-count tensor (both overwritten per step).
+        ``stats_out=(loss, correct)`` redirects the two words, e.g. into pinned mapped host memory.
 
         With ``row_offset`` (int32 device scalar) ``x``/``labels`` are a whole resident dataset and
         the batch is rows ``[*row_offset, *row_offset + batch)`` — read on the device, no copies."""
         B = x.shape[0] if row_offset is None else batch
         bufs = self._buffers(B, x.device, 0 if rank is None else rank)
         z2, dz2, loss, correct = bufs["z2"], bufs["dz2"], bufs["loss"], bufs["correct"]
+        if stats_out is not None:
+            loss, correct = stats_out
         w1 = store.var(self.W1, rank)
         off = dict(a_row_offset=row_offset, a_rows=B) if row_offset is not None else {}
         # split-K over CTAs, each writing its own slab of z2; the head kernel sums the slabs in a

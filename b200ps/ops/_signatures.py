@@ -31,6 +31,13 @@ SIGNATURES = {
     "b200ps_device_count": [C.POINTER(i32)],
     "b200ps_can_access_peer": [i32, i32, C.POINTER(i32)],
     "b200ps_host_step": [vp, vp, u64, vp, vp, u64, vp, vp, vp, u64, vp, vp],
+    "b200ps_feeder_create": [C.POINTER(vp), i32, u64, u64, u64],
+    "b200ps_feeder_result_ptr": [vp, i32, C.POINTER(vp)],
+    "b200ps_feeder_bind": [vp, i32, vp, vp, vp],
+    "b200ps_feeder_submit": [vp, vp, vp, vp, C.POINTER(i64)],
+    "b200ps_feeder_wait": [vp, i64, vp],
+    "b200ps_feeder_stats": [vp, C.POINTER(C.c_double), C.POINTER(i64)],
+    "b200ps_feeder_destroy": [vp],
     "b200ps_event_create": [C.POINTER(vp)],
     "b200ps_event_synchronize": [vp],
     "b200ps_event_destroy": [vp],

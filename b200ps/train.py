@@ -112,15 +112,6 @@ class _TrainerBase:
         self.ctx.close()
 
 
-class _NativeLossHandle:
-    def __init__(self, view, event, lib):
-        self._view, self._event, self._lib = view, event, lib
-
-    def result(self) -> float:
-        self._lib.b200ps_event_synchronize(self._event)
-        return float(self._view[0])
-
-
 class _LossHandle:
     """Result of ``step_from_host_async``: ``result()`` blocks until that step's loss is on the host."""
 
@@ -232,31 +223,90 @@ class MLPTrainer(_TrainerBase):
 
     def step_from_host_async(self, x_pinned: torch.Tensor, labels_pinned: torch.Tensor):
         """Queue one end-to-end step and return a handle whose ``result()`` is that step's loss.
-        Once the step graph exists the whole host side (2 H2D copies, graph launch, loss D2H copy,
-        completion event) is ONE native call (``b200ps_host_step``)."""
-        g = self._step.graph
-        if g is None or len(self.local_ranks) != 1:
+        Once the trainer is warm the whole host side is ONE native call into the ``HostFeeder``
+        (copy-stream H2D into a staging slot, event hand-off, graph launch; the loss is written by
+        the step kernel into pinned host memory)."""
+        if not self._step.use_graph or self._step.calls < self._step.warmup or len(self.local_ranks) != 1:
             return super().step_from_host_async(x_pinned, labels_pinned)
-        import ctypes as C
-        from .ops import native
-        lib = native.load()
-        if not hasattr(self, "_nring"):
-            self._nring, self._nring_i = [], 0
-            for _ in range(4):
-                ev = C.c_void_p()
-                native.check(lib.b200ps_event_create(C.byref(ev)), "event_create")
-                slot = torch.zeros(1).pin_memory()
-                self._nring.append((slot, slot.numpy(), ev))
-            self._gexec = g.raw_cuda_graph_exec()
-        r = self.local_ranks[0]
-        slot, view, ev = self._nring[self._nring_i % 4]
-        self._nring_i += 1
-        x, y, loss = self.x[r], self.labels[r], self._losses[r]
-        native.check(lib.b200ps_host_step(
-            x.data_ptr(), x_pinned.data_ptr(), x.numel() * 4, y.data_ptr(), labels_pinned.data_ptr(), y.numel() * 4,
-            self._gexec, slot.data_ptr(), loss.data_ptr(), 4, ev, native.stream_ptr()), "host_step")
+        if getattr(self, "_feeder1", None) is None:
+            self._feeder1 = self.host_feeder(steps_per_call=1, slots=8)
         self.local_step += 1
-        return _NativeLossHandle(view, ev, lib)
+        return self._feeder1.submit(x_pinned, labels_pinned)
+
+    def host_feeder(self, steps_per_call: int = 1, slots: int = 4):
+        """A ``HostFeeder`` whose unit is ``steps_per_call`` consecutive training steps on a pinned host
+        chunk ``x[steps_per_call*B, in_dim]``, ``labels[steps_per_call*B]``.  ``submit(x, labels).result()``
+        is the loss of the step (a float) or the ``steps_per_call`` losses (numpy array).  The trainer
+        must have been warmed up (two eager ``step`` calls) so that nothing allocates during capture."""
+        from .runtime import HostFeeder
+        if len(self.local_ranks) != 1:
+            raise NotImplementedError("host_feeder needs one rank per process")
+        if self._step.use_graph and self._step.calls < self._step.warmup:
+            raise RuntimeError("host_feeder: run %d eager step() calls first (warm-up)" % self._step.warmup)
+        K, B, r, dev = max(1, steps_per_call), self.batch_size, self.local_ranks[0], self.device
+        trainer = self
+
+        def make_slot(slot, result):
+            x = torch.zeros(K * B, self.model.in_dim, device=dev)
+            y = torch.zeros(K * B, device=dev, dtype=torch.int32)
+            words = result.view(K, 2)
+            correct_words = words.view(torch.int32)
+
+            def body():
+                for i in range(K):
+                    trainer.opt.prepare(trainer.store)
+                    trainer.model.forward_backward(trainer.store, x[i * B:(i + 1) * B], y[i * B:(i + 1) * B], rank=r,
+                                                   stats_out=(words[i, 0:1], correct_words[i, 1:2]))
+                    trainer.opt.apply(trainer.store)
+            return _capture(body, dev), (x, y)
+
+        if K == 1:
+            decode = lambda out: float(out[0])                                  # noqa: E731
+        else:
+            decode = lambda out: out.reshape(K, 2)[:, 0].copy()                 # noqa: E731
+        f = HostFeeder(make_slot, (K * B * self.model.in_dim * 4, K * B * 4), 2 * K, slots=slots, decode=decode)
+        f.steps_per_call = K
+        return f
+
+    def fit_from_host(self, x_pinned: torch.Tensor, labels_pinned: torch.Tensor, steps_per_call: int = 8,
+                      on_loss=None) -> int:
+        """Train once over a pinned host dataset ``x[N, in_dim]``, ``labels[N]`` (the ``for i in
+        range(batch_count): next_batch(); sess.run(...)`` epoch of example.py:163-170) through a
+        chunked feeder: ``steps_per_call`` batches per H2D copy / graph launch, every step's loss
+        delivered to ``on_loss(step_index, loss)``.  Returns the number of steps taken."""
+        K, B = max(1, steps_per_call), self.batch_size
+        key = "_feederK%d" % K
+        if getattr(self, key, None) is None:
+            setattr(self, key, self.host_feeder(steps_per_call=K))
+        f = getattr(self, key)
+        n_chunks = x_pinned.shape[0] // (K * B)
+        pending, done = [], 0
+        for c in range(n_chunks):
+            pending.append(f.submit(x_pinned[c * K * B:(c + 1) * K * B], labels_pinned[c * K * B:(c + 1) * K * B]))
+            if len(pending) > f.slots - 2:
+                losses = pending.pop(0).result()
+                if on_loss is not None:
+                    for v in (losses if K > 1 else [losses]):
+                        on_loss(done, float(v)); done += 1
+                else:
+                    done += K
+        for t in pending:
+            losses = t.result()
+            if on_loss is not None:
+                for v in (losses if K > 1 else [losses]):
+                    on_loss(done, float(v)); done += 1
+            else:
+                done += K
+        self.local_step += n_chunks * K
+        # the remainder (fewer than K batches) goes through the per-step feeder
+        rest = x_pinned.shape[0] // B - n_chunks * K
+        for i in range(rest):
+            lo = (n_chunks * K + i) * B
+            v = self.step_from_host(x_pinned[lo:lo + B], labels_pinned[lo:lo + B])
+            if on_loss is not None:
+                on_loss(done, v)
+            done += 1
+        return done
 
     def evaluate(self, x: torch.Tensor, labels: torch.Tensor):
         return self.model.evaluate(self.store, x, labels, rank=self.local_ranks[0])

@@ -273,6 +273,22 @@ int b200ps_can_access_peer(int32_t dev, int32_t peer, int32_t* ok);
 int b200ps_host_step(void* dst0, const void* src0, uint64_t bytes0, void* dst1, const void* src1,
                      uint64_t bytes1, void* graph_exec, void* result_host, const void* result_dev,
                      uint64_t result_bytes, void* done_event, b200ps_stream_t stream);
+
+/* HostFeeder: a ring of `slots` (staging buffers, step graph, events).  submit() copies two pinned
+ * host buffers into the next slot on a private copy stream and replays the slot's graph on `stream`
+ * once they have landed; the copy of unit t+1 overlaps the kernels of unit t.  The graphs write their
+ * results (loss words) directly into the slot's pinned, device-mapped result block
+ * (b200ps_feeder_result_ptr), so no D2H copy is queued.  wait() blocks on one unit only.  Only the
+ * last `slots` tickets can be waited for.  Not thread-safe: one submitting thread per feeder. */
+int b200ps_feeder_create(void** feeder, int32_t slots, uint64_t bytes0, uint64_t bytes1, uint64_t result_bytes);
+int b200ps_feeder_result_ptr(void* feeder, int32_t slot, void** ptr);
+int b200ps_feeder_bind(void* feeder, int32_t slot, void* graph_exec, void* dst0, void* dst1);
+int b200ps_feeder_submit(void* feeder, const void* src0, const void* src1, b200ps_stream_t stream,
+                         int64_t* ticket);
+int b200ps_feeder_wait(void* feeder, int64_t ticket, void* out /* result_bytes, may be NULL */);
+int b200ps_feeder_stats(void* feeder, double* phase_ns /* 5: wait, copies, hand-off, launch, record */,
+                        int64_t* submitted);
+int b200ps_feeder_destroy(void* feeder);
 int b200ps_event_create(void** ev);
 int b200ps_event_synchronize(void* ev);
 int b200ps_event_destroy(void* ev);

@@ -108,7 +108,40 @@ def test_native_host_step_matches_python_path(native_lib):
         b.step(xs[i % 6], ys[i % 6])
         lb.append(b.read_loss())
     la += [h.result() for h in pending]
-    assert hasattr(a, "_gexec") and la == lb and a.global_step == b.global_step == 12
+    assert a._feeder1 is not None and la == lb and a.global_step == b.global_step == 12
+
+
+def test_chunked_host_feeder_and_fit_from_host(native_lib):
+    """K steps per H2D copy / graph launch: same parameters and per-step losses as stepping one by one;
+    tickets older than the ring are refused instead of returning another unit's losses."""
+    import pytest as _pytest
+    from b200ps.ops.native import NativeError
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    n = 2 + 3 * 4 + 1                                   # warm-up + three chunks of 4 + a remainder batch
+    xs, ys = _mnist_batches(n)
+    hx, hy = xs.cpu().pin_memory(), ys.cpu().pin_memory()
+    a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    lb = []
+    for i in range(n):
+        b.step(xs[i], ys[i]); lb.append(b.read_loss())
+    for i in range(2):
+        a.step(xs[i], ys[i])
+    la = []
+    steps = a.fit_from_host(hx[2:].reshape(-1, 784), hy[2:].reshape(-1), steps_per_call=4,
+                            on_loss=lambda i, v: la.append(v))
+    torch.cuda.synchronize()
+    assert steps == n - 2 and la == lb[2:] and a.global_step == b.global_step == n
+    sa, sb = a.store.state_dict(), b.store.state_dict()
+    for name in a.model.names():
+        assert torch.equal(sa[name], sb[name]), name
+    f = a.host_feeder(steps_per_call=1, slots=2)
+    tickets = [f.submit(hx[i], hy[i]) for i in range(3)]
+    assert tickets[2].result() == tickets[2].result()
+    with _pytest.raises(NativeError):
+        tickets[0].result()                              # slot reused by ticket 2
+    f.close()
 
 
 def test_sync_virtual_ranks_equal_big_batch(native_lib):
