@@ -35,6 +35,7 @@ from ..io import log
 from ..io.log import debug, error, info  # noqa: F401  (the reference's helpers, lr2.py:38-48)
 from ..metrics.auc import StreamingAUC
 from ..models.sparse_lr import SparseLR, sparse_lr_reference
+from ..models.wide_deep import SparseWideDeep, wide_deep_reference
 
 FLAGS = flags.FLAGS
 flags.define_role_flags(job_name_default="worker")
@@ -55,6 +56,10 @@ flags.DEFINE_integer("train_queue_capacity", 2000, "train queue capacity")
 flags.DEFINE_integer("test_queue_capacity", 2000, "test queue capacity")
 flags.DEFINE_string("train_file_list", "", "file holding one train path per line (lr2_debug.py:30)")
 flags.DEFINE_string("test_file_list", "", "file holding one test path per line (lr2_debug.py:31)")
+flags.DEFINE_integer("deep_dim", 0, "0 = plain LR (lr2.py); 128/256/512 adds the [features,dim] embedding + [dim,1] "
+                     "deep part sketched at lr2_debug.py:423-428")
+flags.DEFINE_float("init_stddev", 0.0, "stddev of the weight initialiser; 0 = the script's default (1.0 for LR as in "
+                   "lr2.py:384, 0.01 with --deep_dim as in lr2_debug.py:288-289)")
 flags.DEFINE_integer("synthetic_rows", 4000, "rows per synthetic file when --train/--test is 'synthetic'")
 
 
@@ -92,6 +97,45 @@ class _CpuRunner:
 
     def eval_batch(self, samples):
         loss, pred, _, _, _, labels = self._fwd(samples, False)
+        return float(loss), pred.float(), labels
+
+
+class _CpuWideDeepRunner:
+    """gloo path of the wide & deep extension: unique ids up, W/E rows down, w2 whole, four pushes."""
+
+    def __init__(self, store, model, lr, sync, replicas):
+        self.store, self.model, self.lr, self.sync, self.replicas = store, model, lr, sync, replicas
+        self._all = torch.arange(model.dim)
+
+    def _fwd(self, samples, train):
+        m = self.model
+        row_ptr, fid, fval, labels = (torch.from_numpy(a) for a in Sample.format_samples_csr(samples))
+        uniq, inv = torch.unique(fid, return_inverse=True)
+        W = self.store.sparse_pull(m.W, uniq) if m.wide else None
+        E = self.store.sparse_pull(m.E, uniq)
+        w2 = self.store.sparse_pull(m.W2, self._all)
+        self.store.pull()
+        b = self.store.var(m.Bn)
+        loss, pred, grads = wide_deep_reference(W, E, w2, b, row_ptr, inv, fval, labels, train=train)
+        return loss, pred, grads, uniq, labels
+
+    def train_step(self, samples):
+        m = self.model
+        loss, pred, g, uniq, _ = self._fwd(samples, True)
+        lr = self.lr * (1.0 / self.replicas if self.sync else 1.0)
+        if m.wide:
+            self.store.sparse_push(m.W, uniq, g["W"].float(), lr)
+        self.store.sparse_push(m.E, uniq, g["E"].float(), lr)
+        self.store.sparse_push(m.W2, self._all, g["w2"].float(), lr)
+        self.store.grad(m.Bn).fill_(float(g["b"]))
+        if self.sync:
+            self.store.push_sync(self.lr, self.replicas)
+        else:
+            self.store.push_async(self.lr)
+        return float(loss)
+
+    def eval_batch(self, samples):
+        loss, pred, _, _, labels = self._fwd(samples, False)
         return float(loss), pred.float(), labels
 
 
@@ -164,13 +208,17 @@ def main(argv=None) -> int:
 
     info("build graph")
     gpu = server.backend == "nvlink"
-    model = SparseLR(FLAGS.features)
+    deep = FLAGS.deep_dim > 0
+    if deep:
+        model = SparseWideDeep(FLAGS.features, dim=FLAGS.deep_dim, stddev=FLAGS.init_stddev or 0.01)
+    else:
+        model = SparseLR(FLAGS.features, stddev=FLAGS.init_stddev or 1.0)
     sync = bool(FLAGS.sync)
     if gpu:
         from ..train import SparseLRTrainer
         ctx = server.nvlink_context()
         trainer = SparseLRTrainer(ctx, FLAGS.features, lr=learning_rate, mode="sync" if sync else "async",
-                                  placement=FLAGS.placement, seed=FLAGS.seed, use_graph=False)
+                                  placement=FLAGS.placement, seed=FLAGS.seed, use_graph=False, model=model)
         store, runner = trainer.store, _GpuRunner(trainer)
     else:
         from ..ps.gloo_store import GlooParameterStore
@@ -178,7 +226,8 @@ def main(argv=None) -> int:
         store = GlooParameterStore(server, placement=FLAGS.placement, seed=FLAGS.seed)
         model.register(store)
         store.build()
-        runner = _CpuRunner(store, model, learning_rate, sync, FLAGS.replicas_to_aggregate or num_workers)
+        runner = (_CpuWideDeepRunner if deep else _CpuRunner)(store, model, learning_rate, sync,
+                                                              FLAGS.replicas_to_aggregate or num_workers)
     supervisor = Supervisor(is_chief=is_chief, store=store, ctx=ctx, logdir=FLAGS.logdir or None,
                             save_model_secs=FLAGS.save_secs, ready_timeout_secs=FLAGS.barrier_timeout_secs)
 

@@ -175,8 +175,9 @@ class _PsService:
             elif op == OP_INIT:            # chief pushes initial values of this ps's slice
                 self.slices[a0] = self._recv(a1, src)
                 self.initialized = bool(a2) or self.initialized
-            elif op == OP_SPARSE_INIT:     # a0 = var id, a1 = rows held here
-                self.sparse[a0] = self._recv(a1, src)
+            elif op == OP_SPARSE_INIT:     # a0 = var id, a1 = rows held here, a2 = row width (0 = 1)
+                dim = max(a2, 1)
+                self.sparse[a0] = self._recv(a1 * dim, src).view(a1, dim)
             elif op == OP_SET_STEP:
                 self.global_step = a0
                 self.initialized = True
@@ -222,10 +223,11 @@ class _PsService:
                     self._release_tokens()
             elif op == OP_SPARSE_PULL:     # a0 = var id, a1 = number of ids (local row indices)
                 ids = self._recv(a1, src, torch.int64)
-                self._send(self.sparse[a0][ids], src)
+                self._send(self.sparse[a0][ids].reshape(-1), src)
             elif op == OP_SPARSE_PUSH:     # a0 = var id, a1 = n ids, a2 = lr bits
                 ids = self._recv(a1, src, torch.int64)
-                vals = self._recv(a1, src)
+                dim = self.sparse[a0].shape[1]
+                vals = self._recv(a1 * dim, src).view(a1, dim)
                 self.sparse[a0].index_add_(0, ids, vals, alpha=-i2f(a2))   # ScatterSub (duplicates summed)
             elif op == OP_GET_STEP:
                 self._send(torch.tensor([self.global_step], dtype=torch.int64), src)

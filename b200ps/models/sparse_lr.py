@@ -41,14 +41,14 @@ def sparse_lr_reference(W: torch.Tensor, b: torch.Tensor, row_ptr, fid, fval, la
 class SparseLR:
     W, Bn = "weights/Variable", "bias/Variable"
 
-    def __init__(self, features: int):
-        self.features = int(features)
+    def __init__(self, features: int, stddev: float = 1.0):
+        self.features, self.stddev = int(features), float(stddev)
         self._bufs: Dict[int, dict] = {}
 
     def register(self, store) -> None:
         if hasattr(store, "note_untracked_variable"):
             store.note_untracked_variable("global_step")
-        store.register(self.W, (self.features, 1), group="sparse", init="normal", stddev=1.0)
+        store.register(self.W, (self.features, 1), group="sparse", init="normal", stddev=self.stddev)
         store.register(self.Bn, (1,), group="fp32", init="zeros")
 
     def _buffers(self, B: int, device, key: int) -> dict:

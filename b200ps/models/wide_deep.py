@@ -1,0 +1,123 @@
+"""Sparse wide & deep logistic model (N5) — the extension sketched at lr2_debug.py:423-428.
+
+The reference's scratch trainer adds, commented out, "two more layers" to the sparse LR::
+
+    py_x  = embedding_lookup_sparse(W[F,1], ids, vals, 'sum')                      # wide (lr2.py:390)
+    py_x += embedding_lookup_sparse(deep_w1[F,128], ids, vals, 'sum') @ deep_w2[128,1]
+
+with ``init_weights(stddev=0.01)`` (lr2_debug.py:288-289) and the same sigmoid cross-entropy / SGD.
+Here it is a working model: the three tables are row-sharded ``sparse`` variables (no replicated
+copy anywhere) and one fused kernel (``b200ps_sparse_wd``) does gather, loss and all four Hogwild
+updates per launch.  Variables, in creation order after ``global_step``: ``weights/Variable``
+[F,1], ``deep/weights`` [F,D], ``deep/weights_1`` [D,1], ``bias/Variable`` [1].
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from .. import ops
+
+
+def wide_deep_reference(W, E, w2, b, row_ptr, fid, fval, labels, train: bool = True):
+    """float64 oracle.  Returns (loss, pred, grads) with dense grads dict {W, E, w2, b} (or None)."""
+    B = labels.numel()
+    n = int(row_ptr[-1])
+    lens = (row_ptr[1:] - row_ptr[:-1]).long()
+    row_of = torch.repeat_interleave(torch.arange(B), lens)
+    fid = fid[:n].long()
+    fval = fval[:n].double()
+    E = E.double()
+    w2 = w2.double().reshape(-1)
+    h = torch.zeros(B, E.shape[1], dtype=torch.float64).index_add_(0, row_of, E[fid] * fval[:, None])
+    z = h @ w2 + b.double().reshape(())
+    if W is not None:
+        z = z + torch.zeros(B, dtype=torch.float64).index_add_(0, row_of, W.reshape(-1).double()[fid] * fval)
+    y = labels.double().reshape(-1)
+    loss = (torch.clamp(z, min=0) - z * y + torch.log1p(torch.exp(-z.abs()))).mean()
+    pred = torch.sigmoid(z)
+    if not train:
+        return loss, pred, None
+    dz = (pred - y) / B
+    grads = {"w2": h.T @ dz, "b": dz.sum(),
+             "E": torch.zeros_like(E).index_add_(0, fid, (dz[row_of] * fval)[:, None] * w2[None, :])}
+    if W is not None:
+        grads["W"] = torch.zeros(W.shape[0], dtype=torch.float64).index_add_(0, fid, dz[row_of] * fval)
+    return loss, pred, grads
+
+
+class SparseWideDeep:
+    W, E, W2, Bn = "weights/Variable", "deep/weights", "deep/weights_1", "bias/Variable"
+
+    def __init__(self, features: int, dim: int = 128, wide: bool = True, stddev: float = 0.01):
+        if dim not in (128, 256, 512):
+            raise ValueError("SparseWideDeep: dim must be 128, 256 or 512")
+        self.features, self.dim, self.wide, self.stddev = int(features), int(dim), wide, stddev
+        self._bufs: Dict[int, dict] = {}
+
+    def register(self, store) -> None:
+        if hasattr(store, "note_untracked_variable"):
+            store.note_untracked_variable("global_step")
+        if self.wide:
+            store.register(self.W, (self.features, 1), group="sparse", init="normal", stddev=self.stddev)
+        store.register(self.E, (self.features, self.dim), group="sparse", init="normal", stddev=self.stddev)
+        store.register(self.W2, (self.dim, 1), group="sparse", init="normal", stddev=self.stddev)
+        store.register(self.Bn, (1,), group="fp32", init="zeros")
+
+    def names(self):
+        return ((self.W,) if self.wide else ()) + (self.E, self.W2, self.Bn)
+
+    def _buffers(self, B: int, device, key: int) -> dict:
+        k = (B, key)
+        if k not in self._bufs:
+            self._bufs[k] = dict(pred=torch.empty(B, device=device), dz=torch.empty(B, device=device),
+                                 loss=torch.zeros(1, device=device))
+        return self._bufs[k]
+
+    def _tables(self, store) -> dict:
+        from ..parallel.symm import tensor_from_ptr
+        if not hasattr(self, "_tab"):
+            e, w2 = store.sparse_var(self.E), store.sparse_var(self.W2)
+            w = store.sparse_var(self.W) if self.wide else None
+            if w2.rows_per_shard % 4:
+                raise ValueError("SparseWideDeep: w2 shard size must be a multiple of 4 rows")
+            self._tab = dict(
+                wide_table=None if w is None else w.table, wide_rows_per_shard=0 if w is None else w.rows_per_shard,
+                emb_table=e.table, emb_rows_per_shard=e.rows_per_shard, dim=self.dim,
+                w2_table=w2.table, w2_rows_per_shard=w2.rows_per_shard,
+                bias=tensor_from_ptr(store.master_address(self.Bn), 4, store.device).view(torch.float32))
+            self._gs0 = tensor_from_ptr(store.gstep.ptrs[0], 8, store.device).view(torch.int64)
+        return self._tab
+
+    def step_async(self, store, batch, lr: float, rank: Optional[int] = None):
+        """One fused Hogwild step — gather, loss, four scatter-updates, global_step — one launch."""
+        row_ptr, fid, fval, labels = batch
+        bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
+        bufs["loss"].zero_()
+        ops.sparse_wd(row_ptr, fid, fval, labels, **self._tables(store), pred=bufs["pred"],
+                      loss_sum=bufs["loss"], global_step=self._gs0, forward=True, update=True, lr=lr)
+        return bufs["loss"]
+
+    def step_sync(self, store, batch, lr: float, rank: Optional[int] = None, replicas: Optional[int] = None):
+        """Synchronous replicas: all read the same tables (barrier), then the mean gradient is applied."""
+        row_ptr, fid, fval, labels = batch
+        bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
+        bufs["loss"].zero_()
+        N = replicas or store.world
+        tabs = self._tables(store)
+        ops.sparse_wd(row_ptr, fid, fval, labels, **tabs, pred=bufs["pred"], dz_out=bufs["dz"],
+                      loss_sum=bufs["loss"], forward=True, update=False)
+        store.barrier()
+        ops.sparse_wd(row_ptr, fid, fval, labels, **tabs, dz_in=bufs["dz"],
+                      global_step=store.global_step_tensor(rank), forward=False, update=True, lr=lr / N)
+        store.barrier()
+        return bufs["loss"]
+
+    def predict(self, store, batch, rank: Optional[int] = None):
+        row_ptr, fid, fval, labels = batch
+        bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
+        bufs["loss"].zero_()
+        ops.sparse_wd(row_ptr, fid, fval, labels, **self._tables(store), pred=bufs["pred"],
+                      loss_sum=bufs["loss"], forward=True, update=False)
+        return bufs["pred"], bufs["loss"]

@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_wd", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words",
 ]
 
@@ -248,6 +248,21 @@ def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, pred
                                          ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in), ptr(loss_sum),
                                          ptr(global_step), B, rows_per_shard, int(forward), int(update),
                                          lr, gs, ls, stream_ptr(stream)), "sparse_lr")
+
+
+def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, emb_table, emb_rows_per_shard, dim,
+              w2_table, w2_rows_per_shard, bias, pred=None, dz_out=None, dz_in=None, loss_sum=None,
+              global_step=None, forward=True, update=True, lr=0.0, grad_scale=None, loss_scale=None, stream=None):
+    """Sparse wide & deep step over row-sharded tables (K4w/K5w): see include/b200ps.h b200ps_sparse_wd."""
+    _cuda(row_ptr, fid, fval, labels, emb_table, w2_table, bias)
+    B = labels.numel()
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    check(native.load().b200ps_sparse_wd(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), ptr(wide_table),
+                                         wide_rows_per_shard, ptr(emb_table), emb_rows_per_shard, dim,
+                                         ptr(w2_table), w2_rows_per_shard, ptr(bias), ptr(pred), ptr(dz_out),
+                                         ptr(dz_in), ptr(loss_sum), ptr(global_step), B, int(forward),
+                                         int(update), lr, gs, ls, stream_ptr(stream)), "sparse_wd")
 
 
 def auc_hist(pred, labels, thresholds, hist_pos, hist_neg, stream=None):

@@ -79,13 +79,13 @@ class GlooParameterStore:
             lo, hi = self.layout.bounds[k], self.layout.bounds[k + 1]
             self._hdr(k, S.OP_REGISTER, 0, hi - lo)
         for vid, s in enumerate(x for x in self._specs if x.group == "sparse"):
-            rows = s.shape[0]
+            rows, dim = int(s.shape[0]), int(s.shape[1])
             if self.placement == "round_robin_variable":
                 owner = self._order[s.name] % self.num_ps
-                self.sparse[s.name] = dict(spec=s, vid=vid, rows=rows, rows_per_shard=rows, owner=owner)
+                self.sparse[s.name] = dict(spec=s, vid=vid, rows=rows, rows_per_shard=rows, owner=owner, dim=dim)
             else:
                 rps = (rows + self.num_ps - 1) // self.num_ps
-                self.sparse[s.name] = dict(spec=s, vid=vid, rows=rows, rows_per_shard=rps, owner=None)
+                self.sparse[s.name] = dict(spec=s, vid=vid, rows=rows, rows_per_shard=rps, owner=None, dim=dim)
         self._built = True
         return self
 
@@ -139,8 +139,8 @@ class GlooParameterStore:
             for k in range(self.num_ps):
                 lo, hi = self._sparse_range(sv, k)
                 if hi > lo:
-                    self._hdr(k, S.OP_SPARSE_INIT, sv["vid"], hi - lo)
-                    self._send(k, full[lo:hi])
+                    self._hdr(k, S.OP_SPARSE_INIT, sv["vid"], hi - lo, sv["dim"])
+                    self._send(k, full.reshape(-1)[lo * sv["dim"]:hi * sv["dim"]])
         step = 0 if state is None or "global_step" not in state else int(round(float(state["global_step"])))
         for k in range(self.num_ps):
             self._hdr(k, S.OP_SET_STEP, step)           # also flips the "initialized" flag
@@ -203,7 +203,8 @@ class GlooParameterStore:
     # sparse rows (E3/E4 of SURVEY §2.5.3): ids up, rows down; ids+values up
     def sparse_pull(self, name: str, ids: torch.Tensor) -> torch.Tensor:
         sv = self.sparse[name]
-        out = torch.empty(ids.numel(), dtype=torch.float32)
+        dim = sv["dim"]
+        out = torch.empty(ids.numel(), dim, dtype=torch.float32)
         owner = (ids // sv["rows_per_shard"]) if sv["owner"] is None else torch.full_like(ids, sv["owner"])
         local = ids - owner * sv["rows_per_shard"] if sv["owner"] is None else ids
         masks = []
@@ -216,8 +217,8 @@ class GlooParameterStore:
                 self._send(k, local[m])
         for k, (m, n) in enumerate(masks):
             if n:
-                out[m] = self._recv(k, n)
-        return out
+                out[m] = self._recv(k, n * dim).view(n, dim)
+        return out.view(-1) if dim == 1 else out
 
     def sparse_push(self, name: str, ids: torch.Tensor, vals: torch.Tensor, lr: float) -> None:
         sv = self.sparse[name]
@@ -229,7 +230,7 @@ class GlooParameterStore:
             if n:
                 self._hdr(k, S.OP_SPARSE_PUSH, sv["vid"], n, S.f2i(lr))
                 self._send(k, local[m])
-                self._send(k, vals[m].float())
+                self._send(k, vals[m].float().reshape(-1))
 
     # ------------------------------------------------------------------ state
     @property

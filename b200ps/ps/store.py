@@ -51,13 +51,15 @@ class _Group:
 
 @dataclass
 class _SparseVar:
-    """A row-sharded [rows, 1] fp32 variable with NO replicated working copy: workers touch
-    only the rows a batch names, through peer pointers (lr2.py:384 keeps W on the ps)."""
+    """A row-sharded [rows, dim] fp32 variable with NO replicated working copy: workers touch
+    only the rows a batch names, through peer pointers (lr2.py:384 keeps W on the ps; dim > 1 is
+    the embedding table of the wide&deep sketch, lr2_debug.py:423-428)."""
     spec: VarSpec
     rows: int
     rows_per_shard: int
     shards: SymmBuffer
     table: torch.Tensor
+    dim: int = 1
 
 
 def _stream_id(name: str) -> int:
@@ -96,8 +98,8 @@ class ParameterStore:
             raise ValueError(f"variable {name!r} registered twice")
         if group.split(":")[0] not in _DT and group != "sparse":
             raise ValueError(f"unknown group {group!r}")
-        if group == "sparse" and not (len(shape) == 2 and int(shape[1]) == 1):
-            raise ValueError("sparse variables are [rows, 1] (lr2.py:384)")
+        if group == "sparse" and not (len(shape) == 2 and int(shape[1]) >= 1):
+            raise ValueError("sparse variables are [rows, dim] (lr2.py:384, lr2_debug.py:423)")
         self._order[name] = len(self._order)          # creation order drives round-robin placement
         self._specs.append(VarSpec(name, tuple(int(s) for s in shape), group, init, stddev, mean, value,
                                    trainable))
@@ -155,12 +157,12 @@ class ParameterStore:
         for s in self._specs:
             if s.group != "sparse":
                 continue
-            rows = s.shape[0]
+            rows, dim = int(s.shape[0]), int(s.shape[1])
             if self.placement == "round_robin_variable":
                 # whole variable on one ps task (the reference's only option)
                 owner = self._order[s.name] % self.world
                 rps = rows
-                shards = pool.alloc(f"sparse.{s.name}", max(rows, 8) * 4)
+                shards = pool.alloc(f"sparse.{s.name}", max(rows * dim, 8) * 4)
                 ptrs = [shards.ptrs[owner]] * self.world    # every lookup resolves to the owner
                 table = ops.device_ptr_table(ptrs, dev)
             else:
@@ -169,9 +171,9 @@ class ParameterStore:
                 while p2 < rps:
                     p2 <<= 1
                 rps = p2 if p2 * self.world < rows * 2 and p2 * (self.world - 1) < rows else ((rps + 3) // 4 * 4)
-                shards = pool.alloc(f"sparse.{s.name}", max(rps, 8) * 4)
+                shards = pool.alloc(f"sparse.{s.name}", max(rps * dim, 8) * 4)
                 table = ops.device_ptr_table(shards.ptrs, dev)
-            self.sparse[s.name] = _SparseVar(s, rows, rps, shards, table)
+            self.sparse[s.name] = _SparseVar(s, rows, rps, shards, table, dim)
         self._built = True
         return self
 
@@ -181,7 +183,7 @@ class ParameterStore:
     def sparse_shard(self, name: str, rank: Optional[int] = None) -> torch.Tensor:
         sv = self.sparse[name]
         return sv.shards.view(self.pool.local_ranks[0] if rank is None else rank, torch.float32,
-                              0, sv.rows_per_shard)
+                              0, sv.rows_per_shard * sv.dim)
 
     def _sparse_owned(self, sv: _SparseVar, r: int):
         """Global row range stored in rank r's shard buffer."""
@@ -252,10 +254,10 @@ class ParameterStore:
                 lo, hi = self._sparse_owned(sv, r)
                 if hi <= lo:
                     continue
-                dst = sv.shards.view(r, torch.float32, 0, hi - lo)
+                dst = sv.shards.view(r, torch.float32, 0, (hi - lo) * sv.dim)
                 if sv.spec.init == "normal":
                     ops.init_normal(dst, mean=sv.spec.mean, stddev=sv.spec.stddev, seed=self.seed,
-                                    stream_id=_stream_id(sv.spec.name), elem_offset=lo)
+                                    stream_id=_stream_id(sv.spec.name), elem_offset=lo * sv.dim)
                 else:
                     dst.fill_(sv.spec.value if sv.spec.init == "constant" else 0.0)
         for r in self.pool.local_ranks:
@@ -312,12 +314,12 @@ class ParameterStore:
                         full[a - off: b - off] = src.cpu()
             out[s.name] = full.view(s.shape)
         for name, sv in self.sparse.items():
-            full = torch.empty(sv.rows, dtype=torch.float32)
+            full = torch.empty(sv.rows * sv.dim, dtype=torch.float32)
             for r in range(self.world):
                 lo, hi = self._sparse_owned(sv, r)
                 if hi > lo:
-                    src = tensor_from_ptr(sv.shards.ptrs[r], 4 * (hi - lo), self.device).view(torch.float32)
-                    full[lo:hi] = src.cpu()
+                    src = tensor_from_ptr(sv.shards.ptrs[r], 4 * (hi - lo) * sv.dim, self.device).view(torch.float32)
+                    full[lo * sv.dim:hi * sv.dim] = src.cpu()
             out[name] = full.view(sv.spec.shape)
         out["global_step"] = torch.tensor(float(self.global_step), dtype=torch.float32)
         return out
@@ -332,12 +334,13 @@ class ParameterStore:
             self._assign(s, t.reshape(-1).to(self.device))
         for name, sv in self.sparse.items():
             t = torch.as_tensor(state[name], dtype=torch.float32).reshape(-1)
-            if t.numel() != sv.rows:
-                raise ValueError(f"{name}: checkpoint has {t.numel()} rows, want {sv.rows}")
+            if t.numel() != sv.rows * sv.dim:
+                raise ValueError(f"{name}: checkpoint has {t.numel()} elements, want {sv.rows * sv.dim}")
             for r in self.pool.local_ranks:
                 lo, hi = self._sparse_owned(sv, r)
                 if hi > lo:
-                    sv.shards.view(r, torch.float32, 0, hi - lo).copy_(t[lo:hi].to(self.device))
+                    sv.shards.view(r, torch.float32, 0, (hi - lo) * sv.dim).copy_(
+                        t[lo * sv.dim:hi * sv.dim].to(self.device))
         if "global_step" in state:
             for r in self.pool.local_ranks:
                 self.gstep.view(r, torch.int64)[0] = int(round(float(state["global_step"])))

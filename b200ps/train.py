@@ -397,9 +397,9 @@ class SparseLRTrainer(_TrainerBase):
     """lr2.py's trainer over a row-sharded weight: async (default, like the reference) or sync."""
 
     def __init__(self, ctx, features: int, lr: float = 0.001, mode: str = "async",
-                 placement: str = "flat_shard", seed: int = 1, use_graph: bool = True):
+                 placement: str = "flat_shard", seed: int = 1, use_graph: bool = True, model=None):
         super().__init__(ctx, mode, lr, None, placement, seed)
-        self.model = SparseLR(features)
+        self.model = model or SparseLR(features)
         self.model.register(self.store)
         self.store.build()
         self.store.initialize()
@@ -447,3 +447,14 @@ class SparseLRTrainer(_TrainerBase):
 
     def predict(self, batch):
         return self.model.predict(self.store, batch)
+
+
+class SparseWideDeepTrainer(SparseLRTrainer):
+    """The wide & deep extension of the LR trainer (lr2_debug.py:423-428): same step API and modes,
+    model = wide [F,1] + embedding [F,dim] x [dim,1]."""
+
+    def __init__(self, ctx, features: int, dim: int = 128, wide: bool = True, lr: float = 0.001,
+                 mode: str = "async", placement: str = "flat_shard", seed: int = 1, use_graph: bool = True):
+        from .models.wide_deep import SparseWideDeep
+        super().__init__(ctx, features, lr=lr, mode=mode, placement=placement, seed=seed, use_graph=use_graph,
+                         model=SparseWideDeep(features, dim=dim, wide=wide))

@@ -205,6 +205,18 @@ int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, const float* fv
                      float* dz_out, const float* dz_in, float* loss_sum, uint64_t* global_step,
                      int32_t B, int64_t rows_per_shard, int32_t do_forward, int32_t do_update,
                      float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+/* K4w/K5w: the wide & deep extension sketched at lr2_debug.py:423-428 —
+ *   z = sum_j W[fid_j]*val_j + (sum_j val_j*E[fid_j,:]) . w2 + b
+ * over row-sharded tables W [F,1] (optional: wide_shards may be NULL), E [F,dim] (dim 128/256/512) and
+ * w2 [dim,1] (rows_per_shard a multiple of 4), addressed like w_shards above.  One fused Hogwild launch
+ * (do_forward && do_update) gathers, evaluates the loss and scatters all four updates; forward-only
+ * evaluates; update-only re-gathers h and applies dz_in (the synchronous-replica split). */
+int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
+                     float* const* wide_shards, int64_t wide_rows_per_shard, float* const* emb_shards,
+                     int64_t emb_rows_per_shard, int32_t dim, float* const* w2_shards,
+                     int64_t w2_rows_per_shard, float* bias, float* pred, float* dz_out, const float* dz_in,
+                     float* loss_sum, uint64_t* global_step, int32_t B, int32_t do_forward, int32_t do_update,
+                     float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
 int b200ps_auc_hist(const float* pred, const float* labels, int32_t B, const float* thresholds,
                     int32_t T, uint64_t* hist_pos, uint64_t* hist_neg, b200ps_stream_t stream);
 

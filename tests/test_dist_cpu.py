@@ -135,6 +135,27 @@ def test_lr2_round_robin_vs_flat_shard_two_ps(tmp_path):
         assert "Finish train." in out
 
 
+def test_lr2_wide_deep_over_gloo_and_debug_driver(tmp_path):
+    """--deep_dim adds the [F,128] embedding + [128,1] layer of lr2_debug.py:423-428; on the gloo backend the
+    rows of both tables travel as messages.  The debug driver counts the lines of its shard of a file list."""
+    rc, out = launch(tmp_path / "wd", ["--num_ps", "2", "--num_workers", "2", "lr2", "--", "--backend", "gloo",
+                                       "--train", "synthetic", "--test", "synthetic", "--features", "2000",
+                                       "--num_epochs", "3", "--batch_size", "200", "--synthetic_rows", "400",
+                                       "--deep_dim", "128", "--learning_rate", "0.5"])
+    assert rc == 0, out
+    assert any(re.search(r"Finish evaluate, auc: \(0\.\d+, 0\.\d+\)", l) for l in lines_of(out, "worker:0")), out
+    from b200ps.data.synthetic import write_libsvm_files
+    files = write_libsvm_files(str(tmp_path / "data" / "train"), 4, 50, features=500)
+    (tmp_path / "data" / "train_file_list").write_text("\n".join(files) + "\n")
+    (tmp_path / "cluster_conf.json").write_text('{"ps": ["localhost:2222"], "worker": ["localhost:2223", "localhost:2224"]}')
+    for loader in ("thread", "process"):
+        r = subprocess.run([sys.executable, "-m", "b200ps.apps.lr2_debug", "--task_index", "1", "--loader", loader,
+                            "--test_file_list", ""], cwd=tmp_path, env=ENV, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout + r.stderr
+        text = r.stdout + r.stderr
+        assert "train lines: 100" in text and "part-00001" in text and "part-00003" in text and "part-00000" not in text
+
+
 def test_model_export_and_pipeline_demos(tmp_path):
     r = subprocess.run([sys.executable, "-m", "b200ps.apps.model_export", "--device", "cpu", "--work_dir", str(tmp_path / "model")],
                        env=ENV, capture_output=True, text=True, timeout=120)
@@ -159,7 +180,7 @@ def test_shell_launchers(tmp_path):
     write_libsvm_files(str(tmp_path / "data" / "train"), 3, 200, features=500)
     write_libsvm_files(str(tmp_path / "data" / "test"), 1, 200, features=500)
     r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "run_lr2.sh"), "--help"], capture_output=True, text=True)
-    assert r.returncode == 0 and "--load_mode" in r.stdout and "-j, --job_name" in r.stdout
+    assert r.returncode == 0 and "--load_mode" in r.stderr and "-j,--job_name" in r.stderr
     r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "run.sh"), "-t", "data/train", "-T", "data/test"], cwd=tmp_path,
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr

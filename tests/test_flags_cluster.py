@@ -85,3 +85,56 @@ def test_flat_shard_placement_is_even_and_aligned():
         assert all(lay.offsets[s.name] % 8 == 0 for s in specs)
     with pytest.raises(ValueError):
         plan_layout(specs, 2, "nope")
+
+
+def _bashflags(script_body, *args):
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = ". %s/scripts/bashflags\n%s" % (root, script_body)
+    return subprocess.run(["bash", "-c", script, "prog"] + list(args), capture_output=True, text=True)
+
+
+def test_bashflags_types_spellings_and_errors():
+    """scripts/bashflags: the shflags role (typed DEFINE_*, long/short/=/--no, multi flags, help, validation)."""
+    body = """
+DEFINE_string job_name ps "job" j
+DEFINE_integer task_index 0 "idx" i
+DEFINE_float lr 0.001 "step"
+DEFINE_boolean dry false "dry run" n
+DEFINE_boolean verbose true "talk" v
+DEFINE_multi_string extra "" "repeatable" x
+FLAGS "$@" || exit $?
+eval set -- "${FLAGS_ARGV}"
+echo "job=${FLAGS_job_name} idx=${FLAGS_task_index} lr=${FLAGS_lr} dry=${FLAGS_dry} verbose=${FLAGS_verbose} n=${#FLAGS_extra[@]} last=${FLAGS_extra[1]:-} argc=$# args=$*"
+"""
+    r = _bashflags(body, "-j", "worker", "-i3", "--lr=1e-2", "-nv", "--noverbose", "-x", "a", "--extra", "b c", "pos 1", "-7", "--", "--raw")
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.strip() == "job=worker idx=3 lr=1e-2 dry=0 verbose=1 n=2 last=b c argc=3 args=pos 1 -7 --raw"
+    r = _bashflags(body)
+    assert r.stdout.strip() == "job=ps idx=0 lr=0.001 dry=1 verbose=0 n=0 last= argc=0 args="
+    for bad, msg in ((["--task_index", "abc"], "invalid integer"), (["--lr", "fast"], "invalid float"),
+                     (["--bogus"], "unknown flag --bogus"), (["-q"], "unknown flag -q"), (["--job_name"], "needs a value"),
+                     (["--dry=maybe"], "invalid boolean")):
+        r = _bashflags(body, *bad)
+        assert r.returncode == 2 and msg in r.stderr, (bad, r.stderr)
+    r = _bashflags(body, "--help")
+    assert r.returncode == 1 and "-j,--job_name:  job (string; default: 'ps')" in r.stderr and "--[no]dry" in r.stderr
+    r = _bashflags(body, "--helpxml")
+    assert "<name>task_index</name>" in r.stdout and "<type>integer</type>" in r.stdout
+
+
+def test_bashflags_definition_errors_required_and_passthrough():
+    r = _bashflags('DEFINE_integer n abc "bad default"; echo rc=$?')
+    assert "rc=2" in r.stdout and "invalid integer" in r.stderr
+    r = _bashflags('DEFINE_string a x "1" s; DEFINE_string b y "2" s; echo rc=$?')
+    assert "rc=2" in r.stdout and "defined twice" in r.stderr
+    r = _bashflags('DEFINE_string ARGV x "reserved"; echo rc=$?')
+    assert "rc=2" in r.stdout and "reserved" in r.stderr
+    r = _bashflags('DEFINE_string train "" "t"; flags_required train; FLAGS "$@"; echo rc=$?')
+    assert "rc=2" in r.stdout and "required flag(s) missing: --train" in r.stderr
+    r = _bashflags('FLAGS_PASSTHROUGH=1; DEFINE_integer k 1 "k"; FLAGS "$@" || exit 9; echo "k=${FLAGS_k} rest=${FLAGS_ARGV}"',
+                   "--k", "5", "--backend", "gloo", "--sync")
+    assert r.stdout.strip() == "k=5 rest=--backend gloo --sync"
+    r = _bashflags('DEFINE_integer k 1 "k"; flags_reset; DEFINE_string k z "again"; FLAGS "$@"; echo "k=${FLAGS_k}"', "--k", "w")
+    assert r.stdout.strip() == "k=w"

@@ -223,6 +223,57 @@ def test_sparse_lr_vs_dense_reference(native_lib, world):
     assert (torch.cat(shards2).double() - W_ref).abs().max().item() < 1e-3 and gstep.item() == 2
 
 
+@pytest.mark.parametrize("world,dim,wide", [(1, 128, True), (4, 128, True), (2, 256, False), (2, 512, True)])
+def test_sparse_wide_deep_vs_float64_reference(native_lib, world, dim, wide):
+    """K4w/K5w: forward exact on frozen tables; update-only conserves every contribution of all four
+    gradients; the fused Hogwild launch lands close to the frozen-weight result."""
+    from b200ps import ops
+    from b200ps.models.wide_deep import wide_deep_reference
+    F, B = 1 << 14, 300
+    rp, fid, fv, y = _sparse_batch(B=B, nnz=40, spread=10, F=F)
+    g = torch.Generator(device=DEV).manual_seed(9)
+    W = torch.randn(F, device=DEV, generator=g) * 0.1
+    E = torch.randn(F, dim, device=DEV, generator=g) * 0.1
+    w2 = torch.randn(dim, device=DEV, generator=g) * 0.3
+    rows, rows2 = F // world, dim // world
+
+    def tables():
+        ws = [W[r * rows:(r + 1) * rows].clone() for r in range(world)]
+        es = [E[r * rows:(r + 1) * rows].clone() for r in range(world)]
+        w2s = [w2[r * rows2:(r + 1) * rows2].clone() for r in range(world)]
+        kw = dict(wide_table=ops.device_ptr_table([t.data_ptr() for t in ws], DEV) if wide else None,
+                  wide_rows_per_shard=rows if wide else 0,
+                  emb_table=ops.device_ptr_table([t.data_ptr() for t in es], DEV), emb_rows_per_shard=rows, dim=dim,
+                  w2_table=ops.device_ptr_table([t.data_ptr() for t in w2s], DEV), w2_rows_per_shard=rows2,
+                  bias=torch.full((1,), 0.25, device=DEV))
+        return ws, es, w2s, kw
+
+    lr = 0.5
+    loss_ref, p_ref, gr = wide_deep_reference(W.cpu() if wide else None, E.cpu(), w2.cpu(), torch.tensor(0.25),
+                                              rp.cpu(), fid.cpu(), fv.cpu(), y.cpu())
+    ws, es, w2s, kw = tables()
+    pred = torch.empty(B, device=DEV); loss = torch.zeros(1, device=DEV); dz = torch.empty(B, device=DEV)
+    gstep = torch.zeros(1, device=DEV, dtype=torch.int64)
+    ops.sparse_wd(rp, fid, fv, y, **kw, pred=pred, dz_out=dz, loss_sum=loss, forward=True, update=False)
+    torch.cuda.synchronize()
+    assert torch.allclose(pred.cpu().double(), p_ref, atol=2e-5)
+    assert abs(loss.item() - loss_ref.item()) < 2e-5
+    assert torch.equal(torch.cat(es), E) and torch.equal(torch.cat(w2s), w2)
+    ops.sparse_wd(rp, fid, fv, y, **kw, dz_in=dz, global_step=gstep, forward=False, update=True, lr=lr)
+    torch.cuda.synchronize()
+    assert (torch.cat(es).cpu().double() - (E.cpu().double() - lr * gr["E"])).abs().max().item() < 1e-5
+    assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 1e-5
+    if wide:
+        assert (torch.cat(ws).cpu().double() - (W.cpu().double() - lr * gr["W"])).abs().max().item() < 1e-5
+    assert abs(kw["bias"].item() - (0.25 - lr * gr["b"].item())) < 1e-5 and gstep.item() == 1
+    ws, es, w2s, kw = tables()
+    ops.sparse_wd(rp, fid, fv, y, **kw, loss_sum=loss, global_step=gstep, forward=True, update=True, lr=lr)
+    torch.cuda.synchronize()
+    assert (torch.cat(es).cpu().double() - (E.cpu().double() - lr * gr["E"])).abs().max().item() < 1e-3
+    assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 1e-3
+    assert gstep.item() == 2
+
+
 def test_auc_hist(native_lib):
     from b200ps import ops
     from b200ps.metrics.auc import StreamingAUC, auc_from_counts_reference

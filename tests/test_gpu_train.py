@@ -263,3 +263,42 @@ def test_sparse_lr_trainer_learns(native_lib):
             pred, _ = tr.predict(b)
             auc.update(pred, b[3])
         assert auc.result() > 0.65, (mode, auc.result())
+
+
+def test_sparse_wide_deep_trainer_learns_and_checkpoints(native_lib, tmp_path):
+    """The wide & deep extension (lr2_debug.py:423-428) trains in both modes, on 1 and 2 (virtual) ranks,
+    and its [F,D] table round-trips through the TF-bundle checkpoint."""
+    from b200ps import ops
+    from b200ps.io.saver import Saver
+    from b200ps.metrics.auc import StreamingAUC
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import SparseWideDeepTrainer
+    F, B, nnz, spread = 1 << 12, 500, 40, 10
+    batches = []
+    for i in range(40):
+        rp = torch.empty(B + 1, device=DEV, dtype=torch.int32)
+        fid = torch.empty(B * (nnz + spread), device=DEV, dtype=torch.int64)
+        fv = torch.empty(B * (nnz + spread), device=DEV); y = torch.empty(B, device=DEV)
+        ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=5, offset=i * B)
+        batches.append((rp, fid, fv, y))
+    for mode, world in (("async", 1), ("sync", 1), ("async", 2)):
+        ctx = init_from_env(virtual_world=world)
+        tr = SparseWideDeepTrainer(ctx, features=F, dim=128, lr=2.0, mode=mode)
+        for epoch in range(6):
+            for b in batches[:32]:
+                tr.step(b)
+        assert tr.global_step == 6 * 32
+        auc = StreamingAUC(200, device=DEV)
+        for b in batches[32:]:
+            pred, _ = tr.predict(b)
+            auc.update(pred, b[3])
+        assert auc.result() > 0.65, (mode, world, auc.result())
+    state = tr.store.state_dict()
+    assert state["deep/weights"].shape == (F, 128) and state["deep/weights_1"].shape == (128, 1)
+    from b200ps.io.saver import store_variables
+    prefix = Saver().save(store_variables(tr.store), str(tmp_path / "model.ckpt"), global_step=tr.global_step)
+    back = Saver().restore(prefix)
+    tr2 = SparseWideDeepTrainer(init_from_env(virtual_world=2), features=F, dim=128, lr=2.0)
+    tr2.store.load_state_dict({k: torch.as_tensor(v) for k, v in back.items()})
+    p1, _ = tr.predict(batches[33]); p2, _ = tr2.predict(batches[33])
+    assert torch.equal(p1, p2)

@@ -100,3 +100,30 @@ def test_linear_regression_demo_converges_cpu():
     assert float(loss) < first and 0.8 < m.w.item() < 1.4       # y ~ x + bounded wiggle => slope near 1
     v = m.variables()
     assert v["test/weights"].shape == (1, 1) and v["test/bias"].shape == (1,)
+
+
+def test_wide_deep_reference_matches_autograd():
+    """The float64 oracle of the wide & deep model (lr2_debug.py:423-428) against torch autograd."""
+    import torch
+    from b200ps.models.wide_deep import wide_deep_reference
+    g = torch.Generator().manual_seed(3)
+    F, D, B = 50, 8, 6
+    lens = torch.randint(1, 5, (B,), generator=g)
+    row_ptr = torch.cat([torch.zeros(1, dtype=torch.long), lens.cumsum(0)]).int()
+    n = int(row_ptr[-1])
+    fid = torch.randint(0, F, (n,), generator=g)
+    fval = torch.rand(n, generator=g)
+    y = (torch.rand(B, generator=g) > 0.5).float()
+    W = torch.randn(F, 1, generator=g, dtype=torch.float64, requires_grad=True)
+    E = torch.randn(F, D, generator=g, dtype=torch.float64, requires_grad=True)
+    w2 = torch.randn(D, 1, generator=g, dtype=torch.float64, requires_grad=True)
+    b = torch.zeros(1, dtype=torch.float64, requires_grad=True)
+    row_of = torch.repeat_interleave(torch.arange(B), lens)
+    z = torch.zeros(B, dtype=torch.float64).index_add(0, row_of, W[fid, 0] * fval) \
+        + (torch.zeros(B, D, dtype=torch.float64).index_add(0, row_of, E[fid] * fval[:, None]) @ w2)[:, 0] + b
+    loss = torch.nn.functional.binary_cross_entropy_with_logits(z, y.double())
+    loss.backward()
+    l2, pred, gr = wide_deep_reference(W.detach(), E.detach(), w2.detach(), b.detach(), row_ptr, fid, fval, y)
+    assert abs(l2.item() - loss.item()) < 1e-12 and torch.allclose(pred, torch.sigmoid(z.detach()))
+    assert torch.allclose(gr["W"], W.grad[:, 0]) and torch.allclose(gr["E"], E.grad)
+    assert torch.allclose(gr["w2"], w2.grad[:, 0]) and torch.allclose(gr["b"], b.grad[0])
