@@ -87,7 +87,7 @@ class SigmoidMLP:
     # -- GPU path -------------------------------------------------------------------------
     def forward_backward(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None,
                          global_batch: Optional[int] = None, row_offset: Optional[torch.Tensor] = None,
-                         batch: Optional[int] = None, stats_out=None):
+                         batch: Optional[int] = None, stats_out=None, fused: bool = False):
         """Forward + backward of one worker's batch; gradients land in ``store.grad(...)``.
         Returns the (device) loss tensor and the correct-count tensor (both overwritten per step).
         ``stats_out=(loss, correct)`` redirects the two words, e.g. into pinned mapped host memory.
@@ -100,6 +100,13 @@ class SigmoidMLP:
         if stats_out is not None:
             loss, correct = stats_out
         w1 = store.var(self.W1, rank)
+        if fused and self.supports_fused(B):
+            # K13: the whole forward/backward in one launch (exact fp32), gradients for the push
+            ops.mlp_fused_step(x, labels, w1, store.var(self.B1, rank), store.var(self.W2, rank),
+                               store.var(self.B2, rank), loss=loss, correct=correct, batch=B, cursor=row_offset,
+                               grads=(store.grad(self.W1, rank), store.grad(self.B1, rank),
+                                      store.grad(self.W2, rank), store.grad(self.B2, rank)))
+            return loss, correct
         off = dict(a_row_offset=row_offset, a_rows=B) if row_offset is not None else {}
         # split-K over CTAs, each writing its own slab of z2; the head kernel sums the slabs in a
         # fixed order (an atomic split-K would make the step irreproducible bit for bit)
@@ -111,6 +118,25 @@ class SigmoidMLP:
                      grad_scale=1.0 / B, loss_scale=1.0 / B, overwrite_stats=True, label_offset=row_offset,
                      z2_splits=ksplits, z2_split_stride=z2.stride(0))
         ops.gemm(x, dz2, store.grad(self.W1, rank), a_mn_major=True, b_mn_major=True, **off)
+        return loss, correct
+
+    def supports_fused(self, batch: int) -> bool:
+        """Shapes the one-launch step kernel (K13, csrc/kernels/mlp_fused.cu) covers."""
+        return (batch <= 128 and self.hidden <= 128 and self.hidden % 4 == 0 and self.classes <= 16
+                and self.in_dim % 16 == 0 and self.hidden * self.classes <= 2048)
+
+    def fused_train_step(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, rank: Optional[int] = None,
+                         row_offset: Optional[torch.Tensor] = None, batch: Optional[int] = None, stats_out=None,
+                         cursor: Optional[torch.Tensor] = None, cursor_step: int = 0, cursor_wrap: int = 1):
+        """Single-replica step entirely in K13: forward, backward, SGD in place, ``global_step += 1`` and the
+        resident-dataset cursor advance — one launch (what example.py:168 asks of one ``sess.run``)."""
+        B = x.shape[0] if row_offset is None else batch
+        bufs = self._buffers(B, x.device, 0 if rank is None else rank)
+        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
+        ops.mlp_fused_step(x, labels, store.var(self.W1, rank), store.var(self.B1, rank), store.var(self.W2, rank),
+                           store.var(self.B2, rank), loss=loss, correct=correct, batch=B, cursor=row_offset, lr=lr,
+                           global_step=store.global_step_tensor(rank), cursor_rw=cursor, cursor_step=cursor_step,
+                           cursor_wrap=cursor_wrap)
         return loss, correct
 
     def evaluate(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None):

@@ -16,7 +16,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
                      GemmArgs, check, ptr, stream_ptr)
 
 __all__ = [
-    "gemm", "mlp_tail", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
+    "gemm", "mlp_tail", "mlp_fused_step", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
     "cast_f32_bf16", "sparse_lr", "sparse_wd", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words",
@@ -147,6 +147,26 @@ def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=No
                                         (native.TAIL_CLEAR_Z2 if clear_z2 else 0), ptr(label_offset), z2_splits,
                                         z2_split_stride,
                                         stream_ptr(stream)), "mlp_tail")
+
+
+def mlp_fused_step(x, labels, w1, b1, w2, b2, *, loss, correct=None, grads=None, lr=0.0, batch=None, cursor=None,
+                   global_step=None, cursor_rw=None, cursor_step=0, cursor_wrap=1, grad_scale=None, loss_scale=None,
+                   stream=None):
+    """Whole narrow-MLP training step in one launch (K13): see include/b200ps.h b200ps_mlp_fused_step.
+    ``grads=None``: apply SGD in place (single replica); ``grads=(gw1, gb1, gw2, gb2)``: write gradients."""
+    _cuda(x, labels, w1, b1, w2, b2)
+    B = x.shape[0] if batch is None else batch
+    D, H = w1.shape
+    Cn = w2.shape[1]
+    if labels.dtype != torch.int32:
+        raise TypeError("mlp_fused_step: labels must be int32 class ids")
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    g = grads or (None, None, None, None)
+    check(native.load().b200ps_mlp_fused_step(
+        ptr(x), ptr(labels), ptr(cursor), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(g[0]), ptr(g[1]), ptr(g[2]),
+        ptr(g[3]), ptr(loss), ptr(correct), ptr(global_step), ptr(cursor_rw), cursor_step, cursor_wrap, B, D, H, Cn,
+        int(grads is None), lr, gs, ls, stream_ptr(stream)), "mlp_fused_step")
 
 
 def softmax_ce(logits, labels, *, dlogits=None, loss_sum=None, correct=None, grad_scale=None,

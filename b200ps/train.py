@@ -128,10 +128,19 @@ class MLPTrainer(_TrainerBase):
 
     def __init__(self, ctx, batch_size: int = 100, lr: float = 0.0005, mode: str = "sync",
                  replicas_to_aggregate: Optional[int] = None, placement: str = "flat_shard",
-                 seed: int = 1, use_graph: bool = True, model: Optional[SigmoidMLP] = None):
+                 seed: int = 1, use_graph: bool = True, model: Optional[SigmoidMLP] = None,
+                 fused_step: Optional[bool] = None):
         super().__init__(ctx, mode, lr, replicas_to_aggregate, placement, seed)
         self.model = model or SigmoidMLP()
         self.batch_size = batch_size
+        # K13: forward+backward (and, for a single replica, the update) as one launch.  Default on
+        # where the kernel applies; B200PS_FUSED_STEP=0 or fused_step=False selects the 4-kernel
+        # tcgen05 chain (the path for larger batches / widths).
+        import os
+        if fused_step is None:
+            fused_step = os.environ.get("B200PS_FUSED_STEP", "1") != "0"
+        self.fused = bool(fused_step) and self.device.type == "cuda" and self.model.supports_fused(batch_size)
+        self.fused_apply = self.fused and mode == "sync" and ctx.world == 1 and (replicas_to_aggregate in (None, 1))
         self.model.register(self.store)
         self.store.build()
         self.store.initialize()
@@ -144,16 +153,29 @@ class MLPTrainer(_TrainerBase):
         if ctx.group is not None:
             ctx.control_barrier()
 
+    def _one_step(self, r, x, labels, row_offset=None, stats_out=None, **cursor_kw):
+        """One replica step on rank ``r``'s batch: returns (loss, correct) device/host words."""
+        st = self.store
+        if self.fused_apply:
+            ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
+                      cursor_wrap=cursor_kw.get("cursor_wrap", 1))
+            return self.model.fused_train_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                               batch=self.batch_size, stats_out=stats_out, **ck)
+        out = self.model.forward_backward(st, x, labels, rank=r, row_offset=row_offset, batch=self.batch_size,
+                                          stats_out=stats_out, fused=self.fused)
+        if self.mode == "async":
+            self.opt.apply(st, rank=r, **cursor_kw)
+        elif len(self.local_ranks) == 1:
+            self.opt.apply(st, **cursor_kw)
+        return out
+
     def _body(self):
         st = self.store
         self.opt.prepare(st)
         for r in self.local_ranks:
-            loss, correct = self.model.forward_backward(st, self.x[r], self.labels[r], rank=r)
-            self._losses[r], self._corrects[r] = loss, correct
-            if self.mode == "async":
-                self.opt.apply(st, rank=r)
-        if self.mode == "sync":
-            self.opt.apply(st)
+            self._losses[r], self._corrects[r] = self._one_step(r, self.x[r], self.labels[r])
+        if self.mode == "sync" and len(self.local_ranks) > 1:
+            self.opt.apply(st)                     # virtual ranks: one push launch for all of them
 
     # -- resident dataset: the whole (per-worker) epoch lives on the device and the captured step
     #    walks it through a device-side cursor — no per-step input copies, no host work but the
@@ -176,10 +198,9 @@ class MLPTrainer(_TrainerBase):
         data, labels, n = self._ds
         r = self.local_ranks[0]
         self.opt.prepare(self.store)             # async: refresh the peer-owned slices (no-op for sync)
-        loss, correct = self.model.forward_backward(self.store, data, labels, rank=r, row_offset=self._cursor,
-                                                    batch=self.batch_size)
-        self._losses[r], self._corrects[r] = loss, correct
-        self.opt.apply(self.store, cursor=self._cursor, cursor_step=self.batch_size, cursor_wrap=n)
+        self._losses[r], self._corrects[r] = self._one_step(r, data, labels, row_offset=self._cursor,
+                                                            cursor=self._cursor, cursor_step=self.batch_size,
+                                                            cursor_wrap=n)
 
     def _body_resident_multi(self):
         for _ in range(self._spg):
@@ -255,9 +276,8 @@ class MLPTrainer(_TrainerBase):
             def body():
                 for i in range(K):
                     trainer.opt.prepare(trainer.store)
-                    trainer.model.forward_backward(trainer.store, x[i * B:(i + 1) * B], y[i * B:(i + 1) * B], rank=r,
-                                                   stats_out=(words[i, 0:1], correct_words[i, 1:2]))
-                    trainer.opt.apply(trainer.store)
+                    trainer._one_step(r, x[i * B:(i + 1) * B], y[i * B:(i + 1) * B],
+                                      stats_out=(words[i, 0:1], correct_words[i, 1:2]))
             return _capture(body, dev), (x, y)
 
         if K == 1:

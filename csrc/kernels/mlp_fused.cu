@@ -1,0 +1,541 @@
+// b200ps K13 — the whole training step of the narrow sigmoid MLP (example.py:95-118) as ONE launch.
+//
+// The 784-100-10 step is 48 MFLOP: on a B200 it is bounded by dependent-launch and pipeline
+// set-up latency, not by arithmetic.  As a chain of four kernels (tcgen05 GEMM, head, tcgen05 GEMM,
+// push) it costs ~25 us, of which < 2 us is math.  This kernel runs the step as three phases of one
+// co-resident grid separated by two device-wide barriers:
+//
+//   A  Z2 partials      CTA (row tile, K slice): X[16 x ks] . W1[ks x H]  -> slab[slice][B][H]
+//   --------------------------------------------------------------- grid barrier 1
+//   B  head             warp per example: sum slabs + b1, sigmoid, 100x10 head, stable
+//                       log-softmax CE, accuracy, dZ3, dZ2 -> dz2[B][H]; per-CTA partials of
+//                       dW2 / db2 / db1 / loss / correct -> part[cta][P]
+//   --------------------------------------------------------------- grid barrier 2
+//   C  dW1 + apply      CTA (8 rows of W1): X^T[8 x B] . dZ2[B x H]; every CTA also merges a
+//                       chunk of the head partials in fixed CTA order; then either
+//                         apply = 1 (one replica): W -= lr * dW in place, global_step += 1, or
+//                         apply = 0: gradients written for the push kernel that follows.
+//
+// fp32 FMA on the CUDA cores, exact fp32 accumulation in a fixed order: the step is bit-reproducible
+// and matches the reference's fp32 CPU arithmetic more closely than a tf32 tensor-core product.  A
+// tensor-core tile (tcgen05, M=128) would spend longer allocating TMEM and fetching its tensor maps
+// than these 100-row products take; the tcgen05 GEMM remains the path for every shape where math
+// matters (b200ps_gemm) and for this model when batch or width outgrow the limits below.
+//
+// Every operand a phase needs that does not depend on the previous phase is fetched with cp.async at
+// kernel entry (three commit groups), so each phase pays at most one L2 round trip after its barrier.
+//
+// Limits: B <= 128, H <= 128 (multiple of 4), C <= 16, D multiple of 8.
+#include "../common.h"
+#include "../workspace.h"
+#include "ptx.cuh"
+
+namespace b200ps {
+
+constexpr int kFsThreads = 256;
+constexpr int kFsWarps = kFsThreads / 32;
+constexpr int kFsRowTile = 16;     // phase A: batch rows per CTA (2 per thread row group)
+constexpr int kFsDRows = 8;        // phase C: rows of W1 per CTA
+constexpr int kFsCP = 16;          // padded class count
+constexpr int kFsCPP = 20;         // padded W2 row in shared memory
+constexpr int kFsMaxPer = 8;       // dW2 outputs per thread: H*C <= 2048
+
+struct FusedParams {
+  const float* x;            // [rows, D]; the batch is rows [*cursor, *cursor + B)
+  const int* labels;         // [rows]
+  const int* cursor;         // device scalar row offset, or null (= 0)
+  float* w1; float* b1; float* w2; float* b2;       // parameters (updated in place when apply)
+  float* gw1; float* gb1; float* gw2; float* gb2;   // gradients (written when !apply)
+  float* slabs;              // [KS][B][H]
+  float* dz2;                // [B][H]
+  float* part;               // [NT][P]
+  unsigned int* bar;         // two barrier counters
+  float* loss; int* correct; // step statistics (overwritten)
+  unsigned long long* global_step;
+  int* cursor_rw; int cursor_step, cursor_wrap;
+  int B, D, H, C;
+  int RT, KS, ks, xpitch;    // phase A: row tiles, K slices, slice width, smem pitch of the X tile
+  int NT, NC, cpitch;        // phase B / C active CTAs, smem pitch of the X^T tile
+  int apply;
+  float lr, grad_scale, loss_scale;
+  long long* timing;         // debug: SM-clock stamps of CTA 0 at the phase boundaries (or null)
+};
+
+__device__ __forceinline__ float fs_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
+
+__device__ __forceinline__ void fs_grid_barrier(unsigned int* ctr, unsigned int expected) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(ctr, 1u);
+    if (ld_acquire_gpu(ctr) < expected) {
+      const uint64_t t0 = globaltimer_ns();
+      uint32_t spins = 0;
+      while (ld_acquire_gpu(ctr) < expected) {
+        if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > B200PS_WAIT_TIMEOUT_NS) {
+          printf("b200ps: fused step grid barrier timed out (block %d, want %u, have %u)\n", blockIdx.x, expected,
+                 ld_acquire_gpu(ctr));
+          __trap();
+        }
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// acc[i][:] += sum_k xs[rg + 8 i][k] * ws[k][4 cg .. 4 cg + 3]   for k in [0, K), K a multiple of 4.
+// xs rows are K-contiguous with a pitch whose quarter is odd, so the 8 row groups of a warp hit 8
+// different 16-byte bank groups; the 4 column groups of a warp read 4 consecutive float4 of ws.
+template <int RPT>
+__device__ __forceinline__ void fs_tile_fma(const float* __restrict__ xs, int xpitch, const float* __restrict__ ws,
+                                            int wpitch, int K, int rg, int cg, float (&acc)[RPT][4]) {
+  const float* xr = xs + rg * xpitch;
+  const float* wc = ws + cg * 4;
+#pragma unroll 2
+  for (int k = 0; k < K; k += 4) {
+    float4 xv[RPT], wv[4];
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) xv[i] = *reinterpret_cast<const float4*>(xr + i * 8 * xpitch + k);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) wv[kk] = *reinterpret_cast<const float4*>(wc + (k + kk) * wpitch);
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const float xk[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        acc[i][0] = fmaf(xk[kk], wv[kk].x, acc[i][0]);
+        acc[i][1] = fmaf(xk[kk], wv[kk].y, acc[i][1]);
+        acc[i][2] = fmaf(xk[kk], wv[kk].z, acc[i][2]);
+        acc[i][3] = fmaf(xk[kk], wv[kk].w, acc[i][3]);
+      }
+    }
+  }
+}
+
+#define FS_STAMP(i) do { if (p.timing && cta == 0 && tid == 0) p.timing[i] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedParams p) {
+  extern __shared__ __align__(16) float sm[];
+  const int B = p.B, D = p.D, H = p.H, C = p.C;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cta = blockIdx.x, G = gridDim.x;
+  const int H4 = (H + 3) & ~3, B4 = (B + 3) & ~3;
+  // persistent regions
+  float* s_w2 = sm;                               // [H][CPP]
+  float* s_b2 = s_w2 + H * kFsCPP;                // [16]
+  float* s_b1 = s_b2 + kFsCP;                     // [H4]
+  int* s_lab = reinterpret_cast<int*>(s_b1 + H4); // [8]       labels of this CTA's examples
+  float* s_xt = s_b1 + H4 + kFsWarps;             // [8][cpitch]  X^T tile of phase C (prefetched)
+  float* s_w1c = s_xt + kFsDRows * p.cpitch;      // [8][H]    W1 rows of phase C (apply only)
+  float* s_u = s_w1c + kFsDRows * H;              // union of the per-phase buffers
+  __shared__ float s_loss[kFsWarps];
+  __shared__ int s_corr[kFsWarps];
+
+  FS_STAMP(0);
+  pdl_wait();        // parameters and the cursor were written by the previous step
+  pdl_trigger();
+  FS_STAMP(1);
+  const int row0 = p.cursor ? __ldcg(p.cursor) : 0;
+  const float* xb = p.x + (size_t)row0 * D;
+  if (cta == 0 && tid == 0) p.bar[1] = 0;         // nobody can reach barrier 2 before we reach barrier 1
+
+  // ---------------------------------------------------------------- operand fetch: three cp.async groups
+  // group 0: phase A tiles; group 1: head constants + labels; group 2: X^T tile and W1 rows of phase C.
+  const bool in_a = cta < p.RT * p.KS;
+  const int rt = cta % p.RT, sl_a = cta / p.RT;
+  const int r0 = rt * kFsRowTile, k0 = sl_a * p.ks;
+  const int kw = in_a ? min(p.ks, D - k0) : 0;    // multiple of 4
+  float* s_xs = s_u;                              // [16][xpitch]
+  float* s_ws = s_u + kFsRowTile * p.xpitch;      // [ks][H]
+  if (in_a) {
+    const int QK = kw >> 2;
+    for (int q = tid & 15; q < QK; q += 16) {                      // thread -> (row = tid / 16, quads q, q + 16, ...)
+      const int row = tid >> 4;
+      float* dst = s_xs + row * p.xpitch + 4 * q;
+      if (r0 + row < B) cp_async_16(dst, xb + (size_t)(r0 + row) * D + k0 + 4 * q);
+      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float* src = p.w1 + (size_t)k0 * H;
+    for (int i = tid; i < (kw * H) >> 2; i += kFsThreads) cp_async_16(s_ws + 4 * i, src + 4 * i);
+  }
+  cp_async_commit();
+  if (cta < p.NT) {
+    for (int i = tid; i < H * kFsCP; i += kFsThreads) {
+      const int h = i / kFsCP, c = i - h * kFsCP;
+      if (c < C) cp_async_4(s_w2 + h * kFsCPP + c, p.w2 + h * C + c);
+      else s_w2[h * kFsCPP + c] = 0.f;
+    }
+    for (int i = tid; i < kFsCP; i += kFsThreads) {
+      if (i < C) cp_async_4(s_b2 + i, p.b2 + i);
+      else s_b2[i] = 0.f;
+    }
+    for (int i = tid; i < H; i += kFsThreads) cp_async_4(s_b1 + i, p.b1 + i);
+    if (tid < kFsWarps) {
+      const int r = cta * kFsWarps + tid;
+      if (r < B) cp_async_4(s_lab + tid, p.labels + row0 + r);
+      else s_lab[tid] = 0;
+    }
+  }
+  cp_async_commit();
+  const int d0 = cta * kFsDRows;
+  if (cta < p.NC) {
+    for (int idx = tid; idx < kFsDRows * B4; idx += kFsThreads) {     // transposing gather: 32-byte runs of X rows
+      const int b = idx >> 3, dd = idx & 7;
+      float* dst = s_xt + dd * p.cpitch + b;
+      if (b < B && d0 + dd < D) cp_async_4(dst, xb + (size_t)b * D + d0 + dd);
+      else *dst = 0.f;
+    }
+    if (p.apply) {
+      const int nrow = min(kFsDRows, D - d0);
+      for (int i = tid; i < (nrow * H) >> 2; i += kFsThreads) cp_async_16(s_w1c + 4 * i, p.w1 + (size_t)d0 * H + 4 * i);
+    }
+  }
+  cp_async_commit();
+
+  // ---------------------------------------------------------------- phase A: Z2 slabs
+  cp_async_wait<2>();
+  __syncthreads();
+  FS_STAMP(2);
+  const int rg = tid & 7, cg = tid >> 3;
+  if (in_a && cg * 4 < H) {
+    float acc[2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    fs_tile_fma<2>(s_xs, p.xpitch, s_ws, H, kw, rg, cg, acc);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int row = r0 + rg + 8 * i;
+      if (row < B)
+        *reinterpret_cast<float4*>(p.slabs + ((size_t)sl_a * B + row) * H + cg * 4) =
+            make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+  }
+  FS_STAMP(3);
+  fs_grid_barrier(p.bar, G);
+  FS_STAMP(4);
+
+  // ---------------------------------------------------------------- phase B: head, one warp per example
+  const int P = H * C + C + H + 2;
+  cp_async_wait<1>();
+  __syncthreads();
+  if (cta < p.NT) {
+    float* s_a2 = s_u;                            // [8][H]
+    float* s_dz2 = s_a2 + kFsWarps * H;           // [8][H]
+    float* s_dz3 = s_dz2 + kFsWarps * H;          // [8][16]
+    const int r = cta * kFsWarps + warp;
+    const bool row_ok = r < B;
+    const int HK = (H + 31) >> 5;
+    FS_STAMP(9);
+    const int label = s_lab[warp];
+    float zk[4], ak[4];
+    {
+      // out-of-range lanes / rows read a valid (clamped) address and are masked afterwards
+      const float* sp[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        zk[k] = 0.f;
+        sp[k] = p.slabs + (size_t)min(r, B - 1) * H + min(lane + 32 * k, H - 1);
+      }
+      const size_t sstride = (size_t)B * H;
+      int sl = 0;
+      for (; sl + 8 <= p.KS; sl += 8) {           // 8 slabs x 4 units in flight; summed in slice order
+        float part[8][4];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) part[u][k] = __ldcg(sp[k] + u * sstride);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sp[k] += 8 * sstride;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) zk[k] += part[u][k];
+      }
+      if (sl < p.KS) {
+        float part[8][4];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const bool on = sl + u < p.KS;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) part[u][k] = on ? __ldcg(sp[k] + u * sstride) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) zk[k] += part[u][k];
+      }
+    }
+    FS_STAMP(10);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      const bool ok = row_ok && k < HK && h < H;
+      ak[k] = ok ? fs_sigmoid(zk[k] + s_b1[h]) : 0.f;
+      if (k < HK && h < H) s_a2[warp * H + h] = ak[k];
+    }
+    float zc[kFsCP];
+#pragma unroll
+    for (int c = 0; c < kFsCP; ++c) zc[c] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      if (k < HK && h < H) {
+        const float4* w = reinterpret_cast<const float4*>(s_w2 + h * kFsCPP);
+#pragma unroll
+        for (int c4 = 0; c4 < kFsCP / 4; ++c4) {
+          const float4 wv = w[c4];
+          zc[4 * c4] = fmaf(ak[k], wv.x, zc[4 * c4]);
+          zc[4 * c4 + 1] = fmaf(ak[k], wv.y, zc[4 * c4 + 1]);
+          zc[4 * c4 + 2] = fmaf(ak[k], wv.z, zc[4 * c4 + 2]);
+          zc[4 * c4 + 3] = fmaf(ak[k], wv.w, zc[4 * c4 + 3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kFsCP; ++c) zc[c] += __shfl_xor_sync(0xffffffffu, zc[c], 16);
+    // recursive halving over the lane bits: lane l ends up owning class l & 15
+#pragma unroll
+    for (int bit = 8, n = kFsCP / 2; bit >= 1; bit >>= 1, n >>= 1) {
+      const bool up = (lane & bit) != 0;
+#pragma unroll
+      for (int j = 0; j < n; ++j) {
+        const float send = up ? zc[j] : zc[j + n];
+        const float keep = up ? zc[j + n] : zc[j];
+        zc[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+      }
+    }
+    FS_STAMP(11);
+    const int myc = lane & (kFsCP - 1);
+    const float z = zc[0] + s_b2[myc];
+    const bool cls_ok = myc < C;
+    float m = cls_ok ? z : -INFINITY;
+    int arg = myc;
+#pragma unroll
+    for (int o = kFsCP / 2; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, m, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+    }
+    const float e = cls_ok ? __expf(z - m) : 0.f;
+    float se = e;
+#pragma unroll
+    for (int o = kFsCP / 2; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+    const float zl = __shfl_sync(0xffffffffu, z, label & (kFsCP - 1));
+    const float pr = e / se;
+    if (lane == 0) {
+      s_loss[warp] = row_ok ? m + __logf(se) - zl : 0.f;
+      s_corr[warp] = (row_ok && arg == label) ? 1 : 0;
+    }
+    const float mine = (row_ok && cls_ok) ? (pr - (myc == label ? 1.f : 0.f)) * p.grad_scale : 0.f;
+    FS_STAMP(12);
+    if (lane < kFsCP) s_dz3[warp * kFsCP + lane] = mine;
+    __syncwarp();
+    {
+      const float4* dz = reinterpret_cast<const float4*>(s_dz3 + warp * kFsCP);
+#pragma unroll
+      for (int c4 = 0; c4 < kFsCP / 4; ++c4) {
+        const float4 d = dz[c4];
+        zc[4 * c4] = d.x; zc[4 * c4 + 1] = d.y; zc[4 * c4 + 2] = d.z; zc[4 * c4 + 3] = d.w;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int h = lane + 32 * k;
+      if (k < HK && h < H) {
+        const float4* w = reinterpret_cast<const float4*>(s_w2 + h * kFsCPP);
+        float d = 0.f;
+#pragma unroll
+        for (int c4 = 0; c4 < kFsCP / 4; ++c4) {
+          const float4 wv = w[c4];
+          d = fmaf(zc[4 * c4], wv.x, d);
+          d = fmaf(zc[4 * c4 + 1], wv.y, d);
+          d = fmaf(zc[4 * c4 + 2], wv.z, d);
+          d = fmaf(zc[4 * c4 + 3], wv.w, d);
+        }
+        d *= ak[k] * (1.f - ak[k]);
+        s_dz2[warp * H + h] = d;
+        if (row_ok) p.dz2[(size_t)r * H + h] = d;
+      }
+    }
+    FS_STAMP(13);
+    __syncthreads();
+    FS_STAMP(14);
+    // this CTA's 8 examples -> partial dW2 | db2 | db1 | loss | correct (rows beyond B hold zeros)
+    float* mine_p = p.part + (size_t)cta * P;
+    for (int e0 = tid; e0 < H * kFsCP; e0 += kFsThreads) {          // (h, c) = (e0 / 16, e0 % 16)
+      const int h = e0 >> 4, c = e0 & (kFsCP - 1);
+      if (c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < kFsWarps; ++w8) t = fmaf(s_a2[w8 * H + h], s_dz3[w8 * kFsCP + c], t);
+        mine_p[h * C + c] = t;
+      }
+    }
+    if (tid < C) {
+      float t = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < kFsWarps; ++w8) t += s_dz3[w8 * kFsCP + tid];
+      mine_p[H * C + tid] = t;
+    }
+    if (tid < H) {
+      float t = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < kFsWarps; ++w8) t += s_dz2[w8 * H + tid];
+      mine_p[H * C + C + tid] = t;
+    }
+    if (tid == 0) {
+      float l = 0.f;
+      int cr = 0;
+#pragma unroll
+      for (int w8 = 0; w8 < kFsWarps; ++w8) { l += s_loss[w8]; cr += s_corr[w8]; }
+      mine_p[P - 2] = l;
+      mine_p[P - 1] = (float)cr;
+    }
+  }
+  FS_STAMP(5);
+  fs_grid_barrier(p.bar + 1, G);
+  FS_STAMP(6);
+  if (cta == 0 && tid == 0) p.bar[0] = 0;         // everybody is past barrier 1: re-arm it for the next launch
+
+  // ---------------------------------------------------------------- phase C: dW1 (+ apply) and the merge
+  // the merge loads go out first so that they fly under the dW1 product
+  const int chunk = (P + G - 1) / G;
+  const int o_mine = cta * chunk + tid;
+  const bool merge_fast = chunk <= kFsThreads && p.NT <= 16;
+  float mv[16];
+  if (merge_fast) {
+#pragma unroll
+    for (int u = 0; u < 16; ++u)
+      mv[u] = (tid < chunk && o_mine < P && u < p.NT) ? __ldcg(p.part + (size_t)u * P + o_mine) : 0.f;
+  }
+  if (cta < p.NC) {
+    float* s_dz = s_u;                            // [B4][H], rows >= B zero
+    for (int i = tid; i < (B * H) >> 2; i += kFsThreads) cp_async_16(s_dz + 4 * i, p.dz2 + 4 * i);
+    for (int i = B * H + tid; i < B4 * H; i += kFsThreads) s_dz[i] = 0.f;
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
+    if (cg * 4 < H) {
+      float acc[1][4] = {{0.f, 0.f, 0.f, 0.f}};
+      fs_tile_fma<1>(s_xt, p.cpitch, s_dz, H, B4, rg, cg, acc);
+      const int d = d0 + rg;
+      if (d < D) {
+        const size_t off = (size_t)d * H + cg * 4;
+        if (p.apply) {
+          float4 w = *reinterpret_cast<const float4*>(s_w1c + rg * H + cg * 4);
+          w.x = fmaf(-p.lr, acc[0][0], w.x); w.y = fmaf(-p.lr, acc[0][1], w.y);
+          w.z = fmaf(-p.lr, acc[0][2], w.z); w.w = fmaf(-p.lr, acc[0][3], w.w);
+          *reinterpret_cast<float4*>(p.w1 + off) = w;
+        } else {
+          *reinterpret_cast<float4*>(p.gw1 + off) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+        }
+      }
+    }
+  } else {
+    cp_async_wait<0>();
+  }
+  FS_STAMP(7);
+  // merge of the head partials: output o is summed over the NT partials in CTA order
+  {
+    const int o_end = min(P, (cta + 1) * chunk);
+    for (int o = o_mine; o < o_end; o += kFsThreads) {
+      float t = 0.f;
+      if (merge_fast) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) t += mv[u];
+      } else {
+        for (int n = 0; n < p.NT; ++n) t += __ldcg(p.part + (size_t)n * P + o);
+      }
+      if (o < H * C) {
+        if (p.apply) p.w2[o] = fmaf(-p.lr, t, p.w2[o]); else p.gw2[o] = t;
+      } else if (o < H * C + C) {
+        const int c = o - H * C;
+        if (p.apply) p.b2[c] = fmaf(-p.lr, t, p.b2[c]); else p.gb2[c] = t;
+      } else if (o < P - 2) {
+        const int h = o - H * C - C;
+        if (p.apply) p.b1[h] = fmaf(-p.lr, t, p.b1[h]); else p.gb1[h] = t;
+      } else if (o == P - 2) {
+        if (p.loss) *p.loss = t * p.loss_scale;
+      } else {
+        if (p.correct) *p.correct = (int)(t + 0.5f);
+      }
+    }
+  }
+  FS_STAMP(8);
+  if (cta == 0 && tid == 0 && p.apply) {
+    if (p.global_step) *p.global_step += 1ull;
+    if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
+  }
+}
+
+}  // namespace b200ps
+
+using namespace b200ps;
+
+static long long* g_fs_timing = nullptr;
+// Debug hook: SM-clock stamps of CTA 0 at the 9 phase boundaries of every following fused-step launch
+// are written to `buf` (device memory, 16 x int64); null switches it off.
+extern "C" int b200ps_mlp_fused_step_set_timing(void* buf) {
+  g_fs_timing = static_cast<long long*>(buf);
+  return 0;
+}
+
+extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* cursor, float* w1,
+                                     float* b1, float* w2, float* b2, float* gw1, float* gb1, float* gw2,
+                                     float* gb2, float* loss, int32_t* correct, uint64_t* global_step,
+                                     int32_t* cursor_rw, int32_t cursor_step, int32_t cursor_wrap, int32_t B,
+                                     int32_t D, int32_t H, int32_t C, int32_t apply, float lr, float grad_scale,
+                                     float loss_scale, b200ps_stream_t stream) {
+  B200PS_REQUIRE(B > 0 && B <= 128 && H > 0 && H <= 128 && H % 4 == 0 && C > 0 && C <= kFsCP && D > 0 && D % 8 == 0,
+                 "mlp_fused_step: needs B <= 128, H <= 128 (multiple of 4), C <= 16, D multiple of 8 "
+                 "(got B=%d D=%d H=%d C=%d)", B, D, H, C);
+  B200PS_REQUIRE(H * C <= kFsMaxPer * kFsThreads, "mlp_fused_step: H*C too large");
+  B200PS_REQUIRE(apply || (gw1 && gb1 && gw2 && gb2), "mlp_fused_step: gradient outputs needed when apply == 0");
+  FusedParams p;
+  p.x = x; p.labels = labels; p.cursor = cursor; p.w1 = w1; p.b1 = b1; p.w2 = w2; p.b2 = b2;
+  p.gw1 = gw1; p.gb1 = gb1; p.gw2 = gw2; p.gb2 = gb2; p.loss = loss; p.correct = correct;
+  p.global_step = reinterpret_cast<unsigned long long*>(global_step);
+  p.cursor_rw = cursor_rw; p.cursor_step = cursor_step; p.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
+  p.timing = g_fs_timing;
+  p.B = B; p.D = D; p.H = H; p.C = C; p.apply = apply; p.lr = lr; p.grad_scale = grad_scale; p.loss_scale = loss_scale;
+  p.NC = (D + kFsDRows - 1) / kFsDRows;
+  p.NT = (B + kFsWarps - 1) / kFsWarps;
+  p.RT = (B + kFsRowTile - 1) / kFsRowTile;
+  // K slices: enough CTAs to spread the product over the SMs, at most 16 slabs (one batch of loads in the head)
+  int ks_target = std::min(16, std::max(1, std::min(sm_count(), 112) / p.RT));
+  p.ks = std::max(8, (((D + ks_target - 1) / ks_target) + 7) & ~7);
+  p.KS = (D + p.ks - 1) / p.ks;
+  p.xpitch = p.ks + 4;                               // ks % 8 == 0  ->  pitch / 4 odd
+  const int B4 = (B + 3) & ~3;
+  p.cpitch = ((B4 / 4) % 2 == 0) ? B4 + 4 : B4 + 8;  // pitch / 4 odd
+  const int G = std::max(std::max(p.RT * p.KS, p.NC), p.NT);
+  B200PS_REQUIRE(G <= sm_count(), "mlp_fused_step: needs %d co-resident CTAs, device has %d SMs", G, sm_count());
+  const int P = H * C + C + H + 2;
+  const size_t slab_f = (size_t)p.KS * B * H, dz_f = (size_t)B * H, part_f = (size_t)p.NT * P;
+  Workspace ws;
+  int rc = get_workspace(sizeof(float) * (slab_f + dz_f + part_f), &ws);
+  if (rc) return rc;
+  p.slabs = reinterpret_cast<float*>(ws.data);
+  p.dz2 = p.slabs + slab_f;
+  p.part = p.dz2 + dz_f;
+  p.bar = ws.counters + 8;     // counters[8], [9]: the two grid barriers (self re-arming)
+  const int H4 = (H + 3) & ~3;
+  const size_t u_a = (size_t)kFsRowTile * p.xpitch + (size_t)p.ks * H, u_b = (size_t)kFsWarps * (2 * H + kFsCP),
+               u_c = (size_t)B4 * H;
+  const size_t smem = sizeof(float) * ((size_t)H * kFsCPP + kFsCP + H4 + kFsWarps + (size_t)kFsDRows * p.cpitch +
+                                       (size_t)kFsDRows * H + std::max(std::max(u_a, u_b), u_c));
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B200PS_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    B200PS_CUDA_CHECK(cudaFuncSetAttribute(mlp_fused_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  B200PS_REQUIRE(smem <= 200 * 1024, "mlp_fused_step: shared memory %zu too large", smem);
+  B200PS_CUDA_CHECK(launch_pdl(mlp_fused_step_kernel, dim3(G), dim3(kFsThreads), smem, as_stream(stream), p));
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}

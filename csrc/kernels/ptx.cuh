@@ -304,6 +304,21 @@ __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t tar
 }
 
 // ---------------------------------------------------------------------------------
+// cp.async (LDGSTS): per-thread asynchronous global -> shared copies, grouped and awaited
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {   // at most N committed groups still in flight
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ---------------------------------------------------------------------------------
 // warp reductions
 // ---------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -193,6 +193,23 @@ int b200ps_init_normal(float* out, uint64_t n, float mean, float stddev, uint64_
 int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * K13: the whole step of the narrow sigmoid MLP (example.py:95-118) in ONE launch: forward, stable
+ * log-softmax CE + accuracy, backward, and either the SGD update in place (apply = 1: one replica,
+ * also *global_step += 1 and the cursor advance) or the gradients for a following push (apply = 0).
+ * Three phases of one co-resident grid separated by two device-wide barriers; exact fp32 FMA in a
+ * fixed order (bit-reproducible).  x/labels may be a resident dataset addressed through the device
+ * scalar `cursor` (rows [*cursor, *cursor+B)).  Limits: B <= 128, H <= 128 and H % 4 == 0, C <= 16,
+ * D % 16 == 0.  Uses the library workspace (see b200ps_mlp_tail).  loss/correct are overwritten and
+ * may point into pinned, device-mapped host memory.
+ * ---------------------------------------------------------------------------------- */
+int b200ps_mlp_fused_step_set_timing(void* device_buf_16_int64 /* debug: CTA-0 SM-clock stamps; NULL = off */);
+int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* cursor, float* w1, float* b1,
+                          float* w2, float* b2, float* gw1, float* gb1, float* gw2, float* gb2, float* loss,
+                          int32_t* correct, uint64_t* global_step, int32_t* cursor_rw, int32_t cursor_step,
+                          int32_t cursor_wrap, int32_t B, int32_t D, int32_t H, int32_t C, int32_t apply,
+                          float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * K4/K5: sparse logistic regression over a row-sharded [F,1] weight (lr2.py:390-396).
  * w_shards: device array of `world` shard base pointers (peer-mapped); feature id f lives
  * at w_shards[f / rows_per_shard][f % rows_per_shard].  do_forward computes z, p, loss, dz;

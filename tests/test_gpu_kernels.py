@@ -42,6 +42,64 @@ def test_mlp_tail_matches_autograd(native_lib):
     assert torch.allclose(db1, b1r.grad, atol=1e-6, rtol=1e-4)
 
 
+@pytest.mark.parametrize("B,D,H,Cn", [(100, 784, 100, 10), (37, 48, 20, 3), (128, 64, 128, 16), (8, 16, 4, 2)])
+def test_mlp_fused_step_matches_fp32_reference(native_lib, B, D, H, Cn):
+    """K13, both forms: gradients for a push, and the in-place single-replica update with global_step and
+    the resident-dataset cursor.  Exact-fp32 kernel vs the float64 restatement of the same step."""
+    from b200ps import ops
+    g = torch.Generator(device=DEV).manual_seed(4)
+    rows = 3 * B
+    x = torch.rand(rows, D, device=DEV, generator=g)
+    labels = torch.randint(0, Cn, (rows,), device=DEV, generator=g, dtype=torch.int32)
+    w1 = torch.randn(D, H, device=DEV, generator=g) * 0.2
+    b1 = torch.randn(H, device=DEV, generator=g) * 0.1
+    w2 = torch.randn(H, Cn, device=DEV, generator=g) * 0.5
+    b2 = torch.randn(Cn, device=DEV, generator=g) * 0.1
+
+    def ref(xb, yb):
+        W1, B1, W2, B2 = (t.double().clone().requires_grad_(True) for t in (w1, b1, w2, b2))
+        logits = torch.sigmoid(xb.double() @ W1 + B1) @ W2 + B2
+        loss = torch.nn.functional.cross_entropy(logits, yb.long())
+        loss.backward()
+        return loss.item(), int((logits.argmax(1) == yb).sum()), (W1.grad, B1.grad, W2.grad, B2.grad)
+
+    cursor = torch.tensor([B], device=DEV, dtype=torch.int32)           # second batch of the resident rows
+    loss = torch.zeros(1, device=DEV); correct = torch.zeros(1, device=DEV, dtype=torch.int32)
+    grads = (torch.empty_like(w1), torch.empty_like(b1), torch.empty_like(w2), torch.empty_like(b2))
+    before = [t.clone() for t in (w1, b1, w2, b2)]
+    ops.mlp_fused_step(x, labels, w1, b1, w2, b2, loss=loss, correct=correct, grads=grads, batch=B, cursor=cursor)
+    torch.cuda.synchronize()
+    l_ref, c_ref, g_ref = ref(x[B:2 * B], labels[B:2 * B])
+    assert abs(loss.item() - l_ref) < 2e-5 * max(1.0, abs(l_ref)) and correct.item() == c_ref
+    for got, want in zip(grads, g_ref):
+        assert torch.allclose(got.double(), want, atol=2e-6, rtol=2e-4)
+    for t, b in zip((w1, b1, w2, b2), before):
+        assert torch.equal(t, b)                                        # parameters untouched, cursor too
+    assert cursor.item() == B
+    # in-place form: two consecutive steps walk the cursor and count global_step
+    gstep = torch.zeros(1, device=DEV, dtype=torch.int64)
+    lr = 0.1
+    want = [t.double() - lr * gr for t, gr in zip(before, g_ref)]
+    for _ in range(2):
+        ops.mlp_fused_step(x, labels, w1, b1, w2, b2, loss=loss, correct=correct, batch=B, cursor=cursor, lr=lr,
+                           global_step=gstep, cursor_rw=cursor, cursor_step=B, cursor_wrap=3 * B)
+        if _ == 0:
+            torch.cuda.synchronize()
+            for t, w in zip((w1, b1, w2, b2), want):
+                assert torch.allclose(t.double(), w, atol=2e-6, rtol=1e-5)
+    torch.cuda.synchronize()
+    assert gstep.item() == 2 and cursor.item() == 0                     # B -> 2B -> wraps to 0
+    # bit-reproducible: the same two steps from the same start give the same bytes
+    again = [b.clone() for b in before]
+    cursor.fill_(B)
+    for _ in range(2):
+        ops.mlp_fused_step(x, labels, *again, loss=loss, correct=correct, batch=B, cursor=cursor, lr=lr,
+                           global_step=gstep, cursor_rw=cursor, cursor_step=B, cursor_wrap=3 * B)
+    torch.cuda.synchronize()
+    for t, a in zip((w1, b1, w2, b2), again):
+        assert torch.equal(t, a)
+
+
 def test_mlp_tail_eval_large_batch(native_lib):
     from b200ps import ops
     g = torch.Generator(device=DEV).manual_seed(1)

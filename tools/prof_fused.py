@@ -1,0 +1,15 @@
+"""A handful of eager fused-step launches (for ncu)."""
+import torch
+from b200ps import ops
+dev = "cuda"
+B, D, H, C = 100, 784, 100, 10
+rows = 55000
+x = torch.rand(rows, D, device=dev); y = torch.randint(0, C, (rows,), device=dev, dtype=torch.int32)
+w1 = torch.randn(D, H, device=dev); b1 = torch.zeros(H, device=dev); w2 = torch.randn(H, C, device=dev); b2 = torch.zeros(C, device=dev)
+loss = torch.zeros(1, device=dev); corr = torch.zeros(1, device=dev, dtype=torch.int32)
+cur = torch.zeros(1, device=dev, dtype=torch.int32); gs = torch.zeros(1, device=dev, dtype=torch.int64)
+for _ in range(12):
+    ops.mlp_fused_step(x, y, w1, b1, w2, b2, loss=loss, correct=corr, batch=B, cursor=cur, lr=1e-4, global_step=gs,
+                       cursor_rw=cur, cursor_step=B, cursor_wrap=rows - rows % B)
+torch.cuda.synchronize()
+print("ok", loss.item())
