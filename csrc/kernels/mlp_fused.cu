@@ -34,7 +34,7 @@ namespace b200ps {
 
 constexpr int kFsThreads = 256;
 constexpr int kFsWarps = kFsThreads / 32;
-constexpr int kFsRowTile = 16;     // phase A: batch rows per CTA (2 per thread row group)
+constexpr int kFsRowTile = 16;     // phase A: batch rows per CTA (one per thread row group)
 constexpr int kFsDRows = 8;        // phase C: rows of W1 per CTA
 constexpr int kFsCP = 16;          // padded class count
 constexpr int kFsCPP = 20;         // padded W2 row in shared memory
@@ -66,8 +66,8 @@ __device__ __forceinline__ float fs_sigmoid(float x) { return 1.f / (1.f + __exp
 __device__ __forceinline__ void fs_grid_barrier(unsigned int* ctr, unsigned int expected) {
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(ctr, 1u);
+    // release-arrive (orders this CTA's writes, made visible to thread 0 by the bar.sync above) + acquire-poll
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
     if (ld_acquire_gpu(ctr) < expected) {
       const uint64_t t0 = globaltimer_ns();
       uint32_t spins = 0;
@@ -79,15 +79,14 @@ __device__ __forceinline__ void fs_grid_barrier(unsigned int* ctr, unsigned int 
         }
       }
     }
-    __threadfence();
   }
   __syncthreads();
 }
 
-// acc[i][:] += sum_k xs[rg + 8 i][k] * ws[k][4 cg .. 4 cg + 3]   for k in [0, K), K a multiple of 4.
+// acc[i][:] += sum_k xs[rg + RG i][k] * ws[k][4 cg .. 4 cg + 3]   for k in [0, K), K a multiple of 4.
 // xs rows are K-contiguous with a pitch whose quarter is odd, so the 8 row groups of a warp hit 8
 // different 16-byte bank groups; the 4 column groups of a warp read 4 consecutive float4 of ws.
-template <int RPT>
+template <int RPT, int RG>
 __device__ __forceinline__ void fs_tile_fma(const float* __restrict__ xs, int xpitch, const float* __restrict__ ws,
                                             int wpitch, int K, int rg, int cg, float (&acc)[RPT][4]) {
   const float* xr = xs + rg * xpitch;
@@ -96,7 +95,7 @@ __device__ __forceinline__ void fs_tile_fma(const float* __restrict__ xs, int xp
   for (int k = 0; k < K; k += 4) {
     float4 xv[RPT], wv[4];
 #pragma unroll
-    for (int i = 0; i < RPT; ++i) xv[i] = *reinterpret_cast<const float4*>(xr + i * 8 * xpitch + k);
+    for (int i = 0; i < RPT; ++i) xv[i] = *reinterpret_cast<const float4*>(xr + i * RG * xpitch + k);
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) wv[kk] = *reinterpret_cast<const float4*>(wc + (k + kk) * wpitch);
 #pragma unroll
@@ -126,18 +125,25 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   float* s_b2 = s_w2 + H * kFsCPP;                // [16]
   float* s_b1 = s_b2 + kFsCP;                     // [H4]
   int* s_lab = reinterpret_cast<int*>(s_b1 + H4); // [8]       labels of this CTA's examples
-  float* s_xt = s_b1 + H4 + kFsWarps;             // [8][cpitch]  X^T tile of phase C (prefetched)
-  float* s_w1c = s_xt + kFsDRows * p.cpitch;      // [8][H]    W1 rows of phase C (apply only)
+  float* s_w2raw = s_b1 + H4 + kFsWarps;          // [H*C]     W2 as it lies in memory (re-laid into s_w2)
+  float* s_xc = s_w2raw + H * C;                  // [B4][8]   X columns of phase C (prefetched)
+  float* s_w1c = s_xc + B4 * kFsDRows;            // [8][H]    W1 rows of phase C (apply only)
   float* s_u = s_w1c + kFsDRows * H;              // union of the per-phase buffers
   __shared__ float s_loss[kFsWarps];
   __shared__ int s_corr[kFsWarps];
+  __shared__ __align__(8) uint64_t s_mbar[2];   // bulk-copy completion: [0] W1 slice (phase A), [1] dZ2 (phase C)
+  if (tid == 0) {
+    mbar_init(&s_mbar[0], 1);
+    mbar_init(&s_mbar[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
 
   FS_STAMP(0);
   pdl_wait();        // parameters and the cursor were written by the previous step
   pdl_trigger();
   FS_STAMP(1);
-  const int row0 = p.cursor ? __ldcg(p.cursor) : 0;
-  const float* xb = p.x + (size_t)row0 * D;
+  const int row0 = p.cursor ? __ldcg(p.cursor) : 0;      // consumed late: the parameter fetches below go out first
   if (cta == 0 && tid == 0) p.bar[1] = 0;         // nobody can reach barrier 2 before we reach barrier 1
 
   // ---------------------------------------------------------------- operand fetch: three cp.async groups
@@ -148,29 +154,30 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   const int kw = in_a ? min(p.ks, D - k0) : 0;    // multiple of 4
   float* s_xs = s_u;                              // [16][xpitch]
   float* s_ws = s_u + kFsRowTile * p.xpitch;      // [ks][H]
+  if (in_a && tid == 0) {                         // W1[k0 : k0 + kw, :] is one contiguous run: a single bulk copy
+    mbar_arrive_expect_tx(&s_mbar[0], (uint32_t)(kw * H) * 4u);
+    bulk_load_g2s(s_ws, p.w1 + (size_t)k0 * H, (uint32_t)(kw * H) * 4u, &s_mbar[0]);
+  }
+  const float* xb = p.x + (size_t)row0 * D;
   if (in_a) {
     const int QK = kw >> 2;
+#pragma unroll 1
     for (int q = tid & 15; q < QK; q += 16) {                      // thread -> (row = tid / 16, quads q, q + 16, ...)
       const int row = tid >> 4;
       float* dst = s_xs + row * p.xpitch + 4 * q;
       if (r0 + row < B) cp_async_16(dst, xb + (size_t)(r0 + row) * D + k0 + 4 * q);
       else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const float* src = p.w1 + (size_t)k0 * H;
-    for (int i = tid; i < (kw * H) >> 2; i += kFsThreads) cp_async_16(s_ws + 4 * i, src + 4 * i);
   }
   cp_async_commit();
   if (cta < p.NT) {
-    for (int i = tid; i < H * kFsCP; i += kFsThreads) {
-      const int h = i / kFsCP, c = i - h * kFsCP;
-      if (c < C) cp_async_4(s_w2 + h * kFsCPP + c, p.w2 + h * C + c);
-      else s_w2[h * kFsCPP + c] = 0.f;
+#pragma unroll 1
+    for (int i = tid; i < (H * C) >> 2; i += kFsThreads) cp_async_16(s_w2raw + 4 * i, p.w2 + 4 * i);
+    if (tid < (H >> 2)) cp_async_16(s_b1 + 4 * tid, p.b1 + 4 * tid);
+    if (tid < kFsCP) {
+      if (tid < C) cp_async_4(s_b2 + tid, p.b2 + tid);
+      else s_b2[tid] = 0.f;
     }
-    for (int i = tid; i < kFsCP; i += kFsThreads) {
-      if (i < C) cp_async_4(s_b2 + i, p.b2 + i);
-      else s_b2[i] = 0.f;
-    }
-    for (int i = tid; i < H; i += kFsThreads) cp_async_4(s_b1 + i, p.b1 + i);
     if (tid < kFsWarps) {
       const int r = cta * kFsWarps + tid;
       if (r < B) cp_async_4(s_lab + tid, p.labels + row0 + r);
@@ -180,37 +187,43 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   cp_async_commit();
   const int d0 = cta * kFsDRows;
   if (cta < p.NC) {
-    for (int idx = tid; idx < kFsDRows * B4; idx += kFsThreads) {     // transposing gather: 32-byte runs of X rows
-      const int b = idx >> 3, dd = idx & 7;
-      float* dst = s_xt + dd * p.cpitch + b;
-      if (b < B && d0 + dd < D) cp_async_4(dst, xb + (size_t)b * D + d0 + dd);
-      else *dst = 0.f;
+#pragma unroll 1
+    for (int idx = tid; idx < 2 * B4; idx += kFsThreads) {           // 32-byte runs of the batch rows
+      const int b = idx >> 1, q = idx & 1;
+      float* dst = s_xc + b * kFsDRows + 4 * q;
+      if (b < B) cp_async_16(dst, xb + (size_t)b * D + d0 + 4 * q);
+      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (p.apply) {
       const int nrow = min(kFsDRows, D - d0);
+      #pragma unroll 1
       for (int i = tid; i < (nrow * H) >> 2; i += kFsThreads) cp_async_16(s_w1c + 4 * i, p.w1 + (size_t)d0 * H + 4 * i);
     }
   }
   cp_async_commit();
+  FS_STAMP(19);
 
   // ---------------------------------------------------------------- phase A: Z2 slabs
   cp_async_wait<2>();
+  if (in_a) mbar_wait(&s_mbar[0], 0);
   __syncthreads();
   FS_STAMP(2);
-  const int rg = tid & 7, cg = tid >> 3;
-  if (in_a && cg * 4 < H) {
-    float acc[2][4];
+  {
+    const int rg = tid & 7, cg = tid >> 3;        // 8 row groups (rows rg, rg + 8) x 32 column groups
+    if (in_a && cg * 4 < H) {
+      float acc[2][4];
 #pragma unroll
-    for (int i = 0; i < 2; ++i)
+      for (int i = 0; i < 2; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    fs_tile_fma<2>(s_xs, p.xpitch, s_ws, H, kw, rg, cg, acc);
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+      fs_tile_fma<2, 8>(s_xs, p.xpitch, s_ws, H, kw, rg, cg, acc);
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int row = r0 + rg + 8 * i;
-      if (row < B)
-        *reinterpret_cast<float4*>(p.slabs + ((size_t)sl_a * B + row) * H + cg * 4) =
-            make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      for (int i = 0; i < 2; ++i) {
+        const int row = r0 + rg + 8 * i;
+        if (row < B)
+          *reinterpret_cast<float4*>(p.slabs + ((size_t)sl_a * B + row) * H + cg * 4) =
+              make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      }
     }
   }
   FS_STAMP(3);
@@ -222,6 +235,11 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   cp_async_wait<1>();
   __syncthreads();
   if (cta < p.NT) {
+    for (int i = tid; i < H * kFsCP; i += kFsThreads) {           // W2 -> padded rows of 16 classes (+4)
+      const int h = i >> 4, c = i & (kFsCP - 1);
+      s_w2[h * kFsCPP + c] = c < C ? s_w2raw[h * C + c] : 0.f;
+    }
+    __syncthreads();
     float* s_a2 = s_u;                            // [8][H]
     float* s_dz2 = s_a2 + kFsWarps * H;           // [8][H]
     float* s_dz3 = s_dz2 + kFsWarps * H;          // [8][16]
@@ -231,42 +249,22 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
     FS_STAMP(9);
     const int label = s_lab[warp];
     float zk[4], ak[4];
-    {
-      // out-of-range lanes / rows read a valid (clamped) address and are masked afterwards
-      const float* sp[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        zk[k] = 0.f;
-        sp[k] = p.slabs + (size_t)min(r, B - 1) * H + min(lane + 32 * k, H - 1);
-      }
-      const size_t sstride = (size_t)B * H;
-      int sl = 0;
-      for (; sl + 8 <= p.KS; sl += 8) {           // 8 slabs x 4 units in flight; summed in slice order
-        float part[8][4];
+    for (int k = 0; k < 4; ++k) zk[k] = 0.f;
+    for (int sl0 = 0; sl0 < p.KS; sl0 += 16) {    // up to 16 slabs x 4 units in flight; summed in slice order
+      float part[16][4];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < 16; ++u)
 #pragma unroll
-          for (int k = 0; k < 4; ++k) part[u][k] = __ldcg(sp[k] + u * sstride);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) sp[k] += 8 * sstride;
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-#pragma unroll
-          for (int k = 0; k < 4; ++k) zk[k] += part[u][k];
-      }
-      if (sl < p.KS) {
-        float part[8][4];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const bool on = sl + u < p.KS;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) part[u][k] = on ? __ldcg(sp[k] + u * sstride) : 0.f;
+        for (int k = 0; k < 4; ++k) {
+          const int h = lane + 32 * k;
+          part[u][k] = (row_ok && sl0 + u < p.KS && k < HK && h < H)
+                           ? __ldcg(p.slabs + ((size_t)(sl0 + u) * B + r) * H + h) : 0.f;
         }
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < 16; ++u)
 #pragma unroll
-          for (int k = 0; k < 4; ++k) zk[k] += part[u][k];
-      }
+        for (int k = 0; k < 4; ++k) zk[k] += part[u][k];
     }
     FS_STAMP(10);
 #pragma unroll
@@ -365,13 +363,18 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
     FS_STAMP(14);
     // this CTA's 8 examples -> partial dW2 | db2 | db1 | loss | correct (rows beyond B hold zeros)
     float* mine_p = p.part + (size_t)cta * P;
-    for (int e0 = tid; e0 < H * kFsCP; e0 += kFsThreads) {          // (h, c) = (e0 / 16, e0 % 16)
-      const int h = e0 >> 4, c = e0 & (kFsCP - 1);
-      if (c < C) {
-        float t = 0.f;
+    {
+      const int c = tid & (kFsCP - 1);            // thread -> class c, hidden units tid/16, tid/16 + 16, ...
+      float dz[kFsWarps];
 #pragma unroll
-        for (int w8 = 0; w8 < kFsWarps; ++w8) t = fmaf(s_a2[w8 * H + h], s_dz3[w8 * kFsCP + c], t);
-        mine_p[h * C + c] = t;
+      for (int w8 = 0; w8 < kFsWarps; ++w8) dz[w8] = s_dz3[w8 * kFsCP + c];
+      if (c < C) {
+        for (int h = tid >> 4; h < H; h += kFsThreads / kFsCP) {
+          float t = 0.f;
+#pragma unroll
+          for (int w8 = 0; w8 < kFsWarps; ++w8) t = fmaf(s_a2[w8 * H + h], dz[w8], t);
+          mine_p[h * C + c] = t;
+        }
       }
     }
     if (tid < C) {
@@ -395,9 +398,15 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
       mine_p[P - 1] = (float)cr;
     }
   }
+  fence_proxy_async_all();                        // dZ2 is read through the async proxy (bulk copy) in phase C
   FS_STAMP(5);
   fs_grid_barrier(p.bar + 1, G);
   FS_STAMP(6);
+  if (cta < p.NC && tid == 0) {                   // dZ2 is one contiguous run: a single bulk copy, issued first
+    fence_proxy_async_all();
+    mbar_arrive_expect_tx(&s_mbar[1], (uint32_t)(B * H) * 4u);
+    bulk_load_g2s(s_u, p.dz2, (uint32_t)(B * H) * 4u, &s_mbar[1]);
+  }
   if (cta == 0 && tid == 0) p.bar[0] = 0;         // everybody is past barrier 1: re-arm it for the next launch
 
   // ---------------------------------------------------------------- phase C: dW1 (+ apply) and the merge
@@ -413,14 +422,37 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   }
   if (cta < p.NC) {
     float* s_dz = s_u;                            // [B4][H], rows >= B zero
-    for (int i = tid; i < (B * H) >> 2; i += kFsThreads) cp_async_16(s_dz + 4 * i, p.dz2 + 4 * i);
     for (int i = B * H + tid; i < B4 * H; i += kFsThreads) s_dz[i] = 0.f;
-    cp_async_commit();
+    FS_STAMP(17);
     cp_async_wait<0>();
+    mbar_wait(&s_mbar[1], 0);
+    FS_STAMP(18);
     __syncthreads();
+    FS_STAMP(15);
+    const int rg = tid & 7, cg = tid >> 3;
     if (cg * 4 < H) {
       float acc[1][4] = {{0.f, 0.f, 0.f, 0.f}};
-      fs_tile_fma<1>(s_xt, p.cpitch, s_dz, H, B4, rg, cg, acc);
+      {
+        const float* xc = s_xc + rg;              // x[b][d0 + rg], b-major with pitch 8
+        const float* dz = s_dz + cg * 4;
+#pragma unroll 2
+        for (int b = 0; b < B4; b += 4) {
+          float xk[4];
+          float4 wv[4];
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            xk[kk] = xc[(b + kk) * kFsDRows];
+            wv[kk] = *reinterpret_cast<const float4*>(dz + (b + kk) * H);
+          }
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            acc[0][0] = fmaf(xk[kk], wv[kk].x, acc[0][0]);
+            acc[0][1] = fmaf(xk[kk], wv[kk].y, acc[0][1]);
+            acc[0][2] = fmaf(xk[kk], wv[kk].z, acc[0][2]);
+            acc[0][3] = fmaf(xk[kk], wv[kk].w, acc[0][3]);
+          }
+        }
+      }
       const int d = d0 + rg;
       if (d < D) {
         const size_t off = (size_t)d * H + cg * 4;
@@ -477,7 +509,7 @@ using namespace b200ps;
 
 static long long* g_fs_timing = nullptr;
 // Debug hook: SM-clock stamps of CTA 0 at the 9 phase boundaries of every following fused-step launch
-// are written to `buf` (device memory, 16 x int64); null switches it off.
+// are written to `buf` (device memory, 24 x int64); null switches it off.
 extern "C" int b200ps_mlp_fused_step_set_timing(void* buf) {
   g_fs_timing = static_cast<long long*>(buf);
   return 0;
@@ -494,6 +526,8 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
                  "(got B=%d D=%d H=%d C=%d)", B, D, H, C);
   B200PS_REQUIRE(H * C <= kFsMaxPer * kFsThreads, "mlp_fused_step: H*C too large");
   B200PS_REQUIRE(apply || (gw1 && gb1 && gw2 && gb2), "mlp_fused_step: gradient outputs needed when apply == 0");
+  B200PS_REQUIRE(((uintptr_t)x | (uintptr_t)w1 | (uintptr_t)w2 | (uintptr_t)b1 | (uintptr_t)gw1) % 16 == 0,
+                 "mlp_fused_step: x, w1, w2, b1 and gw1 must be 16-byte aligned");
   FusedParams p;
   p.x = x; p.labels = labels; p.cursor = cursor; p.w1 = w1; p.b1 = b1; p.w2 = w2; p.b2 = b2;
   p.gw1 = gw1; p.gb1 = gb1; p.gw2 = gw2; p.gb2 = gb2; p.loss = loss; p.correct = correct;
@@ -525,7 +559,7 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   const int H4 = (H + 3) & ~3;
   const size_t u_a = (size_t)kFsRowTile * p.xpitch + (size_t)p.ks * H, u_b = (size_t)kFsWarps * (2 * H + kFsCP),
                u_c = (size_t)B4 * H;
-  const size_t smem = sizeof(float) * ((size_t)H * kFsCPP + kFsCP + H4 + kFsWarps + (size_t)kFsDRows * p.cpitch +
+  const size_t smem = sizeof(float) * ((size_t)H * kFsCPP + kFsCP + H4 + kFsWarps + (size_t)H * C + (size_t)B4 * kFsDRows +
                                        (size_t)kFsDRows * H + std::max(std::max(u_a, u_b), u_c));
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -535,7 +569,11 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
     attr_set[dev & 63] = true;
   }
   B200PS_REQUIRE(smem <= 200 * 1024, "mlp_fused_step: shared memory %zu too large", smem);
-  B200PS_CUDA_CHECK(launch_pdl(mlp_fused_step_kernel, dim3(G), dim3(kFsThreads), smem, as_stream(stream), p));
+  // one CTA per SM: ask for more than half of an SM's shared memory so that no two CTAs share an SM's
+  // load path and FMA pipes (B200PS_FUSED_SMEM_KB overrides for experiments)
+  static const size_t min_smem = [] { const char* e = getenv("B200PS_FUSED_SMEM_KB"); return (size_t)(e ? atoi(e) : 116) * 1024; }();
+  const size_t smem_launch = std::max(smem, min_smem);
+  B200PS_CUDA_CHECK(launch_pdl(mlp_fused_step_kernel, dim3(G), dim3(kFsThreads), smem_launch, as_stream(stream), p));
   B200PS_LAUNCH_CHECK();
   return 0;
 }

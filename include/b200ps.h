@@ -202,7 +202,7 @@ int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t
  * D % 16 == 0.  Uses the library workspace (see b200ps_mlp_tail).  loss/correct are overwritten and
  * may point into pinned, device-mapped host memory.
  * ---------------------------------------------------------------------------------- */
-int b200ps_mlp_fused_step_set_timing(void* device_buf_16_int64 /* debug: CTA-0 SM-clock stamps; NULL = off */);
+int b200ps_mlp_fused_step_set_timing(void* device_buf_24_int64 /* debug: CTA-0 SM-clock stamps; NULL = off */);
 int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* cursor, float* w1, float* b1,
                           float* w2, float* b2, float* gw1, float* gb1, float* gw2, float* gb2, float* loss,
                           int32_t* correct, uint64_t* global_step, int32_t* cursor_rw, int32_t cursor_step,

@@ -10,7 +10,7 @@ x = torch.rand(rows, D, device=dev); y = torch.randint(0, C, (rows,), device=dev
 w1 = torch.randn(D, H, device=dev); b1 = torch.zeros(H, device=dev); w2 = torch.randn(H, C, device=dev); b2 = torch.zeros(C, device=dev)
 loss = torch.zeros(1, device=dev); corr = torch.zeros(1, device=dev, dtype=torch.int32)
 cur = torch.zeros(1, device=dev, dtype=torch.int32); gs = torch.zeros(1, device=dev, dtype=torch.int64)
-stamps = torch.zeros(16, device=dev, dtype=torch.int64)
+stamps = torch.zeros(24, device=dev, dtype=torch.int64)
 lib = native.load()
 
 
@@ -35,6 +35,9 @@ names = ["pdl_wait", "fetch A", "phase A", "barrier 1", "phase B", "barrier 2", 
 clk = 1.9
 print("CTA0 phases (us at %.1f GHz):" % clk, {k: round(v / n / clk / 1e3, 2) for k, v in zip(names, acc.tolist())},
       "total", round(acc.sum().item() / n / clk / 1e3, 2))
+print("phase C: dz2 fetch %.2f, product+apply %.2f" % ((s[15] - s[6]) / clk / 1e3, (s[7] - s[15]) / clk / 1e3))
+f = lambda a, b: round(float(s[a] - s[b]) / clk / 1e3, 2)
+print("fetch A: issue all groups", f(19, 1), "wait g0", f(2, 19), "| phase C dz2: issue", f(17, 6), "wait", f(18, 17), "sync", f(15, 18))
 print("phase B detail:", dict(zip(["wait+sync", "slab loads", "sigmoid+head+halving", "softmax", "dz2", "syncthreads", "partials"],
                                   [round(v / n / clk / 1e3, 2) for v in accb.tolist()])))
 g = torch.cuda.CUDAGraph()

@@ -68,6 +68,54 @@ __global__ void __launch_bounds__(256) fetch(const float* src, int bytes, int mo
   if (acc == 123.456f) sink[0] = acc + sm[tid];
 }
 
+// write-then-read inside ONE kernel: every CTA writes its share of `bytes`, device-wide barrier, then every CTA
+// fetches all of it (mode 0: cp.async16, 1: bulk copy, 2: ld.cg.v4 batches, 3: plain ld.v4 batches).
+__global__ void __launch_bounds__(256) wr_fetch(float* buf, int bytes, int mode, unsigned* ctr, long long* out, float* sink) {
+  extern __shared__ __align__(128) float sm[];
+  __shared__ __align__(8) unsigned long long bar;
+  const int tid = threadIdx.x, G = gridDim.x;
+  const int nf4 = bytes / 16;
+  if (tid == 0) { asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar))); asm volatile("fence.mbarrier_init.release.cluster;"); }
+  for (int i = blockIdx.x * 256 + tid; i < nf4; i += G * 256) reinterpret_cast<float4*>(buf)[i] = make_float4(i, 1, 2, 3);
+  if (mode == 1) asm volatile("fence.proxy.async;" ::: "memory");
+  __syncthreads();
+  if (tid == 0) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    while (ld_acq(ctr) < (unsigned)G) {}
+  }
+  __syncthreads();
+  const long long t0 = clock64();
+  float acc = 0.f;
+  if (mode == 0) {
+    for (int i = tid; i < nf4; i += 256) cp16(sm + 4 * i, buf + 4 * i);
+    cp_commit_wait();
+  } else if (mode == 1) {
+    if (tid == 0) {
+      asm volatile("fence.proxy.async;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(sm)), "l"(buf), "r"(bytes), "r"(smem_u32(&bar)) : "memory");
+    }
+    unsigned done = 0;
+    while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(smem_u32(&bar)) : "memory");
+  } else {
+    const float4* s = reinterpret_cast<const float4*>(buf);
+    for (int i0 = tid; i0 < nf4; i0 += 256 * 8) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = min(i0 + u * 256, nf4 - 1);
+        if (mode == 2) v[u] = __ldcg(s + i); else v[u] = s[i];
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) if (i0 + u * 256 < nf4) reinterpret_cast<float4*>(sm)[i0 + u * 256] = v[u];
+    }
+  }
+  __syncthreads();
+  const long long t1 = clock64();
+  if (tid == 0) out[blockIdx.x] = t1 - t0;
+  if (acc == 123.456f) sink[0] = acc + sm[tid];
+}
+
 // device-wide barrier round trip: all CTAs arrive (fence + atomic), thread 0 spins
 __global__ void __launch_bounds__(256) gbar(unsigned* ctr, int rounds, int variant, long long* out) {
   const int G = gridDim.x;
@@ -112,6 +160,18 @@ int main() {
       char nm[128]; snprintf(nm, sizeof nm, "%2d KB  %s", kb, names[mode]);
       report(nm, out, G);
     }
+  }
+  cudaFuncSetAttribute(wr_fetch, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  const char* wnames[] = {"cp.async16", "cp.async.bulk", "ld.cg.v4 x8", "ld.v4 x8"};
+  for (int mode = 0; mode < 4; ++mode) {
+    for (int rep = 0; rep < 3; ++rep) {
+      cudaMemset(ctr, 0, 4);
+      wr_fetch<<<G, 256, 100 * 1024>>>(buf, 40 * 1024, mode, ctr, out, sink);
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
+    char nm[128]; snprintf(nm, sizeof nm, "40 KB written in-kernel, then %s", wnames[mode]);
+    report(nm, out, G);
   }
   for (int variant = 0; variant < 2; ++variant)
     for (int g : {13, 98, 148}) {
