@@ -139,6 +139,42 @@ class SigmoidMLP:
                            cursor_wrap=cursor_wrap)
         return loss, correct
 
+    def supports_fused_push(self, store) -> bool:
+        """Can the synchronous push run inside K13?  One rank per process, all four variables alone in one
+        fp32 group that has low-latency landing buffers."""
+        try:
+            g = store._group_of(self.W1)
+        except Exception:
+            return False
+        names = {s.name for s in g.specs}
+        return (store.world > 1 and len(store.pool.local_ranks) == 1 and g.t_ll_grads is not None and store.use_ll
+                and names == set(self.names()) and g.layout.offsets[self.W1] % 4 == 0)
+
+    def fused_push_step(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, rank: Optional[int] = None,
+                        row_offset: Optional[torch.Tensor] = None, batch: Optional[int] = None, stats_out=None,
+                        cursor: Optional[torch.Tensor] = None, cursor_step: int = 0, cursor_wrap: int = 1):
+        """Synchronous-replica step as ONE launch per rank: forward, backward, and the low-latency push
+        (gradient packets to the owners, reduce + SGD + publish, unpack) inside K13 — the fused
+        compute + collective form of example.py:110-123."""
+        from ..ops import native
+        B = x.shape[0] if row_offset is None else batch
+        r = store.pool.local_ranks[0] if rank is None else rank
+        bufs = self._buffers(B, x.device, r)
+        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
+        if "push" not in bufs:
+            g = store._group_of(self.W1)
+            off = g.layout.offsets
+            bufs["push"] = native.FusedPush(
+                pads=native.ptr(store.t_pads), masters=native.ptr(g.t_masters), bounds=native.ptr(g.bounds),
+                ll_grads=native.ptr(g.t_ll_grads), ll_params=native.ptr(g.t_ll_params),
+                global_steps=native.ptr(store.t_gsteps), max_shard_elems=max(g.layout.max_shard, 8),
+                off_w1=off[self.W1], off_b1=off[self.B1], off_w2=off[self.W2], off_b2=off[self.B2],
+                world=store.world, rank=r)
+        ops.mlp_fused_step(x, labels, store.var(self.W1, r), store.var(self.B1, r), store.var(self.W2, r),
+                           store.var(self.B2, r), loss=loss, correct=correct, batch=B, cursor=row_offset, lr=lr,
+                           cursor_rw=cursor, cursor_step=cursor_step, cursor_wrap=cursor_wrap, push=bufs["push"])
+        return loss, correct
+
     def evaluate(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None):
         """Accuracy and mean loss over a (possibly large) batch, e.g. the 10 000-image test set
         in one call like example.py:187."""

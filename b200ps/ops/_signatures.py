@@ -19,7 +19,7 @@ SIGNATURES = {
     "b200ps_cast_f32_bf16": [vp, vp, u64, vp],
     "b200ps_mlp_fused_step_set_timing": [vp],
     "b200ps_mlp_fused_step": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
-                              i32, f32, f32, f32, vp],
+                              i32, f32, f32, f32, vp, vp],
     "b200ps_sparse_wd": [vp, vp, vp, vp, vp, i64, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp, vp, i32, i32, i32,
                          f32, f32, f32, vp],
     "b200ps_sparse_lr": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, f32, f32, f32, vp],

@@ -44,6 +44,16 @@ class GemmArgs(C.Structure):
     ]
 
 
+class FusedPush(C.Structure):
+    """Mirror of ``b200ps_fused_push`` (include/b200ps.h)."""
+    _fields_ = [
+        ("pads", C.c_void_p), ("masters", C.c_void_p), ("bounds", C.c_void_p), ("ll_grads", C.c_void_p),
+        ("ll_params", C.c_void_p), ("global_steps", C.c_void_p), ("max_shard_elems", C.c_int64),
+        ("off_w1", C.c_int64), ("off_b1", C.c_int64), ("off_w2", C.c_int64), ("off_b2", C.c_int64),
+        ("world", C.c_int32), ("rank", C.c_int32),
+    ]
+
+
 DT_BF16, DT_F32 = 0, 1
 ACT_NONE, ACT_SIGMOID = 0, 1
 EPI_STORE, EPI_ATOMIC_ADD, EPI_SGD = 0, 1, 2

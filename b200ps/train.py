@@ -141,9 +141,15 @@ class MLPTrainer(_TrainerBase):
             fused_step = os.environ.get("B200PS_FUSED_STEP", "1") != "0"
         self.fused = bool(fused_step) and self.device.type == "cuda" and self.model.supports_fused(batch_size)
         self.fused_apply = self.fused and mode == "sync" and ctx.world == 1 and (replicas_to_aggregate in (None, 1))
+        self._want_fused_push = (self.fused and mode == "sync" and ctx.world > 1 and
+                                 replicas_to_aggregate in (None, ctx.world) and
+                                 os.environ.get("B200PS_FUSED_PUSH", "1") != "0")
+        self.fused_push = False
         self.model.register(self.store)
         self.store.build()
         self.store.initialize()
+        # synchronous replicas, one rank per GPU: the push runs inside the step kernel (one launch per step)
+        self.fused_push = self._want_fused_push and self.model.supports_fused_push(self.store)
         dev = self.device
         self.x = {r: torch.zeros(batch_size, self.model.in_dim, device=dev) for r in self.local_ranks}
         self.labels = {r: torch.zeros(batch_size, device=dev, dtype=torch.int32) for r in self.local_ranks}
@@ -161,6 +167,11 @@ class MLPTrainer(_TrainerBase):
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
             return self.model.fused_train_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
                                                batch=self.batch_size, stats_out=stats_out, **ck)
+        if self.fused_push:
+            ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
+                      cursor_wrap=cursor_kw.get("cursor_wrap", 1))
+            return self.model.fused_push_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                              batch=self.batch_size, stats_out=stats_out, **ck)
         out = self.model.forward_backward(st, x, labels, rank=r, row_offset=row_offset, batch=self.batch_size,
                                           stats_out=stats_out, fused=self.fused)
         if self.mode == "async":

@@ -14,7 +14,21 @@
 //   C  dW1 + apply      CTA (8 rows of W1): X^T[8 x B] . dZ2[B x H]; every CTA also merges a
 //                       chunk of the head partials in fixed CTA order; then either
 //                         apply = 1 (one replica): W -= lr * dW in place, global_step += 1, or
-//                         apply = 0: gradients written for the push kernel that follows.
+//                         apply = 0: gradients written for the push kernel that follows, or
+//                         apply = 2 (synchronous replicas, one rank per GPU): the low-latency push runs
+//                         inside this launch — see "in-kernel push" below.
+//
+// In-kernel push (apply = 2).  Phase C does not store its gradients: every value leaves as an 8-byte
+// {value, epoch} packet straight into the landing buffer of the rank that owns it (peer memory over
+// NVLink; its own slot for the part it owns itself).  The packets are the synchronisation, so no third grid
+// barrier and no flag exchange is needed:
+//   D  owner            every CTA takes a stripe of this rank's owned range, polls the packets of all
+//                       replicas in rank order, applies the mean-gradient SGD step to the fp32 master and
+//                       publishes the fresh value as a packet to every other rank
+//   E  replica          polls the other owners' packets into the local working copy
+// i.e. forward, backward, reduce-scatter, optimiser and all-gather of one synchronous step are ONE kernel,
+// and a step costs two one-way NVLink latencies on top of the single-GPU step (protocol: ll_proto.cuh,
+// same landing buffers and epochs as b200ps_push_sync_ll, so the two can be mixed).
 //
 // fp32 FMA on the CUDA cores, exact fp32 accumulation in a fixed order: the step is bit-reproducible
 // and matches the reference's fp32 CPU arithmetic more closely than a tf32 tensor-core product.  A
@@ -29,6 +43,7 @@
 #include "../common.h"
 #include "../workspace.h"
 #include "ptx.cuh"
+#include "ll_proto.cuh"
 
 namespace b200ps {
 
@@ -59,6 +74,11 @@ struct FusedParams {
   int apply;
   float lr, grad_scale, loss_scale;
   long long* timing;         // debug: SM-clock stamps of CTA 0 at the phase boundaries (or null)
+  // in-kernel low-latency push (apply == 2)
+  uint32_t* const* pads; float* const* masters; const long long* bounds;
+  uint2* const* ll_grads; uint2* const* ll_params; unsigned long long* const* global_steps;
+  long long max_shard, off_w1, off_b1, off_w2, off_b2;
+  int world, rank;
 };
 
 __device__ __forceinline__ float fs_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -112,6 +132,23 @@ __device__ __forceinline__ void fs_tile_fma(const float* __restrict__ xs, int xp
   }
 }
 
+// gradient element(s) of flat index i -> the owner's landing buffer as {value, epoch} packets
+__device__ __forceinline__ int fs_owner(const long long* s_bounds, long long i) {
+  int o = 0;
+  while (i >= s_bounds[o + 1]) ++o;
+  return o;
+}
+__device__ __forceinline__ void fs_send1(const FusedParams& p, const long long* s_bounds, long long i, float v, uint32_t epoch) {
+  const int o = fs_owner(s_bounds, i);
+  st_packet(p.ll_grads[o] + (long long)p.rank * p.max_shard + (i - s_bounds[o]), v, epoch);
+}
+__device__ __forceinline__ void fs_send4(const FusedParams& p, const long long* s_bounds, long long i, const float (&v)[4], uint32_t epoch) {
+  const int o = fs_owner(s_bounds, i);      // owner ranges are multiples of 8: a 4-aligned group has one owner
+  uint2* dst = p.ll_grads[o] + (long long)p.rank * p.max_shard + (i - s_bounds[o]);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) st_packet(dst + j, v[j], epoch);
+}
+
 #define FS_STAMP(i) do { if (p.timing && cta == 0 && tid == 0) p.timing[i] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedParams p) {
@@ -144,6 +181,12 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   pdl_trigger();
   FS_STAMP(1);
   const int row0 = p.cursor ? __ldcg(p.cursor) : 0;      // consumed late: the parameter fetches below go out first
+  __shared__ long long s_bounds[kMaxWorld + 1];
+  uint32_t epoch = 0;
+  if (p.apply == 2) {
+    if (tid <= p.world) s_bounds[tid] = p.bounds[tid];
+    epoch = __ldcg(p.pads[p.rank] + kSlotEpoch) + 1;       // made visible to the rest of the CTA by the barriers below
+  }
   if (cta == 0 && tid == 0) p.bar[1] = 0;         // nobody can reach barrier 2 before we reach barrier 1
 
   // ---------------------------------------------------------------- operand fetch: three cp.async groups
@@ -194,7 +237,7 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
       if (b < B) cp_async_16(dst, xb + (size_t)b * D + d0 + 4 * q);
       else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (p.apply) {
+    if (p.apply == 1) {
       const int nrow = min(kFsDRows, D - d0);
       #pragma unroll 1
       for (int i = tid; i < (nrow * H) >> 2; i += kFsThreads) cp_async_16(s_w1c + 4 * i, p.w1 + (size_t)d0 * H + 4 * i);
@@ -456,15 +499,25 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
       const int d = d0 + rg;
       if (d < D) {
         const size_t off = (size_t)d * H + cg * 4;
-        if (p.apply) {
+        if (p.apply == 1) {
           float4 w = *reinterpret_cast<const float4*>(s_w1c + rg * H + cg * 4);
           w.x = fmaf(-p.lr, acc[0][0], w.x); w.y = fmaf(-p.lr, acc[0][1], w.y);
           w.z = fmaf(-p.lr, acc[0][2], w.z); w.w = fmaf(-p.lr, acc[0][3], w.w);
           *reinterpret_cast<float4*>(p.w1 + off) = w;
+        } else if (p.apply == 2) {
+          // staged: the CTA's 8 x H block is one contiguous run of the flat gradient and leaves below as
+          // coalesced packets (32 lanes x 8 bytes per store instruction)
+          *reinterpret_cast<float4*>(s_w1c + rg * H + cg * 4) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
         } else {
           *reinterpret_cast<float4*>(p.gw1 + off) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
         }
       }
+    }
+    if (p.apply == 2) {
+      __syncthreads();
+      const int n = min(kFsDRows, D - d0) * H;
+      const long long base = p.off_w1 + (long long)d0 * H;
+      for (int j = tid; j < n; j += kFsThreads) fs_send1(p, s_bounds, base + j, s_w1c[j], epoch);
     }
   } else {
     cp_async_wait<0>();
@@ -482,13 +535,19 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
         for (int n = 0; n < p.NT; ++n) t += __ldcg(p.part + (size_t)n * P + o);
       }
       if (o < H * C) {
-        if (p.apply) p.w2[o] = fmaf(-p.lr, t, p.w2[o]); else p.gw2[o] = t;
+        if (p.apply == 1) p.w2[o] = fmaf(-p.lr, t, p.w2[o]);
+        else if (p.apply == 2) fs_send1(p, s_bounds, p.off_w2 + o, t, epoch);
+        else p.gw2[o] = t;
       } else if (o < H * C + C) {
         const int c = o - H * C;
-        if (p.apply) p.b2[c] = fmaf(-p.lr, t, p.b2[c]); else p.gb2[c] = t;
+        if (p.apply == 1) p.b2[c] = fmaf(-p.lr, t, p.b2[c]);
+        else if (p.apply == 2) fs_send1(p, s_bounds, p.off_b2 + c, t, epoch);
+        else p.gb2[c] = t;
       } else if (o < P - 2) {
         const int h = o - H * C - C;
-        if (p.apply) p.b1[h] = fmaf(-p.lr, t, p.b1[h]); else p.gb1[h] = t;
+        if (p.apply == 1) p.b1[h] = fmaf(-p.lr, t, p.b1[h]);
+        else if (p.apply == 2) fs_send1(p, s_bounds, p.off_b1 + h, t, epoch);
+        else p.gb1[h] = t;
       } else if (o == P - 2) {
         if (p.loss) *p.loss = t * p.loss_scale;
       } else {
@@ -497,9 +556,81 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
     }
   }
   FS_STAMP(8);
-  if (cta == 0 && tid == 0 && p.apply) {
-    if (p.global_step) *p.global_step += 1ull;
-    if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
+  if (p.apply == 1) {
+    if (cta == 0 && tid == 0) {
+      if (p.global_step) *p.global_step += 1ull;
+      if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
+    }
+    return;
+  }
+  if (p.apply != 2) return;
+
+  // ---------------------------------------------------------------- phases D / E: the in-kernel push
+  {
+    const int world = p.world, rank = p.rank;
+    {   // alignment gaps of the flat layout belong to somebody's range too: they travel as zeros
+      const long long total = s_bounds[world];
+      const long long w1e = p.off_w1 + (long long)D * H, w2e = p.off_w2 + (long long)H * C;
+      const long long b1e = p.off_b1 + H, b2e = p.off_b2 + C;
+      const long long first = p.off_w1 == 0 ? w1e : 0;           // W1 is the (large) prefix in every layout we build
+      for (long long i = first + (long long)cta * kFsThreads + tid; i < total; i += (long long)G * kFsThreads) {
+        const bool covered = (i >= p.off_w1 && i < w1e) || (i >= p.off_w2 && i < w2e) || (i >= p.off_b1 && i < b1e) ||
+                             (i >= p.off_b2 && i < b2e);
+        if (!covered) fs_send1(p, s_bounds, i, 0.f, epoch);
+      }
+    }
+    float* work = p.masters[rank];
+    const long long lo = s_bounds[rank], hi = s_bounds[rank + 1], total = s_bounds[world];
+    const long long gtid = (long long)cta * kFsThreads + tid, gstride = (long long)G * kFsThreads;
+    const float step = p.lr / (float)world;
+    const uint2* mine = p.ll_grads[rank];
+    for (long long i = lo + gtid; i < hi; i += gstride) {          // D: reduce in rank order, apply, publish
+      float sum = 0.f;
+      if (world <= 8) {                                             // all replicas' packets in flight at once
+        uint2 pk[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+          if (r < world) pk[r] = peek_packet(mine + (long long)r * p.max_shard + (i - lo));
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+          if (r < world)
+            sum += pk[r].y == epoch ? __uint_as_float(pk[r].x)
+                                    : poll_packet(mine + (long long)r * p.max_shard + (i - lo), epoch);
+      } else {
+        for (int r = 0; r < world; ++r) sum += poll_packet(mine + (long long)r * p.max_shard + (i - lo), epoch);
+      }
+      const float w = work[i] - step * sum;
+      work[i] = w;
+      for (int q = 0; q < world; ++q)
+        if (q != rank) st_packet(p.ll_params[q] + i, w, epoch);
+    }
+    const uint2* fresh = p.ll_params[rank];
+    for (long long i0 = gtid; i0 < total; i0 += 4 * gstride) {     // E: the other owners' values, 4 polls in flight
+      uint2 pk[4];
+      bool need[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * gstride;
+        need[u] = i < total && !(i >= lo && i < hi);
+        if (need[u]) pk[u] = peek_packet(fresh + i);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * gstride;
+        if (need[u]) work[i] = pk[u].y == epoch ? __uint_as_float(pk[u].x) : poll_packet(fresh + i, epoch);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t* pad = p.pads[rank];
+      __threadfence();
+      if (atomicAdd(pad + kSlotCtaDone, 1u) == (unsigned)G - 1) {
+        pad[kSlotCtaDone] = 0;
+        pad[kSlotEpoch] = epoch;
+        if (p.global_steps) *p.global_steps[rank] += 1ull;
+        if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
+      }
+    }
   }
 }
 
@@ -520,12 +651,17 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
                                      float* gb2, float* loss, int32_t* correct, uint64_t* global_step,
                                      int32_t* cursor_rw, int32_t cursor_step, int32_t cursor_wrap, int32_t B,
                                      int32_t D, int32_t H, int32_t C, int32_t apply, float lr, float grad_scale,
-                                     float loss_scale, b200ps_stream_t stream) {
+                                     float loss_scale, const b200ps_fused_push* push, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && B <= 128 && H > 0 && H <= 128 && H % 4 == 0 && C > 0 && C <= kFsCP && D > 0 && D % 8 == 0,
                  "mlp_fused_step: needs B <= 128, H <= 128 (multiple of 4), C <= 16, D multiple of 8 "
                  "(got B=%d D=%d H=%d C=%d)", B, D, H, C);
   B200PS_REQUIRE(H * C <= kFsMaxPer * kFsThreads, "mlp_fused_step: H*C too large");
-  B200PS_REQUIRE(apply || (gw1 && gb1 && gw2 && gb2), "mlp_fused_step: gradient outputs needed when apply == 0");
+  B200PS_REQUIRE(apply >= 0 && apply <= 2, "mlp_fused_step: apply must be 0, 1 or 2");
+  B200PS_REQUIRE(apply != 0 || (gw1 && gb1 && gw2 && gb2), "mlp_fused_step: gradient outputs needed when apply == 0");
+  B200PS_REQUIRE(apply != 2 || (push && push->pads && push->masters && push->bounds && push->ll_grads && push->ll_params &&
+                                push->world >= 2 && push->world <= kMaxWorld && push->rank >= 0 && push->rank < push->world &&
+                                push->off_w1 % 4 == 0),
+                 "mlp_fused_step: apply == 2 needs the push tables, 2 <= world <= 32 and a 4-aligned W1 offset");
   B200PS_REQUIRE(((uintptr_t)x | (uintptr_t)w1 | (uintptr_t)w2 | (uintptr_t)b1 | (uintptr_t)gw1) % 16 == 0,
                  "mlp_fused_step: x, w1, w2, b1 and gw1 must be 16-byte aligned");
   FusedParams p;
@@ -534,6 +670,16 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   p.global_step = reinterpret_cast<unsigned long long*>(global_step);
   p.cursor_rw = cursor_rw; p.cursor_step = cursor_step; p.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
   p.timing = g_fs_timing;
+  p.pads = nullptr; p.masters = nullptr; p.bounds = nullptr; p.ll_grads = nullptr; p.ll_params = nullptr;
+  p.global_steps = nullptr; p.max_shard = 0; p.off_w1 = p.off_b1 = p.off_w2 = p.off_b2 = 0; p.world = 1; p.rank = 0;
+  if (apply == 2) {
+    p.pads = push->pads; p.masters = push->masters; p.bounds = reinterpret_cast<const long long*>(push->bounds);
+    p.ll_grads = reinterpret_cast<uint2* const*>(push->ll_grads);
+    p.ll_params = reinterpret_cast<uint2* const*>(push->ll_params);
+    p.global_steps = reinterpret_cast<unsigned long long* const*>(push->global_steps);
+    p.max_shard = push->max_shard_elems; p.off_w1 = push->off_w1; p.off_b1 = push->off_b1; p.off_w2 = push->off_w2;
+    p.off_b2 = push->off_b2; p.world = push->world; p.rank = push->rank;
+  }
   p.B = B; p.D = D; p.H = H; p.C = C; p.apply = apply; p.lr = lr; p.grad_scale = grad_scale; p.loss_scale = loss_scale;
   p.NC = (D + kFsDRows - 1) / kFsDRows;
   p.NT = (B + kFsWarps - 1) / kFsWarps;

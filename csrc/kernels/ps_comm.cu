@@ -25,18 +25,9 @@
 // other must not be separate launches.
 #include "../common.h"
 #include "ptx.cuh"
+#include "ll_proto.cuh"
 
 namespace b200ps {
-
-// layout of one rank's signal pad (uint32 words)
-constexpr int kPadWords = 256;
-constexpr int kMaxWorld = 32;
-constexpr int kFlagGradsReady = 0;    // [0,32)   written by peer r at slot r
-constexpr int kFlagParamsDone = 32;   // [32,64)
-constexpr int kFlagBarrier = 64;      // [64,96)
-constexpr int kSlotEpoch = 96;        // push epoch (local)
-constexpr int kSlotBarrierEpoch = 97; // barrier epoch (local)
-constexpr int kSlotCtaDone = 98;      // CTA completion counter (local)
 
 struct CommArgs {
   uint32_t* const* pads;      // [world] signal pads
@@ -214,26 +205,6 @@ __global__ void __launch_bounds__(1024) push_sync_sgd_kernel(const CommArgs a) {
 // the data it is waiting for).  Semantics are those of push_sync_sgd with all replicas
 // aggregated: mean gradient, one global step, nobody continues before the update has landed.
 // ------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_packet(uint2* p, float v, uint32_t epoch) {
-  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
-}
-__device__ __forceinline__ float poll_packet(const uint2* p, uint32_t epoch) {
-  uint32_t v, f;
-  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(p) : "memory");
-  if (f != epoch) {
-    const uint64_t t0 = globaltimer_ns();
-    uint32_t spins = 0;
-    do {
-      asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(p) : "memory");
-      if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > B200PS_WAIT_TIMEOUT_NS) {
-        printf("b200ps: LL packet wait timed out (block %d, want epoch %u, have %u)\n", blockIdx.x, epoch, f);
-        __trap();
-      }
-    } while (f != epoch);
-  }
-  return __uint_as_float(v);
-}
-
 __global__ void __launch_bounds__(256) push_sync_ll_kernel(const CommArgs a, uint2* const* ll_grads,
                                                           uint2* const* ll_params, long long max_shard) {
   const int rank = a.rank_base + blockIdx.y;

@@ -195,19 +195,36 @@ int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t
 /* ------------------------------------------------------------------------------------
  * K13: the whole step of the narrow sigmoid MLP (example.py:95-118) in ONE launch: forward, stable
  * log-softmax CE + accuracy, backward, and either the SGD update in place (apply = 1: one replica,
- * also *global_step += 1 and the cursor advance) or the gradients for a following push (apply = 0).
+ * also *global_step += 1 and the cursor advance), the gradients for a following push (apply = 0), or the
+ * whole synchronous-replica push inside the same launch (apply = 2: gradients leave as {value, epoch}
+ * packets for their owners over NVLink, owners reduce + apply + publish, replicas unpack; one rank per
+ * GPU, every rank launches the same step; mixes freely with b200ps_push_sync_ll on the same tables).
  * Three phases of one co-resident grid separated by two device-wide barriers; exact fp32 FMA in a
  * fixed order (bit-reproducible).  x/labels may be a resident dataset addressed through the device
  * scalar `cursor` (rows [*cursor, *cursor+B)).  Limits: B <= 128, H <= 128 and H % 4 == 0, C <= 16,
  * D % 16 == 0.  Uses the library workspace (see b200ps_mlp_tail).  loss/correct are overwritten and
  * may point into pinned, device-mapped host memory.
  * ---------------------------------------------------------------------------------- */
+/* In-kernel push of b200ps_mlp_fused_step (apply = 2): the tables of b200ps_push_sync_ll for the fp32 group
+ * that holds the four variables, this rank's index, and the flat offsets of the variables in the group. */
+typedef struct b200ps_fused_push {
+  uint32_t* const* pads;          /* [world] signal pads */
+  float* const* masters;          /* [world] fp32 master == working copy, flat */
+  const int64_t* bounds;          /* [world+1] owner ranges (multiples of 8 elements) */
+  void* const* ll_grads;          /* [world] packet landing buffers, world * max_shard_elems packets each */
+  void* const* ll_params;         /* [world] packet landing buffers, total elements each */
+  uint64_t* const* global_steps;  /* [world] or NULL */
+  int64_t max_shard_elems;
+  int64_t off_w1, off_b1, off_w2, off_b2;
+  int32_t world, rank;
+} b200ps_fused_push;
 int b200ps_mlp_fused_step_set_timing(void* device_buf_24_int64 /* debug: CTA-0 SM-clock stamps; NULL = off */);
 int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* cursor, float* w1, float* b1,
                           float* w2, float* b2, float* gw1, float* gb1, float* gw2, float* gb2, float* loss,
                           int32_t* correct, uint64_t* global_step, int32_t* cursor_rw, int32_t cursor_step,
                           int32_t cursor_wrap, int32_t B, int32_t D, int32_t H, int32_t C, int32_t apply,
-                          float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+                          float lr, float grad_scale, float loss_scale, const b200ps_fused_push* push,
+                          b200ps_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * K4/K5: sparse logistic regression over a row-sharded [F,1] weight (lr2.py:390-396).
