@@ -51,6 +51,21 @@ def main():
     acc, _ = tr.evaluate(x.view(-1, 784), y.view(-1))
     res["sync_acc"] = acc
     ctx.control_barrier()
+    # the same 60 steps with the push as a separate kernel (K13 gradients + push_sync_ll) and with the
+    # four-kernel tcgen05 chain: the in-kernel push must reproduce the former bit for bit
+    res["sync_fused_push_used"] = bool(tr.fused_push)
+    os.environ["B200PS_FUSED_PUSH"] = "0"
+    tr_sep = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    os.environ.pop("B200PS_FUSED_PUSH")
+    tr_chain = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="sync", use_graph=True, fused_step=False)
+    for i in range(60):
+        tr_sep.step(x[i % 20], y[i % 20])
+        tr_chain.step(x[i % 20], y[i % 20])
+    torch.cuda.synchronize()
+    res["sync_fused_push_bitwise"] = (not tr_sep.fused_push) and digest(tr_sep.store.flat_work("fp32")) == d
+    res["sync_chain_close"] = float((tr_chain.store.flat_work("fp32") - tr.store.flat_work("fp32")).abs().max())
+    res["sync_steps_all"] = [tr_sep.global_step, tr_chain.global_step]
+    ctx.control_barrier()
 
     # ---- async MLP (round-robin placement): the chief's counter sees every worker's update
     tr2 = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="async", use_graph=True, placement="round_robin_variable")

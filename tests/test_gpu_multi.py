@@ -28,6 +28,10 @@ def test_multi_gpu_trainers(native_lib, tmp_path):
     assert res["world"] == n
     assert res["sync_digests_equal"] and res["sync_global_step"] == 60
     assert res["sync_loss"][1] < res["sync_loss"][0] and res["sync_acc"] > 0.2
+    # the push ran inside the step kernel and reproduced the separate-kernel push bit for bit; the tf32
+    # tensor-core chain lands within tf32 rounding of the exact-fp32 fused step
+    assert res["sync_fused_push_used"] and res["sync_fused_push_bitwise"], res
+    assert res["sync_chain_close"] < 5e-3 and res["sync_steps_all"] == [60, 60], res
     assert res["async_global_step"] == 40 * n and res["async_loss"][1] < res["async_loss"][0]
     assert res["wide_digests_equal"] and res["wide_loss"][1] < res["wide_loss"][0]
     assert res["wide_fused_pull"] == (512 % (64 * n) == 0)
