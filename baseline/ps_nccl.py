@@ -169,6 +169,66 @@ class SparsePS:
 
 
 # ---------------------------------------------------------------------------------------------
+class WideDeepPS:
+    """The wide & deep extension with stock ops: row-sharded W [F,1] and E [F,D], replicated w2 [D,1];
+    ids / rows / gradient rows move with all_to_all_single, w2 and b gradients with all_reduce."""
+
+    def __init__(self, F, D, rank, world, device):
+        self.rows = (F + world - 1) // world
+        self.rank, self.world, self.device, self.D = rank, world, device, D
+        g = torch.Generator(device=device).manual_seed(1)
+        self.W = torch.randn(self.rows, device=device, generator=g) * 0.01
+        self.E = torch.randn(self.rows, D, device=device, generator=g) * 0.01
+        self.w2 = torch.randn(D, device=device, generator=g) * 0.01
+        self.b = torch.zeros(1, device=device)
+        self.global_step = 0
+
+    def step(self, batch, lr):
+        rp, fid, fv, y = batch
+        n = int(rp[-1])
+        fid, fv = fid[:n], fv[:n]
+        B, D = y.numel(), self.D
+        row_of = torch.repeat_interleave(torch.arange(B, device=self.device), (rp[1:] - rp[:-1]).long())
+        if self.world == 1:
+            w, e = self.W[fid], self.E[fid]
+        else:
+            owner = fid // self.rows
+            order = torch.argsort(owner)
+            counts = torch.bincount(owner, minlength=self.world)
+            recv_counts = torch.empty_like(counts)
+            dist.all_to_all_single(recv_counts, counts)
+            sc, rc = counts.tolist(), recv_counts.tolist()
+            ids_in = torch.empty(sum(rc), dtype=torch.int64, device=self.device)
+            dist.all_to_all_single(ids_in, (fid - owner * self.rows)[order], rc, sc)
+            rows_in = torch.empty(n, D + 1, device=self.device)
+            dist.all_to_all_single(rows_in, torch.cat([self.E[ids_in], self.W[ids_in, None]], 1), sc, rc)
+            both = torch.empty(n, D + 1, device=self.device)
+            both[order] = rows_in
+            e, w = both[:, :D], both[:, D]
+        h = torch.zeros(B, D, device=self.device).index_add_(0, row_of, e * fv[:, None])
+        z = h @ self.w2 + torch.zeros(B, device=self.device).index_add_(0, row_of, w * fv) + self.b
+        loss = Fnn.binary_cross_entropy_with_logits(z, y)
+        dz = (torch.sigmoid(z) - y) / B
+        gv = dz[row_of] * fv
+        ge = gv[:, None] * self.w2[None, :]
+        gw2, db = h.t() @ dz, dz.sum()
+        if self.world == 1:
+            self.W.index_add_(0, fid, gv, alpha=-lr)
+            self.E.index_add_(0, fid, ge, alpha=-lr)
+        else:
+            g_in = torch.empty(sum(rc), D + 1, device=self.device)
+            dist.all_to_all_single(g_in, torch.cat([ge, gv[:, None]], 1)[order], rc, sc)
+            self.E.index_add_(0, ids_in, g_in[:, :D], alpha=-lr)
+            self.W.index_add_(0, ids_in, g_in[:, D], alpha=-lr)
+            small = torch.cat([gw2, db[None]])
+            dist.all_reduce(small)
+            gw2, db = small[:D], small[D]
+        self.w2 -= lr * gw2
+        self.b -= lr * db
+        self.global_step += self.world
+        return loss.detach()
+
+
 def _timed(steps, fn, world):
     if world > 1:
         dist.barrier()
@@ -212,7 +272,8 @@ def main_from_bench(args) -> int:
     from b200ps import ops                      # input tensors only
     out = {}
     W = max(args.warmup, 3)
-    cfgs = ["mnist_mlp_sync", "mnist_mlp_async", "sparse_lr", "wide_mlp"] if args.config == "all" else [args.config]
+    cfgs = (["mnist_mlp_sync", "mnist_mlp_async", "sparse_lr", "sparse_wide_deep", "wide_mlp"] if args.config == "all"
+            else [args.config])
     for cfg in cfgs:
         if cfg.startswith("mnist"):
             mode = "sync" if cfg.endswith("_sync") else "async"
@@ -252,9 +313,10 @@ def main_from_bench(args) -> int:
                 step(i)
             ms = _timed(steps, step, world)
             out[cfg] = {"value": B * world * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps}
-        elif cfg == "sparse_lr":
-            F, B, nnz, spread = 1 << 24, args.sparse_batch, 100, 20
-            sp = SparsePS(F, rank, world, dev)
+        elif cfg in ("sparse_lr", "sparse_wide_deep"):
+            deep = cfg == "sparse_wide_deep"
+            F, B, nnz, spread = (1 << 22 if deep else 1 << 24), args.sparse_batch, 100, 20
+            sp = WideDeepPS(F, 128, rank, world, dev) if deep else SparsePS(F, rank, world, dev)
             batches = []
             for i in range(64):
                 rp = torch.empty(B + 1, device=dev, dtype=torch.int32); fid = torch.empty(B * (nnz + spread), device=dev, dtype=torch.int64)

@@ -322,13 +322,16 @@ def bench_wide(ctx, args, sampler):
     }
 
 
-def bench_sparse(ctx, args, sampler, mode="async"):
+def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     import torch
     from b200ps import ops
     from b200ps.ops import native
-    from b200ps.train import SparseLRTrainer
-    F, B, nnz, spread = 1 << 24, args.sparse_batch, 100, 20
-    tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
+    from b200ps.train import SparseLRTrainer, SparseWideDeepTrainer
+    F, B, nnz, spread = (1 << 22 if deep_dim else 1 << 24), args.sparse_batch, 100, 20
+    if deep_dim:
+        tr = SparseWideDeepTrainer(ctx, features=F, dim=deep_dim, lr=0.05, mode=mode)
+    else:
+        tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
     dev = ctx.device
     ring = 64
     cap = B * (nnz + spread)
@@ -362,9 +365,12 @@ def bench_sparse(ctx, args, sampler, mode="async"):
         "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
         "loss_first": loss0, "loss_last": loss1, "global_step": tr.global_step,
-        "config": {"model": "sparse_lr_2^24_features_~100nnz", "global_batch": B * ctx.world,
+        # rows gathered and scattered per step: one 4*dim-byte row in, one out (red) per non-zero
+        "row_traffic_GBps_per_gpu": (2 * nnz * B * 4 * max(deep_dim, 1) / (ms / args.steps / 1e3) / 1e9),
+        "config": {"model": (f"sparse_wide_deep_2^22_features_dim{deep_dim}_~100nnz" if deep_dim
+                             else "sparse_lr_2^24_features_~100nnz"), "global_batch": B * ctx.world,
                    "per_gpu_batch": B, "mode": mode, "parallelism": f"dp{ctx.world}+row_shard{ctx.world}",
-                   "inputs": f"ring of {ring} device CSR batches; 64 MB weight vector, random rows"},
+                   "inputs": (f"ring of {ring} device CSR batches; {F * max(deep_dim, 1) * 4 >> 20} MB table, random rows")},
     }
 
 
@@ -391,7 +397,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200ps", choices=["b200ps", "reference", "baseline"])
     ap.add_argument("--config", default="all",
-                    choices=["all", "mnist_mlp_sync", "mnist_mlp_async", "wide_mlp", "sparse_lr"])
+                    choices=["all", "mnist_mlp_sync", "mnist_mlp_async", "wide_mlp", "sparse_lr", "sparse_wide_deep"])
     ap.add_argument("--no-graph", dest="no_graph", action="store_true")
     ap.add_argument("--steps-per-graph", dest="steps_per_graph", type=int, default=8,
                     help="training steps chained inside one CUDA-graph replay (device-side batch cursor)")
@@ -437,11 +443,12 @@ def main():
         "mnist_mlp_async": lambda: bench_mnist(ctx, args, sampler, "async"),
         "wide_mlp": lambda: bench_wide(ctx, args, sampler),
         "sparse_lr": lambda: bench_sparse(ctx, args, sampler, "async"),
+        "sparse_wide_deep": lambda: bench_sparse(ctx, args, sampler, "async", deep_dim=128),
     }
     primary = runners[primary_name]()
     extra = {}
     if args.config == "all":
-        for name in ("mnist_mlp_async", "sparse_lr", "wide_mlp"):
+        for name in ("mnist_mlp_async", "sparse_lr", "sparse_wide_deep", "wide_mlp"):
             try:
                 extra[name] = runners[name]()
             except Exception as e:  # an extra config must never cost the headline line

@@ -22,7 +22,7 @@
 
 namespace b200ps {
 
-constexpr int kWdThreads = 256;            // 8 warps = 8 examples in flight per CTA
+constexpr int kWdThreads = 128;            // 4 warps = 4 examples per CTA: a batch of 500 spreads over 125 SMs
 constexpr int kWdWarps = kWdThreads / 32;
 
 struct ShardedTable {
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
 #pragma unroll
     for (int c = 0; c < NCH; ++c) h[c] = make_float4(0.f, 0.f, 0.f, 0.f);
     float zw = 0.f;
-    // ---- gather: lanes fetch 32 (id, value) pairs, then the warp walks them 4 rows at a time
+    // ---- gather: lanes fetch 32 (id, value) pairs, then the warp walks them FL rows at a time
     for (int base = beg; base < end; base += 32) {
       const int j = base + lane;
       const bool live = j < end;
@@ -99,18 +99,19 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
       if (has_wide && live && p.do_forward) zw = fmaf(__ldcg(p.wide.row(id, 1)), v, zw);
       const unsigned long long rowp = reinterpret_cast<unsigned long long>(p.emb.row(id, D));
       const int n = min(32, end - base);
-      for (int k = 0; k < n; k += 4) {
-        float4 e[4][NCH];
-        float vk[4];
+      constexpr int FL = NCH == 1 ? 16 : (NCH == 2 ? 8 : 4);         // embedding rows in flight per warp (the gather is pure latency)
+      for (int k = 0; k < n; k += FL) {
+        float4 e[FL][NCH];
+        float vk[FL];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < FL; ++u) {
           const float* r = reinterpret_cast<const float*>(__shfl_sync(0xffffffffu, rowp, (k + u) & 31));
           vk[u] = __shfl_sync(0xffffffffu, v, (k + u) & 31);
 #pragma unroll
           for (int c = 0; c < NCH; ++c) e[u][c] = ldcg4(r + (c * 32 + lane) * 4);
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < FL; ++u) {
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
             h[c].x = fmaf(vk[u], e[u][c].x, h[c].x);

@@ -32,7 +32,7 @@ def main(tag="r1"):
     mine = load(f"bench_b200ps_n*_{tag}.json")
     print("| config | GPUs | baseline ex/s (PyTorch+NCCL) | b200ps ex/s | ratio | b200ps ms/step | b200ps e2e ex/s | baseline e2e ex/s |")
     print("|---|---|---|---|---|---|---|---|")
-    for cfg in ("mnist_mlp_sync", "mnist_mlp_async", "sparse_lr", "wide_mlp"):
+    for cfg in ("mnist_mlp_sync", "mnist_mlp_async", "sparse_lr", "sparse_wide_deep", "wide_mlp"):
         for n in sorted(mine):
             m = rows(mine[n]).get(cfg)
             b = rows(base[n]).get(cfg) if n in base else None

@@ -8,7 +8,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from b200ps import ops  # noqa: E402
 from b200ps.parallel.context import init_from_env  # noqa: E402
-from b200ps.train import MLPTrainer, SparseLRTrainer, WideMLPTrainer  # noqa: E402
+from b200ps.train import MLPTrainer, SparseLRTrainer, SparseWideDeepTrainer, WideMLPTrainer  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--config", default="mnist")
@@ -31,6 +31,20 @@ elif a.config == "wide":
 elif a.config == "sparse":
     F, B, nnz, spread = 1 << 24, 500, 100, 20
     tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode="async")
+    rp = torch.empty(B + 1, device=dev, dtype=torch.int32); fid = torch.empty(B * (nnz + spread), device=dev, dtype=torch.int64)
+    fv = torch.empty(B * (nnz + spread), device=dev); yy = torch.empty(B, device=dev)
+    ops.synth_sparse(rp, fid, fv, yy, nnz_mean=nnz, spread=spread, features=F, seed=5)
+    for _ in range(a.steps):
+        tr.step((rp, fid, fv, yy))
+elif a.config == "mnist_chain":           # the four-kernel tcgen05 chain (fused step off)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.0005, mode="sync", use_graph=False, fused_step=False)
+    x = torch.empty(100, 784, device=dev); y = torch.empty(100, device=dev, dtype=torch.int32)
+    ops.synth_mnist(x, y, seed=1)
+    for _ in range(a.steps):
+        tr.step(x, y)
+elif a.config == "wd":
+    F, B, nnz, spread = 1 << 22, 500, 100, 20
+    tr = SparseWideDeepTrainer(ctx, features=F, dim=128, lr=0.05, mode="async", use_graph=False)
     rp = torch.empty(B + 1, device=dev, dtype=torch.int32); fid = torch.empty(B * (nnz + spread), device=dev, dtype=torch.int64)
     fv = torch.empty(B * (nnz + spread), device=dev); yy = torch.empty(B, device=dev)
     ops.synth_sparse(rp, fid, fv, yy, nnz_mean=nnz, spread=spread, features=F, seed=5)

@@ -62,7 +62,7 @@ def main():
           "compare shares, not absolutes; the timed numbers are the CUDA-event ones in `bench_*.json`.",
           "`compute-sanitizer` is closed on this pool (the tool answered so; `gpurun_out/sanitizer_memcheck.log`), "
           "so memory safety rests on the bounded-wait traps, shape/alignment checks and the reference-comparison tests.", ""]
-    for cfg in ("mnist", "wide", "sparse"):
+    for cfg in ("mnist", "mnist_chain", "wide", "sparse", "wd"):
         rep = os.path.join(GP, f"prof_{cfg}.ncu-rep")
         if os.path.exists(rep):
             rows = ncu_raw(rep)
