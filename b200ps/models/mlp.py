@@ -150,17 +150,19 @@ class SigmoidMLP:
         return (store.world > 1 and len(store.pool.local_ranks) == 1 and g.t_ll_grads is not None and store.use_ll
                 and names == set(self.names()) and g.layout.offsets[self.W1] % 4 == 0)
 
-    def fused_push_step(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, rank: Optional[int] = None,
-                        row_offset: Optional[torch.Tensor] = None, batch: Optional[int] = None, stats_out=None,
-                        cursor: Optional[torch.Tensor] = None, cursor_step: int = 0, cursor_wrap: int = 1):
-        """Synchronous-replica step as ONE launch per rank: forward, backward, and the low-latency push
-        (gradient packets to the owners, reduce + SGD + publish, unpack) inside K13 — the fused
-        compute + collective form of example.py:110-123."""
+    def supports_fused_async(self, store) -> bool:
+        """Can the asynchronous worker step run entirely inside K13 (parameters read from, and updates added
+        to, the owners' masters)?  All four variables in one fp32 group with 4-aligned offsets."""
+        try:
+            g = store._group_of(self.W1)
+        except Exception:
+            return False
+        off = g.layout.offsets
+        return (g.master is None and {s.name for s in g.specs} == set(self.names())
+                and all(off[n] % 4 == 0 for n in (self.W1, self.W2, self.B1)))
+
+    def _push_tables(self, store, r: int, bufs: dict):
         from ..ops import native
-        B = x.shape[0] if row_offset is None else batch
-        r = store.pool.local_ranks[0] if rank is None else rank
-        bufs = self._buffers(B, x.device, r)
-        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
         if "push" not in bufs:
             g = store._group_of(self.W1)
             off = g.layout.offsets
@@ -170,9 +172,38 @@ class SigmoidMLP:
                 global_steps=native.ptr(store.t_gsteps), max_shard_elems=max(g.layout.max_shard, 8),
                 off_w1=off[self.W1], off_b1=off[self.B1], off_w2=off[self.W2], off_b2=off[self.B2],
                 world=store.world, rank=r)
+        return bufs["push"]
+
+    def fused_async_step(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, rank: Optional[int] = None,
+                         row_offset: Optional[torch.Tensor] = None, batch: Optional[int] = None, stats_out=None,
+                         cursor: Optional[torch.Tensor] = None, cursor_step: int = 0, cursor_wrap: int = 1):
+        """Asynchronous (Hogwild) worker step as ONE launch: parameters fetched from the owners' masters
+        inside the kernel (the pull fused into the first GEMM), ``-lr * g`` added into them unlocked, the
+        chief's ``global_step`` incremented — example.py:108,118 without a local parameter copy."""
+        B = x.shape[0] if row_offset is None else batch
+        r = store.pool.local_ranks[0] if rank is None else rank
+        bufs = self._buffers(B, x.device, r)
+        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
         ops.mlp_fused_step(x, labels, store.var(self.W1, r), store.var(self.B1, r), store.var(self.W2, r),
                            store.var(self.B2, r), loss=loss, correct=correct, batch=B, cursor=row_offset, lr=lr,
-                           cursor_rw=cursor, cursor_step=cursor_step, cursor_wrap=cursor_wrap, push=bufs["push"])
+                           cursor_rw=cursor, cursor_step=cursor_step, cursor_wrap=cursor_wrap,
+                           push=self._push_tables(store, r, bufs), hogwild=True)
+        return loss, correct
+
+    def fused_push_step(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, rank: Optional[int] = None,
+                        row_offset: Optional[torch.Tensor] = None, batch: Optional[int] = None, stats_out=None,
+                        cursor: Optional[torch.Tensor] = None, cursor_step: int = 0, cursor_wrap: int = 1):
+        """Synchronous-replica step as ONE launch per rank: forward, backward, and the low-latency push
+        (gradient packets to the owners, reduce + SGD + publish, unpack) inside K13 — the fused
+        compute + collective form of example.py:110-123."""
+        B = x.shape[0] if row_offset is None else batch
+        r = store.pool.local_ranks[0] if rank is None else rank
+        bufs = self._buffers(B, x.device, r)
+        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
+        ops.mlp_fused_step(x, labels, store.var(self.W1, r), store.var(self.B1, r), store.var(self.W2, r),
+                           store.var(self.B2, r), loss=loss, correct=correct, batch=B, cursor=row_offset, lr=lr,
+                           cursor_rw=cursor, cursor_step=cursor_step, cursor_wrap=cursor_wrap,
+                           push=self._push_tables(store, r, bufs))
         return loss, correct
 
     def evaluate(self, store, x: torch.Tensor, labels: torch.Tensor, rank: Optional[int] = None):

@@ -151,10 +151,11 @@ def mlp_tail(z2, b1, w2, b2, labels, *, loss_sum, correct=None, dz2=None, dw2=No
 
 def mlp_fused_step(x, labels, w1, b1, w2, b2, *, loss, correct=None, grads=None, lr=0.0, batch=None, cursor=None,
                    global_step=None, cursor_rw=None, cursor_step=0, cursor_wrap=1, grad_scale=None, loss_scale=None,
-                   push=None, stream=None):
+                   push=None, hogwild=False, stream=None):
     """Whole narrow-MLP training step in one launch (K13): see include/b200ps.h b200ps_mlp_fused_step.
     ``grads=None``: apply SGD in place (single replica); ``grads=(gw1, gb1, gw2, gb2)``: write gradients;
-    ``push=native.FusedPush(...)``: synchronous-replica push inside the launch (one rank per GPU)."""
+    ``push=native.FusedPush(...)``: synchronous-replica push inside the launch (one rank per GPU);
+    with ``hogwild=True`` the same tables serve the asynchronous in-kernel step (no local parameter copy)."""
     _cuda(x, labels, w1, b1, w2, b2)
     B = x.shape[0] if batch is None else batch
     D, H = w1.shape
@@ -164,7 +165,7 @@ def mlp_fused_step(x, labels, w1, b1, w2, b2, *, loss, correct=None, grads=None,
     gs = (1.0 / B) if grad_scale is None else grad_scale
     ls = (1.0 / B) if loss_scale is None else loss_scale
     g = grads or (None, None, None, None)
-    mode = 2 if push is not None else int(grads is None)
+    mode = (3 if hogwild else 2) if push is not None else int(grads is None)
     import ctypes
     check(native.load().b200ps_mlp_fused_step(
         ptr(x), ptr(labels), ptr(cursor), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(g[0]), ptr(g[1]), ptr(g[2]),

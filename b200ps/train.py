@@ -150,6 +150,9 @@ class MLPTrainer(_TrainerBase):
         self.store.initialize()
         # synchronous replicas, one rank per GPU: the push runs inside the step kernel (one launch per step)
         self.fused_push = self._want_fused_push and self.model.supports_fused_push(self.store)
+        # asynchronous workers: the whole Hogwild step (pull from the owners, compute, unlocked add) in one launch
+        self.fused_async = (self.fused and mode == "async" and os.environ.get("B200PS_FUSED_ASYNC", "1") != "0"
+                            and self.model.supports_fused_async(self.store))
         dev = self.device
         self.x = {r: torch.zeros(batch_size, self.model.in_dim, device=dev) for r in self.local_ranks}
         self.labels = {r: torch.zeros(batch_size, device=dev, dtype=torch.int32) for r in self.local_ranks}
@@ -167,6 +170,11 @@ class MLPTrainer(_TrainerBase):
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
             return self.model.fused_train_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
                                                batch=self.batch_size, stats_out=stats_out, **ck)
+        if self.fused_async:
+            ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
+                      cursor_wrap=cursor_kw.get("cursor_wrap", 1))
+            return self.model.fused_async_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                               batch=self.batch_size, stats_out=stats_out, **ck)
         if self.fused_push:
             ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
@@ -180,9 +188,15 @@ class MLPTrainer(_TrainerBase):
             self.opt.apply(st, **cursor_kw)
         return out
 
+    def _prepare(self):
+        """Refresh the worker's parameter view before a step (async pull; nothing to do when the step kernel
+        reads the owners' masters itself, or in sync mode where the push already broadcast)."""
+        if not self.fused_async:
+            self.opt.prepare(self.store)
+
     def _body(self):
         st = self.store
-        self.opt.prepare(st)
+        self._prepare()
         for r in self.local_ranks:
             self._losses[r], self._corrects[r] = self._one_step(r, self.x[r], self.labels[r])
         if self.mode == "sync" and len(self.local_ranks) > 1:
@@ -208,7 +222,7 @@ class MLPTrainer(_TrainerBase):
     def _body_resident(self):
         data, labels, n = self._ds
         r = self.local_ranks[0]
-        self.opt.prepare(self.store)             # async: refresh the peer-owned slices (no-op for sync)
+        self._prepare()                          # async: refresh the peer-owned slices (no-op for sync)
         self._losses[r], self._corrects[r] = self._one_step(r, data, labels, row_offset=self._cursor,
                                                             cursor=self._cursor, cursor_step=self.batch_size,
                                                             cursor_wrap=n)
@@ -286,7 +300,7 @@ class MLPTrainer(_TrainerBase):
 
             def body():
                 for i in range(K):
-                    trainer.opt.prepare(trainer.store)
+                    trainer._prepare()
                     trainer._one_step(r, x[i * B:(i + 1) * B], y[i * B:(i + 1) * B],
                                       stats_out=(words[i, 0:1], correct_words[i, 1:2]))
             return _capture(body, dev), (x, y)
@@ -340,6 +354,8 @@ class MLPTrainer(_TrainerBase):
         return done
 
     def evaluate(self, x: torch.Tensor, labels: torch.Tensor):
+        if self.fused_async:
+            self.store.pull()                    # the in-kernel Hogwild step keeps no local copy up to date
         return self.model.evaluate(self.store, x, labels, rank=self.local_ranks[0])
 
 

@@ -30,6 +30,13 @@
 // and a step costs two one-way NVLink latencies on top of the single-GPU step (protocol: ll_proto.cuh,
 // same landing buffers and epochs as b200ps_push_sync_ll, so the two can be mixed).
 //
+// In-kernel Hogwild (apply = 3, the reference's default asynchronous mode, example.py:108,118).  There is no
+// local copy of the parameters at all: phase A and the head fetch W1 / W2 / b1 / b2 straight from the fp32
+// masters of the ranks that own them (bulk copies and cp.async over peer-mapped pointers — the pull fused into
+// the first GEMM), and phase C adds -lr * gradient into those masters with fire-and-forget
+// red.global.add.v4.f32 over NVLink, unlocked; one atomicAdd_system on the chief's counter keeps global_step
+// counting every worker's update.  No barrier between ranks, one launch per worker step.
+//
 // fp32 FMA on the CUDA cores, exact fp32 accumulation in a fixed order: the step is bit-reproducible
 // and matches the reference's fp32 CPU arithmetic more closely than a tf32 tensor-core product.  A
 // tensor-core tile (tcgen05, M=128) would spend longer allocating TMEM and fetching its tensor maps
@@ -142,6 +149,9 @@ __device__ __forceinline__ void fs_send1(const FusedParams& p, const long long* 
   const int o = fs_owner(s_bounds, i);
   st_packet(p.ll_grads[o] + (long long)p.rank * p.max_shard + (i - s_bounds[o]), v, epoch);
 }
+__device__ __forceinline__ void fs_red1(const FusedParams& p, const long long* s_bounds, long long i, float g) {
+  red_add_f32_sys(p.masters[fs_owner(s_bounds, i)] + i, -p.lr * g);
+}
 __device__ __forceinline__ void fs_send4(const FusedParams& p, const long long* s_bounds, long long i, const float (&v)[4], uint32_t epoch) {
   const int o = fs_owner(s_bounds, i);      // owner ranges are multiples of 8: a 4-aligned group has one owner
   uint2* dst = p.ll_grads[o] + (long long)p.rank * p.max_shard + (i - s_bounds[o]);
@@ -183,9 +193,10 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   const int row0 = p.cursor ? __ldcg(p.cursor) : 0;      // consumed late: the parameter fetches below go out first
   __shared__ long long s_bounds[kMaxWorld + 1];
   uint32_t epoch = 0;
-  if (p.apply == 2) {
+  if (p.apply >= 2) {
     if (tid <= p.world) s_bounds[tid] = p.bounds[tid];
-    epoch = __ldcg(p.pads[p.rank] + kSlotEpoch) + 1;       // made visible to the rest of the CTA by the barriers below
+    if (p.apply == 2) epoch = __ldcg(p.pads[p.rank] + kSlotEpoch) + 1;
+    __syncthreads();
   }
   if (cta == 0 && tid == 0) p.bar[1] = 0;         // nobody can reach barrier 2 before we reach barrier 1
 
@@ -199,7 +210,20 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   float* s_ws = s_u + kFsRowTile * p.xpitch;      // [ks][H]
   if (in_a && tid == 0) {                         // W1[k0 : k0 + kw, :] is one contiguous run: a single bulk copy
     mbar_arrive_expect_tx(&s_mbar[0], (uint32_t)(kw * H) * 4u);
-    bulk_load_g2s(s_ws, p.w1 + (size_t)k0 * H, (uint32_t)(kw * H) * 4u, &s_mbar[0]);
+    if (p.apply == 3) {                           // ... from the masters of the owner(s) of that run of the flat space
+      long long i = p.off_w1 + (long long)k0 * H;
+      const long long end = i + (long long)kw * H;
+      float* dst = s_ws;
+      while (i < end) {
+        const int o = fs_owner(s_bounds, i);
+        const long long seg = min(end, s_bounds[o + 1]) - i;
+        bulk_load_g2s(dst, p.masters[o] + i, (uint32_t)seg * 4u, &s_mbar[0]);
+        dst += seg;
+        i += seg;
+      }
+    } else {
+      bulk_load_g2s(s_ws, p.w1 + (size_t)k0 * H, (uint32_t)(kw * H) * 4u, &s_mbar[0]);
+    }
   }
   const float* xb = p.x + (size_t)row0 * D;
   if (in_a) {
@@ -213,7 +237,22 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
     }
   }
   cp_async_commit();
-  if (cta < p.NT) {
+  if (cta < p.NT && p.apply == 3) {               // head constants from their owners' masters (4-aligned groups)
+#pragma unroll 1
+    for (int i = tid; i < (H * C) >> 2; i += kFsThreads) {
+      const long long g = p.off_w2 + 4 * i;
+      cp_async_16(s_w2raw + 4 * i, p.masters[fs_owner(s_bounds, g)] + g);
+    }
+    if (tid < (H >> 2)) {
+      const long long g = p.off_b1 + 4 * tid;
+      cp_async_16(s_b1 + 4 * tid, p.masters[fs_owner(s_bounds, g)] + g);
+    }
+    if (tid < kFsCP) {
+      const long long g = p.off_b2 + tid;
+      if (tid < C) cp_async_4(s_b2 + tid, p.masters[fs_owner(s_bounds, g)] + g);
+      else s_b2[tid] = 0.f;
+    }
+  } else if (cta < p.NT) {
 #pragma unroll 1
     for (int i = tid; i < (H * C) >> 2; i += kFsThreads) cp_async_16(s_w2raw + 4 * i, p.w2 + 4 * i);
     if (tid < (H >> 2)) cp_async_16(s_b1 + 4 * tid, p.b1 + 4 * tid);
@@ -221,6 +260,8 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
       if (tid < C) cp_async_4(s_b2 + tid, p.b2 + tid);
       else s_b2[tid] = 0.f;
     }
+  }
+  if (cta < p.NT) {
     if (tid < kFsWarps) {
       const int r = cta * kFsWarps + tid;
       if (r < B) cp_async_4(s_lab + tid, p.labels + row0 + r);
@@ -504,7 +545,7 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
           w.x = fmaf(-p.lr, acc[0][0], w.x); w.y = fmaf(-p.lr, acc[0][1], w.y);
           w.z = fmaf(-p.lr, acc[0][2], w.z); w.w = fmaf(-p.lr, acc[0][3], w.w);
           *reinterpret_cast<float4*>(p.w1 + off) = w;
-        } else if (p.apply == 2) {
+        } else if (p.apply >= 2) {
           // staged: the CTA's 8 x H block is one contiguous run of the flat gradient and leaves below as
           // coalesced packets (32 lanes x 8 bytes per store instruction)
           *reinterpret_cast<float4*>(s_w1c + rg * H + cg * 4) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
@@ -513,11 +554,20 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
         }
       }
     }
-    if (p.apply == 2) {
+    if (p.apply >= 2) {
       __syncthreads();
       const int n = min(kFsDRows, D - d0) * H;
       const long long base = p.off_w1 + (long long)d0 * H;
-      for (int j = tid; j < n; j += kFsThreads) fs_send1(p, s_bounds, base + j, s_w1c[j], epoch);
+      if (p.apply == 2) {
+        for (int j = tid; j < n; j += kFsThreads) fs_send1(p, s_bounds, base + j, s_w1c[j], epoch);
+      } else {                                    // Hogwild: -lr * dW1 added into the owners' masters, unlocked
+        for (int j = tid; j < (n >> 2); j += kFsThreads) {
+          const float4 g = *reinterpret_cast<const float4*>(s_w1c + 4 * j);
+          const long long i = base + 4 * j;
+          red_add_v4f32_sys(p.masters[fs_owner(s_bounds, i)] + i,
+                            make_float4(-p.lr * g.x, -p.lr * g.y, -p.lr * g.z, -p.lr * g.w));
+        }
+      }
     }
   } else {
     cp_async_wait<0>();
@@ -537,16 +587,19 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
       if (o < H * C) {
         if (p.apply == 1) p.w2[o] = fmaf(-p.lr, t, p.w2[o]);
         else if (p.apply == 2) fs_send1(p, s_bounds, p.off_w2 + o, t, epoch);
+        else if (p.apply == 3) fs_red1(p, s_bounds, p.off_w2 + o, t);
         else p.gw2[o] = t;
       } else if (o < H * C + C) {
         const int c = o - H * C;
         if (p.apply == 1) p.b2[c] = fmaf(-p.lr, t, p.b2[c]);
         else if (p.apply == 2) fs_send1(p, s_bounds, p.off_b2 + c, t, epoch);
+        else if (p.apply == 3) fs_red1(p, s_bounds, p.off_b2 + c, t);
         else p.gb2[c] = t;
       } else if (o < P - 2) {
         const int h = o - H * C - C;
         if (p.apply == 1) p.b1[h] = fmaf(-p.lr, t, p.b1[h]);
         else if (p.apply == 2) fs_send1(p, s_bounds, p.off_b1 + h, t, epoch);
+        else if (p.apply == 3) fs_red1(p, s_bounds, p.off_b1 + h, t);
         else p.gb1[h] = t;
       } else if (o == P - 2) {
         if (p.loss) *p.loss = t * p.loss_scale;
@@ -559,6 +612,13 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   if (p.apply == 1) {
     if (cta == 0 && tid == 0) {
       if (p.global_step) *p.global_step += 1ull;
+      if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
+    }
+    return;
+  }
+  if (p.apply == 3) {
+    if (cta == 0 && tid == 0) {
+      if (p.global_steps) atomicAdd_system(p.global_steps[0], 1ull);     // the chief's counter sees every worker's update
       if (p.cursor_rw) *p.cursor_rw = (*p.cursor_rw + p.cursor_step) % p.cursor_wrap;
     }
     return;
@@ -656,7 +716,10 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
                  "mlp_fused_step: needs B <= 128, H <= 128 (multiple of 4), C <= 16, D multiple of 8 "
                  "(got B=%d D=%d H=%d C=%d)", B, D, H, C);
   B200PS_REQUIRE(H * C <= kFsMaxPer * kFsThreads, "mlp_fused_step: H*C too large");
-  B200PS_REQUIRE(apply >= 0 && apply <= 2, "mlp_fused_step: apply must be 0, 1 or 2");
+  B200PS_REQUIRE(apply >= 0 && apply <= 3, "mlp_fused_step: apply must be 0, 1, 2 or 3");
+  B200PS_REQUIRE(apply != 3 || (push && push->masters && push->bounds && push->world >= 1 && push->world <= kMaxWorld &&
+                                push->off_w1 % 4 == 0 && push->off_w2 % 4 == 0 && push->off_b1 % 4 == 0),
+                 "mlp_fused_step: apply == 3 needs masters/bounds and 4-aligned variable offsets");
   B200PS_REQUIRE(apply != 0 || (gw1 && gb1 && gw2 && gb2), "mlp_fused_step: gradient outputs needed when apply == 0");
   B200PS_REQUIRE(apply != 2 || (push && push->pads && push->masters && push->bounds && push->ll_grads && push->ll_params &&
                                 push->world >= 2 && push->world <= kMaxWorld && push->rank >= 0 && push->rank < push->world &&
@@ -672,7 +735,7 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   p.timing = g_fs_timing;
   p.pads = nullptr; p.masters = nullptr; p.bounds = nullptr; p.ll_grads = nullptr; p.ll_params = nullptr;
   p.global_steps = nullptr; p.max_shard = 0; p.off_w1 = p.off_b1 = p.off_w2 = p.off_b2 = 0; p.world = 1; p.rank = 0;
-  if (apply == 2) {
+  if (apply >= 2) {
     p.pads = push->pads; p.masters = push->masters; p.bounds = reinterpret_cast<const long long*>(push->bounds);
     p.ll_grads = reinterpret_cast<uint2* const*>(push->ll_grads);
     p.ll_params = reinterpret_cast<uint2* const*>(push->ll_params);

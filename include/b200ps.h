@@ -198,7 +198,10 @@ int b200ps_cast_f32_bf16(const float* in, void* out, uint64_t n, b200ps_stream_t
  * also *global_step += 1 and the cursor advance), the gradients for a following push (apply = 0), or the
  * whole synchronous-replica push inside the same launch (apply = 2: gradients leave as {value, epoch}
  * packets for their owners over NVLink, owners reduce + apply + publish, replicas unpack; one rank per
- * GPU, every rank launches the same step; mixes freely with b200ps_push_sync_ll on the same tables).
+ * GPU, every rank launches the same step; mixes freely with b200ps_push_sync_ll on the same tables), or the
+ * asynchronous (Hogwild) worker step with no local parameter copy (apply = 3: parameters are fetched from
+ * the owners' masters inside the launch, -lr * gradient is added into them with unlocked red.add over NVLink,
+ * the chief's global_step counts the update; needs only masters, bounds, global_steps, world and the offsets).
  * Three phases of one co-resident grid separated by two device-wide barriers; exact fp32 FMA in a
  * fixed order (bit-reproducible).  x/labels may be a resident dataset addressed through the device
  * scalar `cursor` (rows [*cursor, *cursor+B)).  Limits: B <= 128, H <= 128 and H % 4 == 0, C <= 16,

@@ -69,6 +69,7 @@ def main():
 
     # ---- async MLP (round-robin placement): the chief's counter sees every worker's update
     tr2 = MLPTrainer(ctx, batch_size=100, lr=0.01, mode="async", use_graph=True, placement="round_robin_variable")
+    res["async_in_kernel"] = bool(tr2.fused_async)
     l2 = []
     for i in range(40):
         tr2.step(x[i % 20], y[i % 20])

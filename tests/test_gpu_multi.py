@@ -33,6 +33,7 @@ def test_multi_gpu_trainers(native_lib, tmp_path):
     assert res["sync_fused_push_used"] and res["sync_fused_push_bitwise"], res
     assert res["sync_chain_close"] < 5e-3 and res["sync_steps_all"] == [60, 60], res
     assert res["async_global_step"] == 40 * n and res["async_loss"][1] < res["async_loss"][0]
+    assert res["async_in_kernel"]              # the Hogwild step ran as one launch against the owners' masters
     assert res["wide_digests_equal"] and res["wide_loss"][1] < res["wide_loss"][0]
     assert res["wide_fused_pull"] == (512 % (64 * n) == 0)
     assert res["sparse_async_global_step"] == 10 * n and res["sparse_sync_global_step"] == 10
