@@ -13,12 +13,16 @@ def _mnist_batches(n, B=100, seed=1, offset=0):
     return x.view(n, B, 784), y.view(n, B)
 
 
-def test_mlp_step_matches_reference_math(native_lib):
+@pytest.mark.parametrize("mode,fused", [("sync", True), ("sync", False), ("async", True), ("async", False)])
+def test_mlp_step_matches_reference_math(native_lib, mode, fused):
+    """One step of every single-replica path — one-launch K13 (in-place SGD / in-kernel Hogwild) and the
+    tcgen05 chain with a separate push — against the fp32 restatement of example.py:95-118."""
     from b200ps.models.mlp import mlp_reference_step
     from b200ps.parallel.context import init_from_env
     from b200ps.train import MLPTrainer
     ctx = init_from_env(virtual_world=1)
-    tr = MLPTrainer(ctx, batch_size=100, lr=0.0005, mode="sync", use_graph=False)
+    tr = MLPTrainer(ctx, batch_size=100, lr=0.0005, mode=mode, use_graph=False, fused_step=fused)
+    assert tr.fused == fused and tr.fused_apply == (fused and mode == "sync") and tr.fused_async == (fused and mode == "async")
     xs, ys = _mnist_batches(1)
     params = {k: v.clone() for k, v in tr.store.state_dict().items()}
     loss_ref, grads_ref, correct_ref = mlp_reference_step(params, xs[0].cpu(), ys[0].cpu())
