@@ -1,0 +1,2 @@
+
+from .accuracy import StreamingAccuracy, accuracy  # noqa: F401

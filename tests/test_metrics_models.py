@@ -127,3 +127,17 @@ def test_wide_deep_reference_matches_autograd():
     assert abs(l2.item() - loss.item()) < 1e-12 and torch.allclose(pred, torch.sigmoid(z.detach()))
     assert torch.allclose(gr["W"], W.grad[:, 0]) and torch.allclose(gr["E"], E.grad)
     assert torch.allclose(gr["w2"], w2.grad[:, 0]) and torch.allclose(gr["b"], b.grad[0])
+
+
+def test_accuracy_metric_one_hot_and_streaming():
+    import torch
+    from b200ps.metrics import StreamingAccuracy, accuracy
+    logits = torch.tensor([[0.1, 0.9, 0.0], [0.5, 0.5, 0.1], [0.0, 0.2, 0.7], [1.0, 0.0, 0.0]])
+    labels = torch.tensor([1, 0, 1, 0])
+    assert accuracy(logits, labels) == 0.75                                  # tie -> lowest index (row 1 correct)
+    assert accuracy(logits, torch.nn.functional.one_hot(labels, 3)) == 0.75  # the reference feeds one-hot y_
+    m = StreamingAccuracy()
+    m.update_from_logits(logits[:2], labels[:2]); m.update(torch.tensor([1], dtype=torch.int32), 2)
+    assert m.result() == 0.75
+    m.reset(); m.update(3, 4)
+    assert m.result() == 0.75
