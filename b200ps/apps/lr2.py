@@ -60,6 +60,9 @@ flags.DEFINE_integer("deep_dim", 0, "0 = plain LR (lr2.py); 128/256/512 adds the
                      "deep part sketched at lr2_debug.py:423-428")
 flags.DEFINE_float("init_stddev", 0.0, "stddev of the weight initialiser; 0 = the script's default (1.0 for LR as in "
                    "lr2.py:384, 0.01 with --deep_dim as in lr2_debug.py:288-289)")
+flags.DEFINE_boolean("native_loader", False, "GPU backend: read, sample and batch the train files with the native loader "
+                     "threads (packed pinned batches -> one H2D copy + one graph launch per step) instead of the "
+                     "Python DataProvider")
 flags.DEFINE_integer("synthetic_rows", 4000, "rows per synthetic file when --train/--test is 'synthetic'")
 
 
@@ -255,6 +258,24 @@ def main(argv=None) -> int:
         info("Start train ...")
         step_num, iter_num = 0, 0
         info("num_epochs: %d" % num_epochs)
+        if gpu and FLAGS.native_loader:
+            # the input side of lr2.py:87-169 in native threads: thread_num readers over this worker's files,
+            # Bernoulli sampling, batches of exactly batch_size rows in pinned buffers
+            from ..data.native_loader import NativeLibsvmLoader
+            files = DataProvider.GetFileList(FLAGS.train, num_workers, FLAGS.task_index)
+            while iter_num < num_epochs:
+                loader = NativeLibsvmLoader(files, FLAGS.batch_size, threads=FLAGS.thread_num,
+                                            sampling_rate=FLAGS.train_sampling_rate, epochs=1, seed=FLAGS.seed + iter_num)
+                base = step_num
+
+                def on_loss(i, loss, base=base, epoch=iter_num):
+                    if (base + i + 1) % trace_step_interval == 0:
+                        Test(runner, store, epoch, base + i + 1, test_samples)
+                step_num += trainer.fit_from_loader(loader, on_loss=on_loss)
+                info("native loader: %s" % loader.stats())
+                loader.close()
+                Test(runner, store, iter_num, step_num, test_samples)
+                iter_num += 1
         while iter_num < num_epochs:
             data_provider.Shuffle()
             try:

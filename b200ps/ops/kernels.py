@@ -19,7 +19,7 @@ __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
     "cast_f32_bf16", "sparse_lr", "sparse_wd", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
-    "device_ptr_table", "signal_pad_words",
+    "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
 
@@ -294,6 +294,12 @@ def auc_hist(pred, labels, thresholds, hist_pos, hist_neg, stream=None):
     check(native.load().b200ps_auc_hist(ptr(pred), ptr(labels), pred.numel(), ptr(thresholds),
                                         thresholds.numel(), ptr(hist_pos), ptr(hist_neg),
                                         stream_ptr(stream)), "auc_hist")
+
+
+def copy_words(dst, src, n_words=None, stream=None):
+    """``n_words`` 32-bit words from a device tensor into a device or pinned+mapped host tensor, as a kernel."""
+    n = (src.numel() * src.element_size() // 4) if n_words is None else n_words
+    check(native.load().b200ps_copy_words(ptr(dst), ptr(src), n, stream_ptr(stream)), "copy_words")
 
 
 def signal_pad_words() -> int:

@@ -495,6 +495,66 @@ class SparseLRTrainer(_TrainerBase):
     def predict(self, batch):
         return self.model.predict(self.store, batch)
 
+    # -- packed batches (b200ps.data.native_loader): one pinned buffer per batch, one H2D copy, one graph
+    def host_feeder(self, layout, slots: int = 4):
+        """A ``HostFeeder`` whose unit is one training step on a *packed batch* (``PackedLayout``): the
+        buffer is copied to a staging slot on the copy stream, the slot's captured step graph reads
+        ``row_ptr | fid | fval | labels`` at the layout's fixed offsets, and the loss lands in pinned host
+        memory.  ``submit(packed_uint8_tensor).result()`` is the step's loss."""
+        from . import ops
+        from .runtime import HostFeeder
+        dev = self.device
+        trainer = self
+
+        def make_slot(slot, result):
+            staging = torch.zeros(layout.bytes, dtype=torch.uint8, device=dev)
+            batch = layout.views(staging)
+            if slot == 0:
+                trainer.model.predict(trainer.store, batch)      # loads the kernel before any capture (no update)
+                torch.cuda.synchronize(dev)
+
+            def body():
+                trainer._eager(batch)
+                ops.copy_words(result, trainer._last, 1)
+            return _capture(body, dev), (staging,)
+
+        f = HostFeeder(make_slot, (layout.bytes,), 1, slots=slots, decode=lambda out: float(out[0]))
+        f.layout = layout
+        return f
+
+    def fit_from_loader(self, loader, max_steps: Optional[int] = None, on_loss=None, feeder=None) -> int:
+        """Drain a ``NativeLibsvmLoader`` through a feeder: the loader's reader threads parse and batch, each
+        packed batch costs one H2D copy and one graph launch, losses come back through ``on_loss(step, loss)``.
+        Returns the number of steps.  (The training loop of lr2.py:434-451 without a Python batch formatter.)"""
+        f = feeder or getattr(self, "_loader_feeder", None)
+        if f is None or f.layout != loader.layout:
+            f = self._loader_feeder = self.host_feeder(loader.layout, slots=4)
+        pending, steps = [], 0
+        # batches in flight are ring buffers the reader threads cannot reuse: leave one per reader plus one
+        depth = max(1, min(f.slots - 1, loader.ring - loader.threads - 1))
+
+        def drain(n_keep):
+            nonlocal steps
+            while len(pending) > n_keep:
+                ticket, batch = pending.pop(0)
+                loss = ticket.result()
+                batch.release()                      # the H2D copy of this buffer has completed
+                if on_loss is not None:
+                    on_loss(steps, loss)
+                steps += 1
+
+        submitted = 0
+        while max_steps is None or submitted < max_steps:
+            batch = loader.next()
+            if batch is None:
+                break
+            pending.append((f.submit(batch.tensor), batch))
+            submitted += 1
+            drain(depth)
+        drain(0)
+        self.local_step += steps
+        return steps
+
 
 class SparseWideDeepTrainer(SparseLRTrainer):
     """The wide & deep extension of the LR trainer (lr2_debug.py:423-428): same step API and modes,

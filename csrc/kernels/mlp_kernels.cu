@@ -845,3 +845,24 @@ extern "C" int b200ps_linreg_fwd_bwd(const float* x, const float* y, const float
   B200PS_LAUNCH_CHECK();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------
+// copy_words: n 32-bit words device -> (possibly pinned, device-mapped host) memory as a graph-capturable
+// kernel node: how a step graph delivers its loss into a HostFeeder result block without a memcpy node.
+// ------------------------------------------------------------------------------------
+namespace b200ps {
+__global__ void copy_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, long long n) {
+  pdl_wait();
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = __ldcg(src + i);
+}
+}  // namespace b200ps
+
+extern "C" int b200ps_copy_words(void* dst, const void* src, int64_t n_words, b200ps_stream_t stream) {
+  B200PS_REQUIRE(dst && src && n_words > 0, "copy_words: bad arguments");
+  const int ctas = (int)std::min<long long>((n_words + 255) / 256, sm_count());
+  B200PS_CUDA_CHECK(launch_pdl(copy_words_kernel, dim3(ctas), dim3(256), 0, as_stream(stream),
+                               static_cast<uint32_t*>(dst), static_cast<const uint32_t*>(src), (long long)n_words));
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}

@@ -329,6 +329,8 @@ int b200ps_host_step(void* dst0, const void* src0, uint64_t bytes0, void* dst1, 
  * results (loss words) directly into the slot's pinned, device-mapped result block
  * (b200ps_feeder_result_ptr), so no D2H copy is queued.  wait() blocks on one unit only.  Only the
  * last `slots` tickets can be waited for.  Not thread-safe: one submitting thread per feeder. */
+/* n 32-bit words device -> device or pinned+mapped host memory, as a kernel (graph-capturable result delivery). */
+int b200ps_copy_words(void* dst, const void* src, int64_t n_words, b200ps_stream_t stream);
 int b200ps_feeder_create(void** feeder, int32_t slots, uint64_t bytes0, uint64_t bytes1, uint64_t result_bytes);
 int b200ps_feeder_result_ptr(void* feeder, int32_t slot, void** ptr);
 int b200ps_feeder_bind(void* feeder, int32_t slot, void* graph_exec, void* dst0, void* dst1);
@@ -347,6 +349,26 @@ int b200ps_event_destroy(void* ev);
  * ---------------------------------------------------------------------------------- */
 /* CRC-32C used by tfevents / tensor-bundle files (example.py:154, model_export.py:53). */
 uint32_t b200ps_crc32c_extend(uint32_t init_crc, const void* data, uint64_t n);
+/* Native batch loader (the LoadDataThread / FIFOQueue / tf.train.batch path of lr2.py:87-169, natively):
+ * `threads` reader threads take files[t::threads], parse libsvm lines, keep each with probability
+ * `sampling_rate`, and publish *packed batches* of exactly `batch_rows` rows into a ring of `ring`
+ * buffers (pinned when `pinned` and a CUDA device exists).  A packed batch = 64-byte header (magic, rows,
+ * nnz, capacities, section offsets, epoch, thread, sequence number) + row_ptr int32[rows+1] + fid
+ * int64[cap_nnz] + fval f32[cap_nnz] + labels f32[rows], sections 16-byte aligned at fixed offsets
+ * (b200ps_packed_layout), so ONE H2D copy feeds b200ps_sparse_lr / b200ps_sparse_wd and a captured graph
+ * can keep its device pointers.  epochs <= 0 loops over the files forever (queue mode).
+ * next(): 0 = batch, 1 = end of data, 2 = timeout.  Rows whose non-zeros would overflow cap_nnz and the
+ * incomplete last batch of each thread are dropped and counted (b200ps_loader_stats). */
+int b200ps_loader_create(void** loader, const char* const* files, int32_t nfiles, int32_t threads,
+                         int32_t batch_rows, int64_t cap_nnz, int32_t ring, double sampling_rate, uint64_t seed,
+                         int32_t epochs, int32_t pinned);
+int b200ps_loader_layout(void* loader, int64_t* out7, int32_t* pinned);
+int b200ps_packed_layout(int64_t batch_rows, int64_t cap_nnz, int64_t* out7);
+int b200ps_loader_next(void* loader, void** buf, int32_t timeout_ms);
+int b200ps_loader_release(void* loader, void* buf);
+int b200ps_loader_stats(void* loader, int64_t* out7);
+int b200ps_loader_destroy(void* loader);
+
 /* libsvm text -> CSR (lr2.py:57-84).  Count first, then parse into caller-sized arrays.
  * parse returns 0 or -(1-based line number) of the first malformed line. */
 int b200ps_libsvm_count(const char* buf, uint64_t len, uint64_t* rows, uint64_t* nnz);

@@ -163,3 +163,56 @@ def test_gfile_hdfs_mapping(tmp_path, monkeypatch):
     monkeypatch.setenv("B200PS_HDFS_ROOT", str(tmp_path))
     assert libsvm.count_lines("hdfs://localhost:9000/user/part-0") == 2
     assert libsvm.list_files(str(tmp_path / "user")) == [str(tmp_path / "user" / "part-0")]
+
+
+def test_native_loader_packed_batches_match_python_parser(tmp_path):
+    """csrc/data/loader.cpp: every kept line lands in exactly one packed batch with the values the Python
+    parser gives; thread sharding files[t::threads]; incomplete final batches are dropped and counted."""
+    import numpy as np
+    from b200ps.data.libsvm import Sample
+    from b200ps.data.native_loader import NativeLibsvmLoader, PackedLayout
+    from b200ps.data.synthetic import write_libsvm_files
+    files = write_libsvm_files(str(tmp_path / "train"), 3, 130, nnz_mean=12, spread=4, features=5000, seed=3)
+    # a few awkward lines: tabs, CRLF, exponent notation, a malformed one, a too-short one, no trailing newline
+    with open(files[0], "a") as f:
+        f.write("1\t7:0.5\t9:1e-3\r\n0 3:2 4:.25\nbroken line\n\n1 11:3.125")
+    want = {}
+    for path in files:
+        for line in open(path):
+            if len(line.strip()) < 2 or line.startswith("broken"):
+                continue
+            smp = Sample().parse_line_libsvm(line)
+            want[(smp.label, tuple(smp.indices))] = np.asarray(smp.values, dtype=np.float32)
+    B = 50
+    loader = NativeLibsvmLoader(files, batch_size=B, threads=2, max_nnz_per_row=40, ring=4, epochs=1, pinned=False)
+    got, seqs, threads_seen = 0, [], set()
+    for batch in loader:
+        rp, fid, fval, y = (a.numpy() for a in batch.arrays())
+        assert batch.rows == B and rp[0] == 0 and rp[-1] == batch.nnz == fid.size
+        seqs.append(batch.seq); threads_seen.add(batch.thread)
+        for i in range(B):
+            key = (int(y[i]), tuple(int(v) for v in fid[rp[i]:rp[i + 1]]))
+            np.testing.assert_allclose(fval[rp[i]:rp[i + 1]], want[key], rtol=1e-6)
+            got += 1
+    st = loader.stats()
+    assert st["malformed"] == 1 and st["kept"] == len(want) == 3 * 130 + 3
+    assert got == st["batches"] * B and got + st["dropped_incomplete_batch_rows"] == st["kept"]
+    assert sorted(seqs) == list(range(st["batches"])) and threads_seen == {0, 1}
+    loader.close()
+    # sampling: roughly half of the lines survive; epochs=2 doubles the data; the nnz cap drops rows
+    loader = NativeLibsvmLoader(files, batch_size=10, threads=3, epochs=2, sampling_rate=0.5, seed=7, pinned=False)
+    n = sum(b.rows for b in loader)
+    st = loader.stats()
+    assert st["lines"] == 2 * (3 * 130 + 4) and abs(st["kept"] / st["lines"] - 0.5) < 0.08 and n <= st["kept"]
+    loader.close()
+    loader = NativeLibsvmLoader(files[:1], batch_size=10, threads=1, cap_nnz=60, pinned=False)
+    assert sum(1 for _ in loader) == 0               # 10 rows of ~12 non-zeros never fit 60: nothing is published,
+    st = loader.stats()                              # the rows are counted, and the loader still terminates
+    assert st["dropped_nnz_cap"] > 0 and st["kept"] + st["dropped_nnz_cap"] + st["malformed"] == st["lines"]
+    loader.close()
+    # pack(): the same layout from arrays (what the benchmark and the tests use to feed HostFeeder)
+    lay = PackedLayout.make(4, 16)
+    buf = lay.pack(np.array([0, 2, 2, 5, 6]), np.arange(6) * 10, np.arange(6) / 4, np.array([1, 0, 0, 1]), pin=False)
+    rp, fid, fval, y = lay.views(buf)
+    assert rp.tolist() == [0, 2, 2, 5, 6] and fid[:6].tolist() == [0, 10, 20, 30, 40, 50] and y.tolist() == [1, 0, 0, 1]
+    assert lay.off_fid % 16 == 0 and lay.off_fval % 16 == 0 and lay.off_labels % 16 == 0 and lay.bytes % 16 == 0

@@ -306,3 +306,35 @@ def test_sparse_wide_deep_trainer_learns_and_checkpoints(native_lib, tmp_path):
     tr2.store.load_state_dict({k: torch.as_tensor(v) for k, v in back.items()})
     p1, _ = tr.predict(batches[33]); p2, _ = tr2.predict(batches[33])
     assert torch.equal(p1, p2)
+
+
+def test_native_loader_feeds_sparse_trainer(native_lib, tmp_path):
+    """files -> native reader thread -> packed pinned batches -> HostFeeder (one H2D copy + one graph per step):
+    same losses and weights as formatting the same lines in Python and stepping batch by batch."""
+    import numpy as np
+    from b200ps.data.libsvm import Sample
+    from b200ps.data.native_loader import NativeLibsvmLoader
+    from b200ps.data.synthetic import write_libsvm_files
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import SparseLRTrainer
+    F, B = 5000, 100
+    files = write_libsvm_files(str(tmp_path / "train"), 2, 450, nnz_mean=20, spread=5, features=F, seed=3)
+    # sync mode: forward on frozen weights, then the update — reproducible up to the order of float atomics
+    a = SparseLRTrainer(init_from_env(virtual_world=1), features=F, lr=0.5, mode="sync")
+    b = SparseLRTrainer(init_from_env(virtual_world=1), features=F, lr=0.5, mode="sync", use_graph=False)
+    loader = NativeLibsvmLoader(files, batch_size=B, threads=1, max_nnz_per_row=32, epochs=2)
+    assert loader.pinned
+    la = []
+    steps = a.fit_from_loader(loader, on_loss=lambda i, v: la.append(v))
+    assert steps == 2 * (900 // B) == loader.stats()["batches"] and a.global_step == steps
+    samples = [Sample().parse_line_libsvm(l) for f in files for l in open(f)]
+    lb = []
+    for _ in range(2):
+        for lo in range(0, 900 - B + 1, B):
+            batch = tuple(torch.from_numpy(x).to(DEV) for x in Sample.format_samples_csr(samples[lo:lo + B]))
+            b.step(batch)
+            lb.append(b.read_loss())
+    np.testing.assert_allclose(la, lb, rtol=1e-4, atol=1e-5)
+    wa, wb = a.store.state_dict()[a.model.W], b.store.state_dict()[b.model.W]
+    assert torch.allclose(wa, wb, rtol=1e-4, atol=1e-5)
+    loader.close()
