@@ -49,11 +49,19 @@ def wide_deep_reference(W, E, w2, b, row_ptr, fid, fval, labels, train: bool = T
 
 class SparseWideDeep:
     W, E, W2, Bn = "weights/Variable", "deep/weights", "deep/weights_1", "bias/Variable"
+    P, P2 = "_pending/coefficients", "_pending/deep_weights_1"      # scratch tables of the deferred update
 
-    def __init__(self, features: int, dim: int = 128, wide: bool = True, stddev: float = 0.01):
+    def __init__(self, features: int, dim: int = 128, wide: bool = True, stddev: float = 0.01,
+                 deferred: Optional[bool] = None):
+        """``deferred`` (opt-in, also ``B200PS_WD_DEFERRED=1``): workers push one scalar coefficient
+        per non-zero into a pending table and the owner of a shard folds them into W and E before its next
+        step (the embedding update is rank one, dE[fid,:] = c[fid] * w2) — 4 instead of 516 bytes of remote
+        atomics per non-zero."""
+        import os
         if dim not in (128, 256, 512):
             raise ValueError("SparseWideDeep: dim must be 128, 256 or 512")
         self.features, self.dim, self.wide, self.stddev = int(features), int(dim), wide, stddev
+        self.deferred = (os.environ.get("B200PS_WD_DEFERRED", "0") != "0") if deferred is None else bool(deferred)
         self._bufs: Dict[int, dict] = {}
 
     def register(self, store) -> None:
@@ -64,6 +72,11 @@ class SparseWideDeep:
         store.register(self.E, (self.features, self.dim), group="sparse", init="normal", stddev=self.stddev)
         store.register(self.W2, (self.dim, 1), group="sparse", init="normal", stddev=self.stddev)
         store.register(self.Bn, (1,), group="fp32", init="zeros")
+        if self.deferred and hasattr(store, "sparse_shard") and store.placement == "flat_shard":
+            # GPU store with row sharding only (the pending tables must be sharded exactly like W / E);
+            # the gloo path and whole-variable placement apply their updates directly
+            store.register(self.P, (self.features, 1), group="sparse", init="zeros", trainable=False)
+            store.register(self.P2, (self.dim, 1), group="sparse", init="zeros", trainable=False)
 
     def names(self):
         return ((self.W,) if self.wide else ()) + (self.E, self.W2, self.Bn)
@@ -87,14 +100,36 @@ class SparseWideDeep:
                 emb_table=e.table, emb_rows_per_shard=e.rows_per_shard, dim=self.dim,
                 w2_table=w2.table, w2_rows_per_shard=w2.rows_per_shard,
                 bias=tensor_from_ptr(store.master_address(self.Bn), 4, store.device).view(torch.float32))
+            if self.deferred and self.P in store.sparse:
+                pe, p2 = store.sparse_var(self.P), store.sparse_var(self.P2)
+                self._tab.update(pend_table=pe.table, pend_rows_per_shard=pe.rows_per_shard,
+                                 pend2_table=p2.table, pend2_rows_per_shard=p2.rows_per_shard)
             self._gs0 = tensor_from_ptr(store.gstep.ptrs[0], 8, store.device).view(torch.int64)
         return self._tab
+
+    def flush(self, store, ranks=None) -> None:
+        """Deferred mode: fold the coefficients that have landed in the pending shards of ``ranks`` (default:
+        every rank of this process) into their rows of W / E (phase 1, all ranks) and then their slices of w2
+        (phase 2), so that every row update used the w2 of before.  A no-op in direct mode."""
+        tabs = self._tables(store)
+        if "pend_table" not in tabs:
+            return
+        ranks = list(store.pool.local_ranks) if ranks is None else list(ranks)
+        e, w2 = store.sparse_var(self.E), store.sparse_var(self.W2)
+        for ph in (1, 2):
+            for r in ranks:
+                lo, hi = store._sparse_owned(e, r)
+                lo2, hi2 = store._sparse_owned(w2, r)
+                ops.sparse_wd_apply(store.sparse_shard(self.P, r), store.sparse_shard(self.W, r) if self.wide else None,
+                                    store.sparse_shard(self.E, r), hi - lo, self.dim, w2.table, w2.rows_per_shard,
+                                    store.sparse_shard(self.P2, r), store.sparse_shard(self.W2, r), hi2 - lo2, ph)
 
     def step_async(self, store, batch, lr: float, rank: Optional[int] = None):
         """One fused Hogwild step — gather, loss, four scatter-updates, global_step — one launch."""
         row_ptr, fid, fval, labels = batch
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
+        self.flush(store, None if rank is None else [rank])   # owner side of the deferred update: what peers sent so far
         ops.sparse_wd(row_ptr, fid, fval, labels, **self._tables(store), pred=bufs["pred"],
                       loss_sum=bufs["loss"], global_step=self._gs0, forward=True, update=True, lr=lr)
         return bufs["loss"]
@@ -112,12 +147,16 @@ class SparseWideDeep:
         ops.sparse_wd(row_ptr, fid, fval, labels, **tabs, dz_in=bufs["dz"],
                       global_step=store.global_step_tensor(rank), forward=False, update=True, lr=lr / N)
         store.barrier()
+        if "pend_table" in tabs:                    # every replica's coefficients have landed: owners fold them in
+            self.flush(store)
+            store.barrier()
         return bufs["loss"]
 
     def predict(self, store, batch, rank: Optional[int] = None):
         row_ptr, fid, fval, labels = batch
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
+        self.flush(store)
         ops.sparse_wd(row_ptr, fid, fval, labels, **self._tables(store), pred=bufs["pred"],
                       loss_sum=bufs["loss"], forward=True, update=False)
         return bufs["pred"], bufs["loss"]

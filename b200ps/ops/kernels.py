@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_wd", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -276,8 +276,10 @@ def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, pred
 
 def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, emb_table, emb_rows_per_shard, dim,
               w2_table, w2_rows_per_shard, bias, pred=None, dz_out=None, dz_in=None, loss_sum=None,
-              global_step=None, forward=True, update=True, lr=0.0, grad_scale=None, loss_scale=None, stream=None):
-    """Sparse wide & deep step over row-sharded tables (K4w/K5w): see include/b200ps.h b200ps_sparse_wd."""
+              global_step=None, forward=True, update=True, lr=0.0, grad_scale=None, loss_scale=None,
+              pend_table=None, pend_rows_per_shard=0, pend2_table=None, pend2_rows_per_shard=0, stream=None):
+    """Sparse wide & deep step over row-sharded tables (K4w/K5w): see include/b200ps.h b200ps_sparse_wd.
+    With ``pend_table``/``pend2_table`` the updates are deferred (scalar coefficients; ``sparse_wd_apply``)."""
     _cuda(row_ptr, fid, fval, labels, emb_table, w2_table, bias)
     B = labels.numel()
     gs = (1.0 / B) if grad_scale is None else grad_scale
@@ -286,7 +288,16 @@ def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, em
                                          wide_rows_per_shard, ptr(emb_table), emb_rows_per_shard, dim,
                                          ptr(w2_table), w2_rows_per_shard, ptr(bias), ptr(pred), ptr(dz_out),
                                          ptr(dz_in), ptr(loss_sum), ptr(global_step), B, int(forward),
-                                         int(update), lr, gs, ls, stream_ptr(stream)), "sparse_wd")
+                                         int(update), lr, gs, ls, ptr(pend_table), pend_rows_per_shard,
+                                         ptr(pend2_table), pend2_rows_per_shard, stream_ptr(stream)), "sparse_wd")
+
+
+def sparse_wd_apply(pend_local, wide_local, emb_local, rows_local, dim, w2_table, w2_rows_per_shard, pend2_local,
+                    w2_local, w2_rows_local, phase, stream=None):
+    """Owner-side fold of the deferred wide & deep updates (phase 1: rows, phase 2: w2)."""
+    check(native.load().b200ps_sparse_wd_apply(ptr(pend_local), ptr(wide_local), ptr(emb_local), rows_local, dim,
+                                               ptr(w2_table), w2_rows_per_shard, ptr(pend2_local), ptr(w2_local),
+                                               w2_rows_local, phase, stream_ptr(stream)), "sparse_wd_apply")
 
 
 def auc_hist(pred, labels, thresholds, hist_pos, hist_neg, stream=None):

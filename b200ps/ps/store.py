@@ -314,6 +314,8 @@ class ParameterStore:
                         full[a - off: b - off] = src.cpu()
             out[s.name] = full.view(s.shape)
         for name, sv in self.sparse.items():
+            if name.startswith("_"):                  # scratch tables (e.g. pending coefficients): not model state
+                continue
             full = torch.empty(sv.rows * sv.dim, dtype=torch.float32)
             for r in range(self.world):
                 lo, hi = self._sparse_owned(sv, r)
@@ -333,6 +335,8 @@ class ParameterStore:
                 raise ValueError(f"{s.name}: checkpoint shape {tuple(t.shape)} != {s.shape}")
             self._assign(s, t.reshape(-1).to(self.device))
         for name, sv in self.sparse.items():
+            if name.startswith("_"):
+                continue
             t = torch.as_tensor(state[name], dtype=torch.float32).reshape(-1)
             if t.numel() != sv.rows * sv.dim:
                 raise ValueError(f"{name}: checkpoint has {t.numel()} elements, want {sv.rows * sv.dim}")

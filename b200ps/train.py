@@ -561,7 +561,13 @@ class SparseWideDeepTrainer(SparseLRTrainer):
     model = wide [F,1] + embedding [F,dim] x [dim,1]."""
 
     def __init__(self, ctx, features: int, dim: int = 128, wide: bool = True, lr: float = 0.001,
-                 mode: str = "async", placement: str = "flat_shard", seed: int = 1, use_graph: bool = True):
+                 mode: str = "async", placement: str = "flat_shard", seed: int = 1, use_graph: bool = True,
+                 deferred: Optional[bool] = None):
         from .models.wide_deep import SparseWideDeep
         super().__init__(ctx, features, lr=lr, mode=mode, placement=placement, seed=seed, use_graph=use_graph,
-                         model=SparseWideDeep(features, dim=dim, wide=wide))
+                         model=SparseWideDeep(features, dim=dim, wide=wide, deferred=deferred))
+
+    def flush(self) -> None:
+        """Fold pending (deferred) updates of this process's shards into the tables — before checkpoints and
+        evaluations that must see every update sent so far."""
+        self.model.flush(self.store)

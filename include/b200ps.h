@@ -253,7 +253,17 @@ int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, const float* fv
                      int64_t emb_rows_per_shard, int32_t dim, float* const* w2_shards,
                      int64_t w2_rows_per_shard, float* bias, float* pred, float* dz_out, const float* dz_in,
                      float* loss_sum, uint64_t* global_step, int32_t B, int32_t do_forward, int32_t do_update,
-                     float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+                     float lr, float grad_scale, float loss_scale, float* const* pend_shards,
+                     int64_t pend_rows_per_shard, float* const* pend2_shards, int64_t pend2_rows_per_shard,
+                     b200ps_stream_t stream);
+/* Deferred mode (pend_shards != NULL above): the embedding update of a step is rank one, dE[fid,:] = c[fid]*w2,
+ * so workers add only the scalar c into a pending table P (sharded like W: 4 bytes of remote atomic per
+ * non-zero instead of 516) and the w2 gradient into P2; the OWNER of a shard folds them in with
+ * b200ps_sparse_wd_apply: phase 1 = its rows (W += c, E[row,:] += c*w2, plain stores), phase 2 = its slice
+ * of w2.  Pointers here are local shard bases.  Call it before a step / before reading the tables. */
+int b200ps_sparse_wd_apply(float* pend_local, float* wide_local, float* emb_local, int64_t rows_local, int32_t dim,
+                           float* const* w2_shards, int64_t w2_rows_per_shard, float* pend2_local, float* w2_local,
+                           int64_t w2_rows_local, int32_t phase, b200ps_stream_t stream);
 int b200ps_auc_hist(const float* pred, const float* labels, int32_t B, const float* thresholds,
                     int32_t T, uint64_t* hist_pos, uint64_t* hist_neg, b200ps_stream_t stream);
 

@@ -320,7 +320,8 @@ def test_sparse_wide_deep_vs_float64_reference(native_lib, world, dim, wide):
     ops.sparse_wd(rp, fid, fv, y, **kw, dz_in=dz, global_step=gstep, forward=False, update=True, lr=lr)
     torch.cuda.synchronize()
     assert (torch.cat(es).cpu().double() - (E.cpu().double() - lr * gr["E"])).abs().max().item() < 1e-5
-    assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 1e-5
+    # (the w2 gradient is a sum of 300 signed dz*h terms accumulated in fp32 across warps and CTAs)
+    assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 5e-5
     if wide:
         assert (torch.cat(ws).cpu().double() - (W.cpu().double() - lr * gr["W"])).abs().max().item() < 1e-5
     assert abs(kw["bias"].item() - (0.25 - lr * gr["b"].item())) < 1e-5 and gstep.item() == 1
@@ -330,6 +331,26 @@ def test_sparse_wide_deep_vs_float64_reference(native_lib, world, dim, wide):
     assert (torch.cat(es).cpu().double() - (E.cpu().double() - lr * gr["E"])).abs().max().item() < 1e-3
     assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 1e-3
     assert gstep.item() == 2
+    # deferred mode: workers add one scalar per non-zero into the pending table, the owners fold it in
+    # (rows first, then w2): same result as the direct scatter, and the tables are untouched until the fold
+    ws, es, w2s, kw = tables()
+    pend = [torch.zeros(rows, device=DEV) for _ in range(world)]
+    pend2 = [torch.zeros(rows2, device=DEV) for _ in range(world)]
+    dk = dict(pend_table=ops.device_ptr_table([t.data_ptr() for t in pend], DEV), pend_rows_per_shard=rows,
+              pend2_table=ops.device_ptr_table([t.data_ptr() for t in pend2], DEV), pend2_rows_per_shard=rows2)
+    ops.sparse_wd(rp, fid, fv, y, **kw, **dk, dz_in=dz, global_step=gstep, forward=False, update=True, lr=lr)
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat(es), E) and torch.equal(torch.cat(w2s), w2) and torch.cat(pend).abs().sum() > 0
+    for phase in (1, 2):
+        for r in range(world):
+            ops.sparse_wd_apply(pend[r], ws[r] if wide else None, es[r], rows, dim, kw["w2_table"], rows2, pend2[r], w2s[r],
+                                rows2, phase)
+    torch.cuda.synchronize()
+    assert (torch.cat(es).cpu().double() - (E.cpu().double() - lr * gr["E"])).abs().max().item() < 1e-5
+    assert (torch.cat(w2s).cpu().double() - (w2.cpu().double() - lr * gr["w2"])).abs().max().item() < 5e-5
+    if wide:
+        assert (torch.cat(ws).cpu().double() - (W.cpu().double() - lr * gr["W"])).abs().max().item() < 1e-5
+    assert torch.cat(pend).abs().sum().item() == 0 and torch.cat(pend2).abs().sum().item() == 0
 
 
 def test_auc_hist(native_lib):

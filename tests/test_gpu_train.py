@@ -285,9 +285,11 @@ def test_sparse_wide_deep_trainer_learns_and_checkpoints(native_lib, tmp_path):
         fv = torch.empty(B * (nnz + spread), device=DEV); y = torch.empty(B, device=DEV)
         ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=5, offset=i * B)
         batches.append((rp, fid, fv, y))
-    for mode, world in (("async", 1), ("sync", 1), ("async", 2)):
+    # direct scatter of 512-byte rows, and the deferred form (scalar coefficients folded in by the shard owner)
+    for mode, world, deferred in (("async", 1, False), ("sync", 1, True), ("async", 2, True)):
         ctx = init_from_env(virtual_world=world)
-        tr = SparseWideDeepTrainer(ctx, features=F, dim=128, lr=2.0, mode=mode)
+        tr = SparseWideDeepTrainer(ctx, features=F, dim=128, lr=2.0, mode=mode, deferred=deferred)
+        assert tr.model.deferred == deferred and (("_pending/coefficients" in tr.store.sparse) == deferred)
         for epoch in range(6):
             for b in batches[:32]:
                 tr.step(b)
@@ -297,8 +299,10 @@ def test_sparse_wide_deep_trainer_learns_and_checkpoints(native_lib, tmp_path):
             pred, _ = tr.predict(b)
             auc.update(pred, b[3])
         assert auc.result() > 0.65, (mode, world, auc.result())
+    tr.flush()                                         # deferred updates folded in before the checkpoint
     state = tr.store.state_dict()
     assert state["deep/weights"].shape == (F, 128) and state["deep/weights_1"].shape == (128, 1)
+    assert not any(k.startswith("_") for k in state)   # the pending tables are scratch, not model state
     from b200ps.io.saver import store_variables
     prefix = Saver().save(store_variables(tr.store), str(tmp_path / "model.ckpt"), global_step=tr.global_step)
     back = Saver().restore(prefix)
