@@ -23,6 +23,7 @@ from .models.mlp import SigmoidMLP, WideMLP
 from .models.sparse_lr import SparseLR
 from .optim.sgd import AsyncSGD, SyncReplicasSGD
 from .ps.store import ParameterStore
+from .utils.trace import nvtx_range
 
 
 def _capture(body, device):
@@ -168,31 +169,37 @@ class MLPTrainer(_TrainerBase):
         if self.fused_apply:
             ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
-            return self.model.fused_train_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
-                                               batch=self.batch_size, stats_out=stats_out, **ck)
+            with nvtx_range("fused_step"):
+                return self.model.fused_train_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                                   batch=self.batch_size, stats_out=stats_out, **ck)
         if self.fused_async:
             ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
-            return self.model.fused_async_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
-                                               batch=self.batch_size, stats_out=stats_out, **ck)
+            with nvtx_range("fused_step+pull+push_async"):
+                return self.model.fused_async_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                                   batch=self.batch_size, stats_out=stats_out, **ck)
         if self.fused_push:
             ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
-            return self.model.fused_push_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
-                                              batch=self.batch_size, stats_out=stats_out, **ck)
-        out = self.model.forward_backward(st, x, labels, rank=r, row_offset=row_offset, batch=self.batch_size,
-                                          stats_out=stats_out, fused=self.fused)
-        if self.mode == "async":
-            self.opt.apply(st, rank=r, **cursor_kw)
-        elif len(self.local_ranks) == 1:
-            self.opt.apply(st, **cursor_kw)
+            with nvtx_range("fused_step+push_sync"):
+                return self.model.fused_push_step(st, x, labels, self.lr, rank=r, row_offset=row_offset,
+                                                  batch=self.batch_size, stats_out=stats_out, **ck)
+        with nvtx_range("forward_backward"):
+            out = self.model.forward_backward(st, x, labels, rank=r, row_offset=row_offset, batch=self.batch_size,
+                                              stats_out=stats_out, fused=self.fused)
+        with nvtx_range("push"):
+            if self.mode == "async":
+                self.opt.apply(st, rank=r, **cursor_kw)
+            elif len(self.local_ranks) == 1:
+                self.opt.apply(st, **cursor_kw)
         return out
 
     def _prepare(self):
         """Refresh the worker's parameter view before a step (async pull; nothing to do when the step kernel
         reads the owners' masters itself, or in sync mode where the push already broadcast)."""
         if not self.fused_async:
-            self.opt.prepare(self.store)
+            with nvtx_range("pull"):
+                self.opt.prepare(self.store)
 
     def _body(self):
         st = self.store

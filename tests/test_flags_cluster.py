@@ -138,3 +138,14 @@ def test_bashflags_definition_errors_required_and_passthrough():
     assert r.stdout.strip() == "k=5 rest=--backend gloo --sync"
     r = _bashflags('DEFINE_integer k 1 "k"; flags_reset; DEFINE_string k z "again"; FLAGS "$@"; echo "k=${FLAGS_k}"', "--k", "w")
     assert r.stdout.strip() == "k=w"
+
+
+def test_trace_helpers_step_timer_and_disabled_nvtx():
+    import time
+    from b200ps.utils import StepTimer, nvtx_range
+    with nvtx_range("noop"):            # B200PS_NVTX unset: a plain pass-through, no CUDA needed
+        x = 1
+    t = StepTimer()
+    time.sleep(0.02); t.tick(4)
+    avg = t.report()
+    assert x == 1 and 3.0 < avg < 50.0 and t.report() >= 0.0
