@@ -478,8 +478,8 @@ def main():
             "unit": "examples/s", "n_gpus": ctx.world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": primary["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": (primary["value"] / base) if base else None,
-            "dtype": "tf32 tensor-core math on fp32 storage (fp32 master/accumulate)"
-                     if primary_name.startswith("mnist") else "bf16",
+            "dtype": "fp32 (exact-fp32 one-launch step; B200PS_FUSED_STEP=0 selects the tf32 tensor-core chain)"
+                     if primary_name.startswith("mnist") else ("fp32" if primary_name.startswith("sparse") else "bf16"),
             "data": "synthetic (on-device Philox generators), random-init weights",
             "config": primary["config"], "clocks": sampler.summary(), "e2e": primary["e2e"],
             "gpu_launches": primary["gpu_launches"], "impl": "b200ps",
