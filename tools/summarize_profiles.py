@@ -102,7 +102,10 @@ def main():
     md += ["## SASS evidence", "",
            "`profiles/sass_mnemonics.txt` (from `tools/sass_summary.sh`, cuobjdump of libb200ps.so) lists per kernel the "
            "Blackwell instructions present: `UTCHMMA` (tcgen05.mma), `LDTM` (tcgen05.ld), `UTMALDG` (TMA tensor loads), "
-           "`UBLKCP` (cp.async.bulk of the fused pull), `SYNCS.*` (mbarrier), `REDG.E.ADD.F32...SYS` (peer reductions).", ""]
+           "`UBLKCP` (cp.async.bulk of the fused pull and of the one-launch step), `LDGSTS` (cp.async), `SYNCS.*` (mbarrier), "
+           "`REDG.E.ADD.F32...SYS` (peer reductions), `STG/LDG.E.64.STRONG.SYS` (the 8-byte packets of the low-latency push).",
+           "`profiles/libb200ps.sass.gz` is the full SASS listing of every kernel in the library (instructions only, "
+           "`zcat profiles/libb200ps.sass.gz | less`; regenerate with `tools/sass_listing.py`).", ""]
     open(os.path.join(OUT, "README.md"), "w").write("\n".join(md))
     print("\n".join(md)[:6000])
 
