@@ -216,3 +216,34 @@ def test_native_loader_packed_batches_match_python_parser(tmp_path):
     rp, fid, fval, y = lay.views(buf)
     assert rp.tolist() == [0, 2, 2, 5, 6] and fid[:6].tolist() == [0, 10, 20, 30, 40, 50] and y.tolist() == [1, 0, 0, 1]
     assert lay.off_fid % 16 == 0 and lay.off_fval % 16 == 0 and lay.off_labels % 16 == 0 and lay.bytes % 16 == 0
+
+
+_float_text = st.one_of(
+    st.floats(min_value=-1e6, max_value=1e6, allow_nan=False, width=32).map(lambda v: repr(float(v))),
+    st.floats(min_value=-1e3, max_value=1e3, allow_nan=False).map(lambda v: "%.9f" % v),
+    st.floats(min_value=1e-30, max_value=1e30, allow_nan=False).map(lambda v: "%.6e" % v),
+    st.integers(min_value=-10**9, max_value=10**9).map(str),
+    st.sampled_from(["0", "-0", "+1.5", ".5", "5.", "1e3", "1E-3", "-2.5e+2", "000.250", "123456789012345678.5"]))
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.lists(st.tuples(st.integers(min_value=-1, max_value=1),
+                          st.lists(st.tuples(st.integers(min_value=0, max_value=2**40), _float_text), min_size=1, max_size=6),
+                          st.sampled_from([" ", "\t", "  ", " \t"]), st.sampled_from(["\n", "\r\n"])),
+                min_size=1, max_size=12))
+def test_native_loader_number_parsing_fuzz(tmp_path_factory, rows):
+    """The loader's in-place number parser (fast decimal path + strtof fallback) against Python's int()/float()."""
+    import numpy as np
+    from b200ps.data.native_loader import NativeLibsvmLoader
+    d = tmp_path_factory.mktemp("fuzz")
+    text = "".join(str(lab) + "".join(sep + "%d:%s" % (i, v) for i, v in feats) + eol for lab, feats, sep, eol in rows)
+    (d / "part-0").write_text(text + "0 1:1\n")                    # a short-line-proof terminator row
+    loader = NativeLibsvmLoader([str(d / "part-0")], batch_size=len(rows) + 1, threads=1, max_nnz_per_row=8, pinned=False)
+    batch = loader.next()
+    assert batch is not None and batch.rows == len(rows) + 1 and loader.stats()["malformed"] == 0
+    rp, fid, fval, y = (a.numpy() for a in batch.arrays())
+    for r, (lab, feats, _, _) in enumerate(rows):
+        assert y[r] == lab and fid[rp[r]:rp[r + 1]].tolist() == [i for i, _ in feats]
+        want = np.asarray([float(v) for _, v in feats], dtype=np.float64).astype(np.float32)
+        np.testing.assert_allclose(fval[rp[r]:rp[r + 1]], want, rtol=2e-7, atol=0)
+    batch.release(); loader.close()
