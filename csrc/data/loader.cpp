@@ -269,7 +269,10 @@ extern "C" int b200ps_loader_create(void** out, const char* const* files, int32_
   for (int i = 0; i < nfiles; ++i) L->files.emplace_back(files[i]);
   L->threads = threads; L->epochs = epochs; L->sampling_rate = sampling_rate; L->seed = seed;
   L->lay = make_layout(batch_rows, cap_nnz);
-  B200PS_REQUIRE(L->lay.bytes < (int64_t(1) << 31), "loader_create: packed batch larger than 2 GiB");
+  if (L->lay.bytes >= (int64_t(1) << 31)) {
+    delete L;
+    return set_error(B200PS_ERR_INVALID, "loader_create: packed batch larger than 2 GiB");
+  }
   L->pinned = pinned != 0;
   for (int i = 0; i < ring; ++i) {
     char* p = nullptr;
@@ -284,7 +287,13 @@ extern "C" int b200ps_loader_create(void** out, const char* const* files, int32_
       }
     }
     if (!p) p = static_cast<char*>(aligned_alloc(256, (size_t)((L->lay.bytes + 255) & ~int64_t(255))));
-    if (!p) { delete L; return set_error(B200PS_ERR_INVALID, "loader_create: out of memory"); }
+    if (!p) {
+      for (size_t k = 0; k < L->buffers.size(); ++k) {
+        if (L->buffer_pinned[k]) cudaFreeHost(L->buffers[k]); else free(L->buffers[k]);
+      }
+      delete L;
+      return set_error(B200PS_ERR_INVALID, "loader_create: out of memory");
+    }
     memset(p, 0, L->lay.bytes);
     L->buffers.push_back(p);
     L->buffer_pinned.push_back(is_pinned ? 1 : 0);

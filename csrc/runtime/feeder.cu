@@ -45,6 +45,8 @@ struct Feeder {
 
 }  // namespace
 
+extern "C" int b200ps_feeder_destroy(void* feeder);
+
 extern "C" int b200ps_feeder_create(void** out, int32_t slots, uint64_t bytes0, uint64_t bytes1,
                                     uint64_t result_bytes) {
   B200PS_REQUIRE(out && slots >= 1 && slots <= 64, "feeder_create: slots must be in [1, 64]");
@@ -63,7 +65,7 @@ extern "C" int b200ps_feeder_create(void** out, int32_t slots, uint64_t bytes0, 
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->slots[i].done, cudaEventDisableTiming);
   }
   if (e != cudaSuccess) {
-    delete f;
+    b200ps_feeder_destroy(f);      // releases whatever was created so far
     return set_error(B200PS_ERR_CUDA, "feeder_create: %s", cudaGetErrorString(e));
   }
   memset(f->results, 0, slots * result_bytes);
