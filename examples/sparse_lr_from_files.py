@@ -23,8 +23,8 @@ ap.add_argument("--features", type=int, default=1 << 16)
 args = ap.parse_args()
 
 d = tempfile.mkdtemp(prefix="b200ps_example_")
-train = write_libsvm_files(os.path.join(d, "train"), 4, 5000, nnz_mean=30, spread=10, features=args.features, seed=5)
-test = write_libsvm_files(os.path.join(d, "test"), 1, 2000, nnz_mean=30, spread=10, features=args.features, seed=6)
+files = write_libsvm_files(os.path.join(d, "data"), 5, 5000, nnz_mean=30, spread=10, features=args.features, seed=5)
+train, test = files[:4], files[4:]                    # same generator (same hidden teacher), held-out file
 
 ctx = init_from_env()
 if args.deep_dim:
@@ -33,7 +33,7 @@ else:
     tr = SparseLRTrainer(ctx, args.features, lr=1.0, mode="async")
 tr.store.sparse_shard(tr.model.W).mul_(0.01)          # start near zero so that a short run shows learning
 
-for epoch in range(5):
+for epoch in range(8):
     loader = NativeLibsvmLoader(train, batch_size=500, threads=4, max_nnz_per_row=64, epochs=1, seed=epoch)
     losses = []
     steps = tr.fit_from_loader(loader, on_loss=lambda i, v: losses.append(v))
