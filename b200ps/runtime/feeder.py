@@ -20,6 +20,27 @@ import torch
 from ..ops import native
 
 
+def _load_fastfeed():
+    """The optional CPython extension with the per-step fast paths (csrc/python/fastfeed.c)."""
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(native.lib_path()), "_fastfeed.so")
+    if not os.path.exists(path) or os.environ.get("B200PS_FASTFEED", "1") == "0":
+        return None
+    try:
+        native.load()
+        spec = importlib.util.spec_from_file_location("b200ps._fastfeed", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    except Exception:
+        return None
+
+
+_FF = None
+_FF_TRIED = False
+
+
 class Ticket:
     """Handle of one submitted unit; ``result()`` blocks until its result block is on the host."""
     __slots__ = ("_feeder", "_id")
@@ -28,7 +49,13 @@ class Ticket:
         self._feeder, self._id = feeder, ident
 
     def result(self):
-        return self._feeder.wait(self._id)
+        f = self._feeder
+        if f._fast_wait is not None:
+            try:
+                return f._fast_wait(f._hv, self._id)
+            except RuntimeError as e:
+                raise native.NativeError(str(e)) from None
+        return f.wait(self._id)
 
 
 class HostFeeder:
@@ -66,9 +93,22 @@ class HostFeeder:
         self._submit = self._lib.b200ps_feeder_submit
         self._tref = C.byref(self._ticket)
         self._stream = native.stream_ptr()           # the compute stream the graphs were captured for
+        global _FF, _FF_TRIED
+        if not _FF_TRIED:
+            _FF, _FF_TRIED = _load_fastfeed(), True
+        self._hv = self._h.value
+        self._fast_submit = _FF.submit if _FF is not None else None
+        # a float straight from C when the unit's result is one loss word (first word of a block <= 256 bytes)
+        self._fast_wait = _FF.wait_first if (_FF is not None and result_words <= 64 and getattr(decode, "first_word", False)) else None
 
     def submit(self, src0: torch.Tensor, src1: torch.Tensor = None, stream=None) -> Ticket:
         """Queue one unit from pinned host tensors; returns immediately."""
+        if self._fast_submit is not None and stream is None:
+            try:
+                return Ticket(self, self._fast_submit(self._hv, src0.data_ptr(), 0 if src1 is None else src1.data_ptr(),
+                                                      self._stream))
+            except RuntimeError as e:
+                raise native.NativeError(str(e)) from None
         rc = self._submit(self._h, src0.data_ptr(), 0 if src1 is None else src1.data_ptr(),
                           self._stream if stream is None else native.stream_ptr(stream), self._tref)
         if rc:
@@ -91,6 +131,7 @@ class HostFeeder:
         if self._h:
             self._lib.b200ps_feeder_destroy(self._h)
             self._h = C.c_void_p()
+            self._hv, self._fast_submit, self._fast_wait = 0, None, None
             self._keep.clear()
 
     def __del__(self):

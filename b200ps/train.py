@@ -279,12 +279,13 @@ class MLPTrainer(_TrainerBase):
         Once the trainer is warm the whole host side is ONE native call into the ``HostFeeder``
         (copy-stream H2D into a staging slot, event hand-off, graph launch; the loss is written by
         the step kernel into pinned host memory)."""
-        if not self._step.use_graph or self._step.calls < self._step.warmup or len(self.local_ranks) != 1:
-            return super().step_from_host_async(x_pinned, labels_pinned)
-        if getattr(self, "_feeder1", None) is None:
-            self._feeder1 = self.host_feeder(steps_per_call=1, slots=8)
+        f = self.__dict__.get("_feeder1")
+        if f is None:
+            if not self._step.use_graph or self._step.calls < self._step.warmup or len(self.local_ranks) != 1:
+                return super().step_from_host_async(x_pinned, labels_pinned)
+            f = self._feeder1 = self.host_feeder(steps_per_call=1, slots=8)
         self.local_step += 1
-        return self._feeder1.submit(x_pinned, labels_pinned)
+        return f.submit(x_pinned, labels_pinned)
 
     def host_feeder(self, steps_per_call: int = 1, slots: int = 4):
         """A ``HostFeeder`` whose unit is ``steps_per_call`` consecutive training steps on a pinned host
@@ -313,7 +314,9 @@ class MLPTrainer(_TrainerBase):
             return _capture(body, dev), (x, y)
 
         if K == 1:
-            decode = lambda out: float(out[0])                                  # noqa: E731
+            def decode(out):
+                return float(out[0])
+            decode.first_word = True          # lets the feeder return the loss straight from C
         else:
             decode = lambda out: out.reshape(K, 2)[:, 0].copy()                 # noqa: E731
         f = HostFeeder(make_slot, (K * B * self.model.in_dim * 4, K * B * 4), 2 * K, slots=slots, decode=decode)
@@ -525,7 +528,10 @@ class SparseLRTrainer(_TrainerBase):
                 ops.copy_words(result, trainer._last, 1)
             return _capture(body, dev), (staging,)
 
-        f = HostFeeder(make_slot, (layout.bytes,), 1, slots=slots, decode=lambda out: float(out[0]))
+        def decode(out):
+            return float(out[0])
+        decode.first_word = True
+        f = HostFeeder(make_slot, (layout.bytes,), 1, slots=slots, decode=decode)
         f.layout = layout
         return f
 

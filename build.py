@@ -27,10 +27,34 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unus
 def sources():
     out = []
     for d, _, files in os.walk(CSRC):
+        if os.path.basename(d) == "python":          # CPython extension sources are built separately
+            continue
         for f in sorted(files):
             if f.endswith((".cu", ".cpp")):
                 out.append(os.path.join(d, f))
     return sorted(out)
+
+
+def build_python_ext(quiet=False):
+    """Optional CPython extension with the per-step fast paths (csrc/python/fastfeed.c) -> b200ps/_lib/_fastfeed.so.
+    Skipped (ctypes fallback) when Python.h or a C compiler is missing."""
+    import sysconfig
+    src = os.path.join(CSRC, "python", "fastfeed.c")
+    out = os.path.join(OUT_DIR, "_fastfeed.so")
+    inc = sysconfig.get_paths()["include"]
+    if not os.path.exists(os.path.join(inc, "Python.h")):
+        return None
+    if os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(LIB)):
+        return out
+    cmd = [os.environ.get("CC", "gcc"), "-O2", "-shared", "-fPIC", "-Wall", "-I", inc, src, "-o", out,
+           "-L", OUT_DIR, "-lb200ps", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        print("[build] _fastfeed extension skipped:\n" + r.stdout + r.stderr, file=sys.stderr)
+        return None
+    if not quiet:
+        print(f"[build] built {os.path.relpath(out, ROOT)}")
+    return out
 
 
 def headers_digest():
@@ -93,6 +117,7 @@ def build(force=False, verbose=False, quiet=False):
             raise RuntimeError("link failed")
         if not quiet:
             print(f"[build] linked {os.path.relpath(LIB, ROOT)}")
+    build_python_ext(quiet)
     return LIB
 
 
