@@ -428,6 +428,8 @@ def main():
     args = ap.parse_args()
 
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:       # under torchrun: one line, from rank 0
+            return 0
         print(json.dumps({"impl": "reference",
                           "unavailable": "reference = Python-2 scripts on TensorFlow 0.8-0.12; no installable "
                                          "artefact in /root/reference and no TensorFlow wheel offline "
