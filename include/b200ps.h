@@ -379,6 +379,24 @@ int b200ps_loader_release(void* loader, void* buf);
 int b200ps_loader_stats(void* loader, int64_t* out7);
 int b200ps_loader_destroy(void* loader);
 
+/* TensorFlow tensor-bundle (Saver V2) checkpoints, natively (the BundleWriter / BundleReader of tf.train.Saver,
+ * model_export.py:53): <prefix>.index (leveldb-style table: "" -> header, name -> {dtype, shape, offset, size,
+ * masked crc32c}) + <prefix>.data-00000-of-00001 (raw little-endian bytes).  add() streams the caller's buffer
+ * to disk with one CRC pass; finish() writes the sorted index and renames both files into place (the writer
+ * is destroyed by finish or abort).  dtype = TensorFlow DataType enum (1 float32, 2 float64, 3 int32, 9 int64,
+ * 14 bfloat16, ...).  The reader lists entries sorted by name and verifies block and data checksums. */
+int b200ps_bundle_writer_create(void** writer, const char* prefix);
+int b200ps_bundle_writer_add(void* writer, const char* name, int32_t dtype, const int64_t* shape, int32_t ndim,
+                             const void* data, uint64_t nbytes);
+int b200ps_bundle_writer_finish(void* writer);
+int b200ps_bundle_writer_abort(void* writer);
+int b200ps_bundle_reader_open(void** reader, const char* prefix);
+int b200ps_bundle_reader_count(void* reader, int32_t* n);
+int b200ps_bundle_reader_entry(void* reader, int32_t i, char* name, int32_t name_cap, int32_t* dtype,
+                               int64_t* shape8, int32_t* ndim, uint64_t* nbytes);
+int b200ps_bundle_reader_read(void* reader, int32_t i, void* dst, uint64_t nbytes, int32_t verify);
+int b200ps_bundle_reader_close(void* reader);
+
 /* libsvm text -> CSR (lr2.py:57-84).  Count first, then parse into caller-sized arrays.
  * parse returns 0 or -(1-based line number) of the first malformed line. */
 int b200ps_libsvm_count(const char* buf, uint64_t len, uint64_t* rows, uint64_t* nnz);

@@ -148,3 +148,48 @@ def test_proto_codec_roundtrip():
     assert pb.decode(d[3][0])[1] == [(1 << 64) - 1]
     with pytest.raises(ValueError):
         pb.decode(b"\x0a\x05ab")
+
+
+def test_native_bundle_writer_reader_match_python_twin(tmp_path, monkeypatch):
+    """csrc/io/bundle.cpp against b200ps/io/tf_bundle.py: identical bytes for both files (300 entries span
+    several restart groups; scalars, empty and 3-D tensors, every dtype), and each reader reads the other's files."""
+    import numpy as np
+    from b200ps.io import tf_bundle
+    from b200ps.ops import native
+    if not native.available():
+        pytest.skip("libb200ps.so not built")
+    rng = np.random.default_rng(0)
+    tensors = {"global_step": np.float32(17.0), "empty": np.zeros((0, 4), np.float32),
+               "cube": rng.standard_normal((3, 4, 5)).astype(np.float64),
+               "ids": rng.integers(-2**40, 2**40, size=37), "flags": rng.integers(0, 2, size=9).astype(bool)}
+    for i in range(300):
+        tensors["layer_%03d/weights/Variable_%d" % (i // 7, i)] = rng.standard_normal((i % 5 + 1, 3)).astype(np.float32)
+    for dt in ("int32", "uint8", "int16", "int8", "uint16", "float16", "uint32", "uint64"):
+        tensors["dtypes/" + dt] = (rng.standard_normal(11) * 10).astype(dt)
+    monkeypatch.setenv("B200PS_NATIVE_BUNDLE", "1")
+    tf_bundle.write_bundle(str(tmp_path / "nat" / "model.ckpt-5"), tensors)
+    monkeypatch.setenv("B200PS_NATIVE_BUNDLE", "0")
+    tf_bundle.write_bundle(str(tmp_path / "py" / "model.ckpt-5"), tensors)
+    for suffix in (".index", ".data-00000-of-00001"):
+        a = open(str(tmp_path / "nat" / "model.ckpt-5") + suffix, "rb").read()
+        b = open(str(tmp_path / "py" / "model.ckpt-5") + suffix, "rb").read()
+        assert a == b, suffix
+    assert not [f for f in (tmp_path / "nat").iterdir() if f.name.endswith(".tmp")]
+    from_nat_by_py = tf_bundle.read_bundle(str(tmp_path / "nat" / "model.ckpt-5"))
+    monkeypatch.setenv("B200PS_NATIVE_BUNDLE", "1")
+    from_py_by_nat = tf_bundle.read_bundle(str(tmp_path / "py" / "model.ckpt-5"))
+    assert set(from_nat_by_py) == set(from_py_by_nat) == set(tensors)
+    for k, v in tensors.items():
+        v = np.asarray(v)
+        for got in (from_nat_by_py[k], from_py_by_nat[k]):
+            assert got.dtype == v.dtype and got.shape == v.shape and np.array_equal(got, v), k
+    # corruption is caught natively too: a flipped data byte, a flipped index byte
+    p = str(tmp_path / "py" / "model.ckpt-5")
+    raw = bytearray(open(p + ".data-00000-of-00001", "rb").read()); raw[100] ^= 0xFF
+    open(p + ".data-00000-of-00001", "wb").write(bytes(raw))
+    with pytest.raises(ValueError, match="checksum"):
+        tf_bundle.read_bundle(p)
+    idx = bytearray(open(p + ".index", "rb").read()); idx[40] ^= 0x01
+    open(p + ".index", "wb").write(bytes(idx))
+    with pytest.raises(ValueError):
+        tf_bundle.read_bundle(p)
