@@ -21,6 +21,17 @@ from . import proto as pb
 from .crc32c import masked_crc32c
 
 
+def _native_lib():
+    """libb200ps.so when built (native writer, csrc/io/events.cpp); B200PS_NATIVE_EVENTS=0 forces Python."""
+    if os.environ.get("B200PS_NATIVE_EVENTS", "1") == "0":
+        return None
+    try:
+        from ..ops import native
+        return native if native.available() else None
+    except Exception:
+        return None
+
+
 def _record(payload: bytes) -> bytes:
     hdr = struct.pack("<Q", len(payload))
     return hdr + struct.pack("<I", masked_crc32c(hdr)) + payload + struct.pack("<I", masked_crc32c(payload))
@@ -51,6 +62,16 @@ class SummaryWriter:
         self.logdir = logdir
         name = "events.out.tfevents.%010d.%s%s" % (int(time.time()), socket.gethostname(), filename_suffix)
         self.path = os.path.join(logdir, name)
+        self._closed = False
+        self._native = None
+        nat = _native_lib()
+        if nat is not None:                  # csrc/io/events.cpp: encoding, framing and the writer thread in C++
+            import ctypes as C
+            self._C, self._lib, self._check = C, nat.load(), nat.check
+            h = C.c_void_p()
+            nat.check(self._lib.b200ps_events_open(C.byref(h), self.path.encode(), float(flush_secs)), "events_open")
+            self._native = h
+            return
         self._f = open(self.path, "wb")
         self._q: "queue.Queue" = queue.Queue(max_queue)
         self._flush_secs = flush_secs
@@ -79,6 +100,13 @@ class SummaryWriter:
     def add_summary(self, values: Dict[str, float], global_step: int, wall_time: Optional[float] = None) -> None:
         if self._closed:
             raise RuntimeError("SummaryWriter is closed")
+        if self._native is not None:
+            C, n = self._C, len(values)
+            tags = (C.c_char_p * max(1, n))(*[str(t).encode("utf-8") for t in values])
+            vals = (C.c_float * max(1, n))(*[float(v) for v in values.values()])
+            self._check(self._lib.b200ps_events_add_scalars(self._native, -1.0 if wall_time is None else float(wall_time),
+                                                            int(global_step), tags, vals, n), "events_add_scalars")
+            return
         ev = _event(time.time() if wall_time is None else wall_time, int(global_step),
                     summary=_scalar_summary(values))
         self._q.put(_record(ev))
@@ -86,11 +114,19 @@ class SummaryWriter:
     add_scalars = add_summary
 
     def flush(self) -> None:
+        if self._native is not None:
+            self._check(self._lib.b200ps_events_flush(self._native), "events_flush")
+            return
         while not self._q.empty():
             time.sleep(0.005)
         self._f.flush()
 
     def close(self) -> None:
+        if not self._closed and self._native is not None:
+            self._closed = True
+            self._lib.b200ps_events_close(self._native)
+            self._native = None
+            return
         if not self._closed:
             self._closed = True
             self._q.put(None)

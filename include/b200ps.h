@@ -379,6 +379,15 @@ int b200ps_loader_release(void* loader, void* buf);
 int b200ps_loader_stats(void* loader, int64_t* out7);
 int b200ps_loader_destroy(void* loader);
 
+/* TensorBoard event files, natively (the EventsWriter behind tf.train.SummaryWriter, example.py:131-135,154,171):
+ * add_scalars() encodes Event{wall_time, step, summary{value{tag, simple_value}}}, frames it as a TFRecord and
+ * queues it; a writer thread owns the file and flushes at most every flush_secs.  wall_time < 0 = now. */
+int b200ps_events_open(void** writer, const char* path, double flush_secs);
+int b200ps_events_add_scalars(void* writer, double wall_time, int64_t step, const char* const* tags,
+                              const float* values, int32_t n);
+int b200ps_events_flush(void* writer);
+int b200ps_events_close(void* writer);
+
 /* TensorFlow tensor-bundle (Saver V2) checkpoints, natively (the BundleWriter / BundleReader of tf.train.Saver,
  * model_export.py:53): <prefix>.index (leveldb-style table: "" -> header, name -> {dtype, shape, offset, size,
  * masked crc32c}) + <prefix>.data-00000-of-00001 (raw little-endian bytes).  add() streams the caller's buffer

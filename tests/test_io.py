@@ -193,3 +193,27 @@ def test_native_bundle_writer_reader_match_python_twin(tmp_path, monkeypatch):
     open(p + ".index", "wb").write(bytes(idx))
     with pytest.raises(ValueError):
         tf_bundle.read_bundle(p)
+
+
+def test_native_events_writer_matches_python_twin(tmp_path, monkeypatch):
+    """csrc/io/events.cpp vs b200ps/io/events.py: byte-identical scalar records for the same inputs."""
+    from b200ps.io import events
+    from b200ps.ops import native
+    if not native.available():
+        pytest.skip("libb200ps.so not built")
+    paths = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("B200PS_NATIVE_EVENTS", mode)
+        w = events.SummaryWriter(str(tmp_path / mode), flush_secs=0.05)
+        assert (w._native is not None) == (mode == "1")
+        for step in range(0, 300, 3):
+            w.add_summary({"cost": 1.0 / (step + 1), "accuracy": step / 300.0, "zero": 0.0}, step, wall_time=1000.5 + step)
+        w.flush()
+        assert len(list(events.read_events(w.path))) == 101          # visible after flush, before close
+        w.close()
+        paths[mode] = w.path
+    a, b = open(paths["1"], "rb").read(), open(paths["0"], "rb").read()
+    first = 16 + len(b"\x09" + b"\x00" * 8 + b"\x1a\x0d" + b"brain.Event:2")   # the file_version record (wall time differs)
+    assert len(a) == len(b) and a[first:] == b[first:]
+    got = list(events.read_events(paths["1"]))
+    assert got[0][3] == "brain.Event:2" and got[1][1] == 0 and got[2][1] == 3 and abs(got[2][2]["cost"] - 0.25) < 1e-7
