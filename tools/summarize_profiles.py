@@ -62,10 +62,7 @@ def main():
           "compare shares, not absolutes; the timed numbers are the CUDA-event ones in `bench_*.json`.",
           "`compute-sanitizer` is closed on this pool (the tool answered so; `gpurun_out/sanitizer_memcheck.log`), "
           "so memory safety rests on the bounded-wait traps, shape/alignment checks and the reference-comparison tests.",
-          "The ncu captures below were taken before the last tuning steps of two kernels: `mlp_fused_step_kernel` "
-          "(captured in its in-place-update form; the in-kernel push / Hogwild modes add phases after the ones profiled) and "
-          "`sparse_wd_kernel` (captured with 4-8 embedding rows in flight per warp and 256-thread CTAs; the final kernel "
-          "keeps 16 in flight in 128-thread CTAs: 30 us instead of 37 us per step).  The bench JSON files are from the final tree.", ""]
+          "The launch lists of `mnist` and `wd` predate the last tuning step of their kernels (their ncu captures do not).  The bench JSON files are from the final tree.", ""]
     for cfg in ("mnist", "mnist_chain", "wide", "sparse", "wd"):
         rep = os.path.join(GP, f"prof_{cfg}.ncu-rep")
         if os.path.exists(rep):
