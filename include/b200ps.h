@@ -296,6 +296,14 @@ int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* con
  * read round trip and no fence (2 one-way hops instead of ~5).  ll_grads[r]: world*max_shard_elems
  * uint2 per rank; ll_params[r]: total_elems uint2 per rank (both symmetric, zero-initialised).
  * All replicas are aggregated (replicas_to_aggregate == world). */
+/* K1-NVLS: the synchronous push through NVSwitch multicast.  mc_grads / mc_work are MULTICAST addresses of the
+ * fp32 gradient and working-copy buffers (memory bound to an NVLS multicast object, e.g. torch symmetric memory:
+ * b200ps/parallel/nvls.py); the owner of [lo, hi) (multiples of 4) does multimem.ld_reduce.add (the switch sums
+ * the replicas' gradients), master -= step * sum on its fp32 master (indexed by global element), and
+ * multimem.st of the fresh values to every replica.  The caller provides the cross-rank barrier before
+ * ("gradients written") and after ("parameters landed"). */
+int b200ps_push_sync_nvls(const float* mc_grads, float* mc_work, float* master, int64_t lo, int64_t hi, float step,
+                          uint64_t* global_step, int32_t max_ctas, b200ps_stream_t stream);
 int b200ps_push_sync_ll(uint32_t* const* pads, float* const* masters, const void* const* grads,
                         const int64_t* bounds, uint64_t* const* global_steps, void* const* ll_grads,
                         void* const* ll_params, int32_t world, int32_t rank_base, int32_t local_ranks,

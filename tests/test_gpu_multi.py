@@ -53,3 +53,20 @@ def test_multi_gpu_trainers(native_lib, tmp_path):
     ops.synth_mnist(x, y, seed=1, offset=0)
     acc, _ = tr.evaluate(x, y)
     assert abs(acc - res["sync_acc"]) < 1e-6
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_nvls_multimem_push(native_lib, tmp_path):
+    """K1-NVLS: multimem.ld_reduce / multimem.st push on torch symmetric memory == mean-gradient SGD on every replica."""
+    n = min(_ngpu(), 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", "29617", os.path.join(ROOT, "tests", "nvls_worker.py"), str(tmp_path)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+        open(os.path.join(ROOT, "gpurun_out", "nvls_worker.log"), "w").write(r.stdout + r.stderr)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-4000:]
+    res = json.load(open(tmp_path / "nvls_result.json"))
+    if "error" in res and "multicast is not available" in res["error"]:
+        pytest.skip("no NVLS multicast on this system")
+    assert "error" not in res, res
+    assert res["ok"] and res["replicas_identical"] and res["global_step"] == 3, res
