@@ -2,7 +2,7 @@
 # Per-kernel SASS evidence (CPU only): which Blackwell-native instructions each kernel of
 # libb200ps.so contains.  UTC*MMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA tensor load,
 # UBLKCP = cp.async.bulk, LDGSTS = cp.async, SYNCS = mbarrier, RED/ATOM = reductions/atomics, MEMBAR = fences,
-# STG/LDG.E.64.STRONG.SYS = the 8-byte {value, epoch} packets of the low-latency push.
+# STG/LDG.E.64.STRONG.SYS = the 8-byte {value, epoch} packets of the low-latency push, LDGMC = multimem.ld_reduce (NVLS).
 lib=${1:-b200ps/_lib/libb200ps.so}
 cuobjdump -sass "$lib" | awk '
 /Function :/ { fn=$3; next }
@@ -15,7 +15,7 @@ END { for (k in c) print k, c[k] }' | sort | c++filt | awk '{n=$NF; $NF=""; prin
 cuobjdump -sass "$lib" | awk '
 /Function :/ { fn=$3; next }
 fn != "" {
-  if (match($0, /UTC[A-Z]*MMA|UTCBAR|LDTM|UTMALDG|UBLKCP[A-Z.]*|LDGSTS[A-Z.0-9]*|STG\.E\.64\.STRONG\.SYS|LDG\.E\.64\.STRONG\.SYS|SYNCS\.ARRIVE\.TRANS64|SYNCS\.PHASECHK[A-Z.0-9]*|HMMA|RED\.E\.ADD[A-Z.0-9]*|REDG\.E[A-Z.0-9]*|ATOMG\.E[A-Z.0-9]*|ATOM\.E[A-Z.0-9]*|MEMBAR\.[A-Z.]*/)) {
+  if (match($0, /UTC[A-Z]*MMA|UTCBAR|LDTM|UTMALDG|LDGMC[A-Z.0-9x]*|UBLKCP[A-Z.]*|LDGSTS[A-Z.0-9]*|STG\.E\.64\.STRONG\.SYS|LDG\.E\.64\.STRONG\.SYS|SYNCS\.ARRIVE\.TRANS64|SYNCS\.PHASECHK[A-Z.0-9]*|HMMA|RED\.E\.ADD[A-Z.0-9]*|REDG\.E[A-Z.0-9]*|ATOMG\.E[A-Z.0-9]*|ATOM\.E[A-Z.0-9]*|MEMBAR\.[A-Z.]*/)) {
     m=substr($0, RSTART, RLENGTH); c[fn"\t"m]++
   }
 }
