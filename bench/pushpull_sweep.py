@@ -79,12 +79,25 @@ def main():
             dist.reduce_scatter_tensor(sl, g, op=dist.ReduceOp.SUM)
             master.add_(sl, alpha=-1e-3)
 
+        # K1-NVLS: the same push through NVSwitch multicast (torch symmetric memory); skipped where unavailable
+        t_nvls = None
+        if N > 1 and os.environ.get("SWEEP_NVLS", "1") != "0":
+            try:
+                from b200ps.parallel.nvls import NvlsGroup
+                nv = NvlsGroup(total, 1e-3)
+                nv.grads.normal_()
+                t_nvls = timeit(nv.push_sync, iters, ctx)
+                del nv
+            except Exception as e:  # noqa: BLE001
+                if ctx.rank == 0 and S == sizes[0]:
+                    print("nvls push unavailable:", type(e).__name__, str(e)[:200], flush=True)
         n_push = timeit(nccl_push, iters, ctx)
         n_pull = timeit(lambda: dist.all_gather_into_tensor(w, master), iters, ctx)
         n_async = timeit(nccl_async, iters, ctx)
         f = (N - 1) / N
         rec = {"bytes": S, "n_gpus": N,
                "push_sync_us": round(t_push, 2), "nccl_push_us": round(n_push, 2),
+               "nvls_push_us": None if t_nvls is None else round(t_nvls, 2),
                "pull_us": round(t_pull, 2), "nccl_allgather_us": round(n_pull, 2),
                "push_async_us": round(t_async, 2), "nccl_rs_apply_us": round(n_async, 2),
                "push_sync_GBs_per_dir": round(2 * f * S / t_push / 1e3, 1),
