@@ -75,7 +75,7 @@ class SparseLR:
         if not hasattr(self, "_gs0"):
             self._gs0 = tensor_from_ptr(gs, 8, store.device).view(torch.int64)
         ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, pred=bufs["pred"], loss_sum=bufs["loss"],
+                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], loss_sum=bufs["loss"],
                       global_step=self._gs0, forward=True, update=True, lr=lr)
         return bufs["loss"]
 
@@ -88,12 +88,12 @@ class SparseLR:
         bufs["loss"].zero_()
         N = replicas or store.world
         ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, pred=bufs["pred"], dz_out=bufs["dz"],
+                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], dz_out=bufs["dz"],
                       loss_sum=bufs["loss"], forward=True, update=False)
         store.barrier()                       # nobody updates rows somebody is still reading
         gstep = store.global_step_tensor(rank)  # sync: every rank counts one step per aggregate
         ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, dz_in=bufs["dz"], global_step=gstep,
+                      rows_per_shard=sv.rows_per_shard, features=self.features, dz_in=bufs["dz"], global_step=gstep,
                       forward=False, update=True, lr=lr / N)
         store.barrier()                       # all updates landed before the next read
         return bufs["loss"]
@@ -105,6 +105,6 @@ class SparseLR:
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
         ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, pred=bufs["pred"], loss_sum=bufs["loss"],
+                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], loss_sum=bufs["loss"],
                       forward=True, update=False)
         return bufs["pred"], bufs["loss"]

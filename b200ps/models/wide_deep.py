@@ -98,7 +98,7 @@ class SparseWideDeep:
             self._tab = dict(
                 wide_table=None if w is None else w.table, wide_rows_per_shard=0 if w is None else w.rows_per_shard,
                 emb_table=e.table, emb_rows_per_shard=e.rows_per_shard, dim=self.dim,
-                w2_table=w2.table, w2_rows_per_shard=w2.rows_per_shard,
+                w2_table=w2.table, w2_rows_per_shard=w2.rows_per_shard, features=self.features,
                 bias=tensor_from_ptr(store.master_address(self.Bn), 4, store.device).view(torch.float32))
             if self.deferred and self.P in store.sparse:
                 pe, p2 = store.sparse_var(self.P), store.sparse_var(self.P2)

@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -260,27 +260,50 @@ def device_ptr_table(ptrs: Sequence[int], device) -> torch.Tensor:
     return torch.tensor([int(p) for p in ptrs], dtype=torch.int64, device=device)
 
 
-def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, pred=None, dz_out=None,
+def sparse_bad_ids(reset: bool = True) -> int:
+    """Number of feature ids the sparse kernels refused on this device since the last reset (ids outside
+    ``[0, features)`` never touch memory; they are skipped and counted).  Synchronises the device."""
+    n = C.c_uint64()
+    check(native.load().b200ps_sparse_bad_ids(C.byref(n), int(reset)), "sparse_bad_ids")
+    return int(n.value)
+
+
+def check_sparse_ids() -> None:
+    """Raise ``ValueError`` if any step since the last check saw a feature id outside ``[0, features)`` — the
+    InvalidArgument of ``embedding_lookup_sparse`` (lr2.py:390), reported at the caller's next sync point."""
+    n = sparse_bad_ids(reset=True)
+    if n:
+        raise ValueError(f"{n} feature id(s) outside [0, features) were skipped by the sparse kernels "
+                         f"(bad input line or wrong --features)")
+
+
+def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, features=None, pred=None, dz_out=None,
               dz_in=None, loss_sum=None, global_step=None, forward=True, update=True, lr=0.0,
               grad_scale=None, loss_scale=None, stream=None):
-    """Sparse LR step over a row-sharded weight (K4/K5).  ``w_table`` = device_ptr_table of shard bases."""
+    """Sparse LR step over a row-sharded weight (K4/K5).  ``w_table`` = device_ptr_table of shard bases.
+    ``features`` bounds the valid ids (default: every row of every shard)."""
+    if features is None:
+        features = rows_per_shard * w_table.numel()
     _cuda(row_ptr, fid, fval, labels, w_table, bias)
     B = labels.numel()
     gs = (1.0 / B) if grad_scale is None else grad_scale
     ls = (1.0 / B) if loss_scale is None else loss_scale
     check(native.load().b200ps_sparse_lr(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), ptr(w_table),
                                          ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in), ptr(loss_sum),
-                                         ptr(global_step), B, rows_per_shard, int(forward), int(update),
-                                         lr, gs, ls, stream_ptr(stream)), "sparse_lr")
+                                         ptr(global_step), B, rows_per_shard, int(features), int(forward),
+                                         int(update), lr, gs, ls, stream_ptr(stream)), "sparse_lr")
 
 
 def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, emb_table, emb_rows_per_shard, dim,
               w2_table, w2_rows_per_shard, bias, pred=None, dz_out=None, dz_in=None, loss_sum=None,
               global_step=None, forward=True, update=True, lr=0.0, grad_scale=None, loss_scale=None,
-              pend_table=None, pend_rows_per_shard=0, pend2_table=None, pend2_rows_per_shard=0, stream=None):
+              pend_table=None, pend_rows_per_shard=0, pend2_table=None, pend2_rows_per_shard=0, features=None,
+              stream=None):
     """Sparse wide & deep step over row-sharded tables (K4w/K5w): see include/b200ps.h b200ps_sparse_wd.
     With ``pend_table``/``pend2_table`` the updates are deferred (scalar coefficients; ``sparse_wd_apply``)."""
     _cuda(row_ptr, fid, fval, labels, emb_table, w2_table, bias)
+    if features is None:
+        features = emb_rows_per_shard * emb_table.numel()
     B = labels.numel()
     gs = (1.0 / B) if grad_scale is None else grad_scale
     ls = (1.0 / B) if loss_scale is None else loss_scale
@@ -289,7 +312,8 @@ def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, em
                                          ptr(w2_table), w2_rows_per_shard, ptr(bias), ptr(pred), ptr(dz_out),
                                          ptr(dz_in), ptr(loss_sum), ptr(global_step), B, int(forward),
                                          int(update), lr, gs, ls, ptr(pend_table), pend_rows_per_shard,
-                                         ptr(pend2_table), pend2_rows_per_shard, stream_ptr(stream)), "sparse_wd")
+                                         ptr(pend2_table), pend2_rows_per_shard, int(features),
+                                         stream_ptr(stream)), "sparse_wd")
 
 
 def sparse_wd_apply(pend_local, wide_local, emb_local, rows_local, dim, w2_table, w2_rows_per_shard, pend2_local,

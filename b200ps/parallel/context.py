@@ -58,7 +58,25 @@ class Context:
         return float(t.item())
 
     def close(self) -> None:
+        """Release the symmetric memory: unmap the peers' buffers, control barrier, free our own."""
         self.pool.close()
+
+    def shutdown(self) -> None:
+        """Orderly end of a multi-process run: ``close()``, a last control barrier, then the control-plane
+        process group is destroyed so that the interpreter exits normally (no ``os._exit``)."""
+        import gc
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        gc.collect()
+        self.close()
+        if self.group is not None:
+            import torch.distributed as dist
+            try:
+                self.control_barrier()
+            finally:
+                self.group = None
+                if dist.is_initialized():
+                    dist.destroy_process_group()
 
 
 def init_from_env(virtual_world: int = 0, device: Optional[str] = None, timeout_s: float = 300.0) -> Context:

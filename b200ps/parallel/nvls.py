@@ -52,12 +52,14 @@ class NvlsGroup:
         self._hw.barrier()
         self._lib = native.load()
 
-    def push_sync(self, stream=None) -> None:
-        """Mean-gradient SGD step on this rank's slice through the switch; all ranks call it together."""
+    def push_sync(self) -> None:
+        """Mean-gradient SGD step on this rank's slice through the switch; all ranks call it together.
+        The two symmetric-memory barriers and the kernel are all issued on torch's CURRENT stream (the barriers
+        have no stream argument, so a launch on any other stream would be unordered against them)."""
         self._hg.barrier()                                   # every replica's gradients are written
         native.check(self._lib.b200ps_push_sync_nvls(int(self._hg.multicast_ptr), int(self._hw.multicast_ptr),
                                                      self.master.data_ptr(), self.lo, self.hi, self.lr / self.world,
-                                                     self.gstep.data_ptr(), 0, native.stream_ptr(stream)),
+                                                     self.gstep.data_ptr(), 0, native.stream_ptr(None)),
                      "push_sync_nvls")
         self._hw.barrier()                                   # every replica's working copy has the fresh values
 

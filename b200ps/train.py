@@ -505,6 +505,14 @@ class SparseLRTrainer(_TrainerBase):
     def predict(self, batch):
         return self.model.predict(self.store, batch)
 
+    def read_loss(self) -> float:
+        """Loss of the last step; raises ``ValueError`` if any step since the last call saw a feature id
+        outside ``[0, features)`` (the kernels skip and count them)."""
+        v = super().read_loss()
+        from . import ops
+        ops.check_sparse_ids()
+        return v
+
     # -- packed batches (b200ps.data.native_loader): one pinned buffer per batch, one H2D copy, one graph
     def host_feeder(self, layout, slots: int = 4):
         """A ``HostFeeder`` whose unit is one training step on a *packed batch* (``PackedLayout``): the

@@ -34,8 +34,9 @@ MNIST_TRAIN = 55000
 class ShardedPS:
     """Flat fp32 parameters, 1/N master slice per rank, NCCL collectives for pull/push."""
 
-    def __init__(self, shapes, rank, world, device, seed=1, lowp=None):
+    def __init__(self, shapes, rank, world, device, seed=1, lowp=None, group=None):
         self.rank, self.world, self.device = rank, world, device
+        self.group = group
         self.shapes = shapes
         sizes = [int(torch.Size(s).numel()) for s in shapes.values()]
         total = sum(sizes)
@@ -71,13 +72,13 @@ class ShardedPS:
         if self.world == 1:
             self.work[:self.shard].copy_(src)
         else:
-            dist.all_gather_into_tensor(self.work, src)
+            dist.all_gather_into_tensor(self.work, src, group=self.group)
 
     def push_sync(self, lr):
         if self.world == 1:
             self.master.add_(self.grads[:self.shard].float(), alpha=-lr)
         else:
-            dist.reduce_scatter_tensor(self._gslice, self.grads, op=dist.ReduceOp.AVG)
+            dist.reduce_scatter_tensor(self._gslice, self.grads, op=dist.ReduceOp.AVG, group=self.group)
             self.master.add_(self._gslice.float(), alpha=-lr)
         self.global_step += 1
         self.pull()
@@ -86,7 +87,7 @@ class ShardedPS:
         if self.world == 1:
             self.master.add_(self.grads[:self.shard].float(), alpha=-lr)
         else:
-            dist.reduce_scatter_tensor(self._gslice, self.grads, op=dist.ReduceOp.SUM)
+            dist.reduce_scatter_tensor(self._gslice, self.grads, op=dist.ReduceOp.SUM, group=self.group)
             self.master.add_(self._gslice.float(), alpha=-lr)
         self.global_step += self.world
         self.pull()
@@ -129,9 +130,11 @@ class SparsePS:
 
     def step(self, batch, lr):
         rp, fid, fv, y = batch
-        n = int(rp[-1])
-        fid, fv = fid[:n], fv[:n]
         B = y.numel()
+        if self.world == 1:
+            return self._step_local(rp, fid, fv, y, lr)
+        n = int(rp[-1])          # the variable-split all_to_all API needs the counts on the host
+        fid, fv = fid[:n], fv[:n]
         row_of = torch.repeat_interleave(torch.arange(B, device=self.device), (rp[1:] - rp[:-1]).long())
         if self.world == 1:
             w = self.W[fid]
@@ -165,6 +168,24 @@ class SparsePS:
             dist.all_reduce(db)
             self.b -= lr * db
         self.global_step += self.world
+        return loss.detach()
+
+
+    def _step_local(self, rp, fid, fv, y, lr):
+        """One GPU: no host read anywhere (capturable).  The CSR buffers are padded to a fixed capacity;
+        slots past rp[-1] are masked on the device."""
+        B, cap = y.numel(), fid.numel()
+        pos = torch.arange(cap, device=self.device, dtype=torch.int32)
+        live = pos < rp[-1]
+        row_of = torch.searchsorted(rp[1:].contiguous(), pos, right=True).clamp_(max=B - 1).long()
+        fidc = torch.where(live, fid, torch.zeros_like(fid))
+        fvm = torch.where(live, fv, torch.zeros_like(fv))
+        z = torch.zeros(B, device=self.device).index_add_(0, row_of, self.W[fidc] * fvm) + self.b
+        loss = Fnn.binary_cross_entropy_with_logits(z, y)
+        dz = (torch.sigmoid(z) - y) / B
+        self.W.index_add_(0, fidc, dz[row_of] * fvm, alpha=-lr)
+        self.b -= lr * dz.sum()
+        self.global_step += 1
         return loss.detach()
 
 
@@ -229,9 +250,76 @@ class WideDeepPS:
         return loss.detach()
 
 
-def _timed(steps, fn, world):
+class GraphedMLPStep:
+    """The same `mlp_step` (autograd + NCCL collectives) captured once into a CUDA graph on static input
+    buffers and replayed: the launch-overhead-free form of the baseline."""
+
+    def __init__(self, ps, B, lr, mode, device):
+        self.ps, self.lr, self.mode = ps, lr, mode
+        self.x = torch.zeros(B, 784, device=device)
+        self.y = torch.zeros(B, device=device, dtype=torch.int64)
+        self.loss = torch.zeros((), device=device)
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self.loss.copy_(mlp_step(ps, self.x, self.y, lr, mode))
+        torch.cuda.current_stream(device).wait_stream(side)
+        torch.cuda.synchronize(device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss.copy_(mlp_step(ps, self.x, self.y, lr, mode))
+
+    def __call__(self, x, y):
+        self.x.copy_(x, non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+        self.graph.replay()
+        return self.loss
+
+
+def run_mnist(args, rank, world, dev, mode, group=None, graphed=True):
+    """MNIST 784-100-10, batch 100 per worker, by bench.py's protocol.  Returns eager numbers and, under
+    "graphed", the CUDA-graph replay of the same step."""
+    sys.path.insert(0, ROOT)
+    from b200ps import ops                      # input tensors only
+    W, B = max(args.warmup, 3), 100
+    ps = ShardedPS({"W1": (784, 100), "W2": (100, 10), "b1": (100,), "b2": (10,)}, rank, world, dev, group=group)
+    data = torch.empty(MNIST_TRAIN, 784, device=dev); lab = torch.empty(MNIST_TRAIN, device=dev, dtype=torch.int32)
+    ops.synth_mnist(data, lab, seed=1, offset=rank * MNIST_TRAIN)
+    xs, ys = data.view(-1, B, 784), lab.long().view(-1, B)
+    nb = xs.shape[0]
+    hx, hy = xs[:64].cpu().pin_memory(), ys[:64].cpu().pin_memory()
+    sx, sy = torch.empty(B, 784, device=dev), torch.empty(B, device=dev, dtype=torch.int64)
+
+    def measure(step_dev, step_host):
+        for i in range(W):
+            step_dev(i)
+        ms = _timed(args.steps, step_dev, world, group)
+        for i in range(W):
+            step_host(i)
+        ms2 = _wall(args.steps, step_host, world, group)
+        return {"value": B * world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
+                "e2e": {"value": B * world * args.steps / (ms2 / 1e3), "unit": "examples/s",
+                        "h2d_bytes_per_step": B * 784 * 4 + B * 8, "d2h_bytes_per_step": 4}}
+
+    def e2e_eager(i):
+        sx.copy_(hx[i % 64], non_blocking=True); sy.copy_(hy[i % 64], non_blocking=True)
+        return float(mlp_step(ps, sx, sy, 0.0005, mode).item())
+
+    out = measure(lambda i: mlp_step(ps, xs[i % nb], ys[i % nb], 0.0005, mode), e2e_eager)
+    if graphed:
+        try:
+            g = GraphedMLPStep(ps, B, 0.0005, mode, dev)
+            out["graphed"] = measure(lambda i: g(xs[i % nb], ys[i % nb]),
+                                     lambda i: float(g(hx[i % 64], hy[i % 64]).item()))
+        except Exception as e:                 # capture of the collectives can fail on some NCCL builds
+            out["graphed"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
+
+
+def _timed(steps, fn, world, group=None):
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=group)
     torch.cuda.synchronize()
     st, en = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     st.record()
@@ -241,13 +329,13 @@ def _timed(steps, fn, world):
     torch.cuda.synchronize()
     ms = torch.tensor([st.elapsed_time(en)], device="cuda")
     if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
     return float(ms.item())
 
 
-def _wall(steps, fn, world):
+def _wall(steps, fn, world, group=None):
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=group)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(steps):
@@ -255,7 +343,7 @@ def _wall(steps, fn, world):
     torch.cuda.synchronize()
     ms = torch.tensor([(time.perf_counter() - t0) * 1e3], device="cuda")
     if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
     return float(ms.item())
 
 
@@ -276,29 +364,7 @@ def main_from_bench(args) -> int:
             else [args.config])
     for cfg in cfgs:
         if cfg.startswith("mnist"):
-            mode = "sync" if cfg.endswith("_sync") else "async"
-            B = 100
-            ps = ShardedPS({"W1": (784, 100), "W2": (100, 10), "b1": (100,), "b2": (10,)}, rank, world, dev)
-            data = torch.empty(MNIST_TRAIN, 784, device=dev); lab = torch.empty(MNIST_TRAIN, device=dev, dtype=torch.int32)
-            ops.synth_mnist(data, lab, seed=1, offset=rank * MNIST_TRAIN)
-            xs, ys = data.view(-1, B, 784), lab.long().view(-1, B)
-            nb = xs.shape[0]
-            step = lambda i: mlp_step(ps, xs[i % nb], ys[i % nb], 0.0005, mode)
-            for i in range(W):
-                step(i)
-            ms = _timed(args.steps, step, world)
-            hx, hy = xs[:64].cpu().pin_memory(), ys[:64].cpu().pin_memory()
-            sx, sy = torch.empty(B, 784, device=dev), torch.empty(B, device=dev, dtype=torch.int64)
-
-            def e2e(i):
-                sx.copy_(hx[i % 64], non_blocking=True); sy.copy_(hy[i % 64], non_blocking=True)
-                return float(mlp_step(ps, sx, sy, 0.0005, mode).item())
-            for i in range(W):
-                e2e(i)
-            ms2 = _wall(args.steps, e2e, world)
-            out[cfg] = {"value": B * world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
-                        "e2e": {"value": B * world * args.steps / (ms2 / 1e3), "unit": "examples/s",
-                                "h2d_bytes_per_step": B * 784 * 4 + B * 8, "d2h_bytes_per_step": 4}}
+            out[cfg] = run_mnist(args, rank, world, dev, "sync" if cfg.endswith("_sync") else "async")
         elif cfg == "wide_mlp":
             B, L, D = args.wide_batch, args.wide_layers, args.wide_hidden
             shapes = {**{f"W{l}": (D, D) for l in range(L)}, **{f"b{l}": (D,) for l in range(L)}}
@@ -337,6 +403,7 @@ def main_from_bench(args) -> int:
                 "value": out[primary]["value"], "unit": "examples/s", "n_gpus": world, "steps": args.steps, "warmup": W,
                 "ms_per_step": out[primary]["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "data": "synthetic", "config": {"model": primary}, "e2e": out[primary].get("e2e"),
+                "graphed": out[primary].get("graphed"),
                 "extra": {k: v for k, v in out.items() if k != primary}}
         print(json.dumps(line))
         sys.stdout.flush()

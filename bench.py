@@ -102,6 +102,24 @@ def _physical_gpu_index(local_index: int) -> int:
 # ----------------------------------------------------------------------------------------
 # measurement helpers
 # ----------------------------------------------------------------------------------------
+TRIALS = 5
+
+
+def timed_trials(ctx, torch, sampler, steps, fn, trials=None):
+    """`trials` back-to-back timed regions of exactly `steps` steps each; returns (median ms, spread dict).
+    The headline is the median trial; min / max travel with it so one sub-millisecond bracket is never the
+    only evidence."""
+    ms = sorted(timed_region(ctx, torch, sampler, steps, fn) for _ in range(trials or TRIALS))
+    med = ms[len(ms) // 2]
+    return med, {"n": len(ms), "steps_per_trial": steps, "ms_median": med, "ms_min": ms[0], "ms_max": ms[-1],
+                 "rel_spread": (ms[-1] - ms[0]) / med if med else None}
+
+
+def wall_trials(ctx, torch, sampler, steps, fn, trials=3):
+    ms = sorted(wall_region(ctx, torch, sampler, steps, fn) for _ in range(trials))
+    return ms[len(ms) // 2]
+
+
 def timed_region(ctx, torch, sampler, steps, fn):
     """barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks."""
     ctx.control_barrier()
@@ -131,6 +149,25 @@ def wall_region(ctx, torch, sampler, steps, fn):
     sampler.active.clear()
     ctx.control_barrier()
     return ctx.all_reduce_max(ms)
+
+
+def _release(tr, *feeders):
+    """Orderly release of a trainer: native feeders (threads, streams, events) first, then the captured
+    graphs; the symmetric buffers themselves go when the context closes."""
+    import gc
+    import torch
+    torch.cuda.synchronize()
+    for f in list(feeders) + [v for k, v in list(vars(tr).items()) if k.startswith(("_feeder", "_loader_feeder"))]:
+        try:
+            if f is not None:
+                f.close()
+        except Exception:
+            pass
+    for k in ("_step", "_step_res", "_step_res_multi", "_graphs", "_ring"):
+        if hasattr(tr, k):
+            delattr(tr, k)
+    gc.collect()
+    torch.cuda.synchronize()
 
 
 def launches_of(fn, native):
@@ -180,10 +217,11 @@ def bench_mnist(ctx, args, sampler, mode):
 
     for i in range(max(args.warmup, 3)):
         dev_step(i)
-    if resident:
-        ms = timed_region(ctx, torch, sampler, 1, lambda i: tr.run_resident(args.steps))   # exactly K steps
+    if resident:       # each trial = exactly K steps
+        ms, spread = timed_trials(ctx, torch, sampler, 1, lambda i: tr.run_resident(args.steps))
+        spread["steps_per_trial"] = args.steps
     else:
-        ms = timed_region(ctx, torch, sampler, args.steps, dev_step)
+        ms, spread = timed_trials(ctx, torch, sampler, args.steps, dev_step)
     loss1 = tr.read_loss()
 
     # ---- end to end: pinned host batch -> H2D -> step -> loss D2H, every step
@@ -214,7 +252,7 @@ def bench_mnist(ctx, args, sampler, mode):
         e2e_pipelined(-1)
     while pending:
         pending.pop(0).result()
-    ms_e2e = wall_region(ctx, torch, sampler, args.steps, e2e_pipelined)
+    ms_e2e = wall_trials(ctx, torch, sampler, args.steps, e2e_pipelined)
     # chunked form (MLPTrainer.host_feeder(steps_per_call=8), what fit_from_host drives): 8 batches per H2D
     # copy and graph launch, all 8 losses written back per chunk — same bytes per step, 1/8 of the host calls
     K = 8
@@ -243,9 +281,9 @@ def bench_mnist(ctx, args, sampler, mode):
     gstep = tr.global_step
     out = {
         "value": B * ctx.world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
-        "gpu_launches": per_step * args.steps, "launches_per_step": per_step,
+        "gpu_launches": per_step * args.steps, "launches_per_step": per_step, "trials": spread,
         "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
-                "ms_per_step": ms_e2e / args.steps,
+                "ms_per_step": ms_e2e / args.steps, "trials": 3,
                 "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 4,
                 "api": "MLPTrainer.step_from_host_async (HostFeeder ring: H2D on a copy stream, loss written to pinned "
                        "host memory by the step kernel; loss of step t read after step t+4 is queued)",
@@ -264,7 +302,7 @@ def bench_mnist(ctx, args, sampler, mode):
                                                         else " (per-step device copy)") + "; no explicit L2 flush",
                    "cuda_graph": not args.no_graph, "steps_per_graph_replay": args.steps_per_graph if resident else 1},
     }
-    tr.store  # keep alive until here
+    _release(tr, feeder)
     return out
 
 
@@ -295,7 +333,7 @@ def bench_wide(ctx, args, sampler):
 
     for i in range(3):
         dev_step(i)
-    ms = timed_region(ctx, torch, sampler, steps, dev_step)
+    ms, spread = timed_trials(ctx, torch, sampler, steps, dev_step, trials=3)
     loss1 = tr.read_loss()
     hx, hy = xs[:2].cpu().pin_memory(), ys[:2].cpu().pin_memory()
 
@@ -307,9 +345,10 @@ def bench_wide(ctx, args, sampler):
     flops = tr.model.flops_per_step(B)
     peak = _measured_peaks().get("bf16_tflops_sustained")
     tf = flops / (ms / steps / 1e3) / 1e12
+    _release(tr)
     return {
         "value": B * ctx.world * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
-        "gpu_launches": per_step * steps, "launches_per_step": per_step,
+        "gpu_launches": per_step * steps, "launches_per_step": per_step, "trials": spread,
         "tflops_per_gpu": tf, "fraction_of_measured_bf16_sustained": (tf / peak) if peak else None,
         "e2e": {"value": B * ctx.world * steps / (ms_e2e / 1e3), "unit": "examples/s",
                 "h2d_bytes_per_step": B * D * 2 + B * 4, "d2h_bytes_per_step": 4},
@@ -351,7 +390,7 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     for i in range(max(args.warmup, 3)):
         tr.step(batches[i % ring])
     loss0 = tr.read_loss()
-    ms = timed_region(ctx, torch, sampler, args.steps, lambda i: tr.step(batches[i % ring]))
+    ms, spread = timed_trials(ctx, torch, sampler, args.steps, lambda i: tr.step(batches[i % ring]))
     loss1 = tr.read_loss()
     # end to end: packed batches (the native loader's format: one pinned buffer per batch) -> HostFeeder:
     # one H2D copy + one graph launch per step, loss written back to pinned memory, 3 steps in flight
@@ -371,17 +410,19 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
 
     for i in range(3):
         feeder.submit(host[i]).result()
-    ms_e2e = wall_region(ctx, torch, sampler, args.steps, e2e_step)
+    ms_e2e = wall_trials(ctx, torch, sampler, args.steps, e2e_step)
     host = [(host[0],)]
     h2d = sum(t.numel() * t.element_size() for t in host[0])
+    gstep = tr.global_step
+    _release(tr, feeder)
     return {
         "value": B * ctx.world * args.steps / (ms / 1e3), "ms_per_step": ms / args.steps,
-        "gpu_launches": per_step * args.steps, "launches_per_step": per_step,
+        "gpu_launches": per_step * args.steps, "launches_per_step": per_step, "trials": spread,
         "e2e": {"value": B * ctx.world * args.steps / (ms_e2e / 1e3), "unit": "examples/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "api": "SparseLRTrainer.host_feeder(PackedLayout): packed pinned batch -> one H2D copy + one graph "
                        "launch per step, loss written to pinned memory, read after 3 more steps are queued"},
-        "loss_first": loss0, "loss_last": loss1, "global_step": tr.global_step,
+        "loss_first": loss0, "loss_last": loss1, "global_step": gstep,
         # rows gathered and scattered per step: one 4*dim-byte row in, one out (red) per non-zero
         "row_traffic_GBps_per_gpu": (2 * nnz * B * 4 * max(deep_dim, 1) / (ms / args.steps / 1e3) / 1e9),
         "config": {"model": (f"sparse_wide_deep_2^22_features_dim{deep_dim}_~100nnz" if deep_dim
@@ -398,12 +439,27 @@ def _measured_peaks():
         return {}
 
 
-def _baseline_number(config: str, n: int):
-    try:
-        d = json.load(open(os.path.join(ROOT, "baseline", "measured.json")))
-        return d.get(config, {}).get(str(n))
-    except Exception:
+def _same_run_baseline(ctx, args, primary_name):
+    """The PyTorch+NCCL(+cuBLAS) baseline arm (baseline/ps_nccl.py) for the PRIMARY config, measured in this very
+    invocation on this very box, after the b200ps arm has released its memory: eager and CUDA-graphed.
+    `vs_baseline` is computed from these numbers only (never from a stored file); null when it cannot run."""
+    if not primary_name.startswith("mnist") or args.no_baseline:
         return None
+    import torch
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import ps_nccl
+        group = None
+        if ctx.world > 1:
+            import datetime
+            import torch.distributed as dist
+            group = dist.new_group(backend="nccl", timeout=datetime.timedelta(seconds=300), device_id=ctx.device)
+        out = ps_nccl.run_mnist(args, ctx.rank, ctx.world, ctx.device,
+                                "sync" if primary_name.endswith("_sync") else "async", group=group)
+        torch.cuda.synchronize()
+        return out
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 # ----------------------------------------------------------------------------------------
@@ -425,6 +481,8 @@ def main():
     ap.add_argument("--wide-hidden", dest="wide_hidden", type=int, default=8192)
     ap.add_argument("--wide-max-steps", dest="wide_max_steps", type=int, default=20)
     ap.add_argument("--sparse-batch", dest="sparse_batch", type=int, default=500)
+    ap.add_argument("--no-baseline", dest="no_baseline", action="store_true",
+                    help="skip the same-run PyTorch+NCCL baseline of the primary config (vs_baseline becomes null)")
     args = ap.parse_args()
 
     if args.impl == "reference":
@@ -472,31 +530,42 @@ def main():
                 extra[name] = runners[name]()
             except Exception as e:  # an extra config must never cost the headline line
                 extra[name] = {"error": f"{type(e).__name__}: {e}"}
+    # ---- orderly teardown of the b200ps arm: peers unmap each other's buffers, a control barrier, owners free
+    torch.cuda.synchronize()
+    import gc
+    gc.collect()
+    ctx.close()
+    base = _same_run_baseline(ctx, args, primary_name)
     sampler.stop()
     if ctx.rank == 0:
-        base = _baseline_number(primary_name, ctx.world)
+        base_best, base_e2e = None, None
+        if base and "value" in base:
+            g = base.get("graphed") or {}
+            base_best = max(base["value"], g.get("value", 0.0))
+            base_e2e = max(base["e2e"]["value"], (g.get("e2e") or {}).get("value", 0.0))
         line = {
             "metric": "examples/sec (device-timed, max over ranks)", "value": primary["value"],
             "unit": "examples/s", "n_gpus": ctx.world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": primary["ms_per_step"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": (primary["value"] / base) if base else None,
-            "dtype": "fp32 (exact-fp32 one-launch step; B200PS_FUSED_STEP=0 selects the tf32 tensor-core chain)"
-                     if primary_name.startswith("mnist") else ("fp32" if primary_name.startswith("sparse") else "bf16"),
+            "vs_baseline": (primary["value"] / base_best) if base_best else None,
+            "dtype": primary.get("dtype") or ("fp32" if primary_name.startswith(("mnist", "sparse")) else "bf16"),
             "data": "synthetic (on-device Philox generators), random-init weights",
             "config": primary["config"], "clocks": sampler.summary(), "e2e": primary["e2e"],
-            "gpu_launches": primary["gpu_launches"], "impl": "b200ps",
+            "gpu_launches": primary["gpu_launches"], "impl": "b200ps", "trials": primary.get("trials"),
+            "baseline_same_run": ({"what": "baseline/ps_nccl.py (PyTorch + NCCL + cuBLAS, same PS semantics), same "
+                                           "invocation, same box; vs_baseline divides by the faster of eager / graphed",
+                                   "eager": {k: v for k, v in base.items() if k != "graphed"},
+                                   "graphed": base.get("graphed"),
+                                   "e2e_ratio": (primary["e2e"]["value"] / base_e2e) if base_e2e else None}
+                                  if base else None),
             "detail": {k: v for k, v in primary.items() if k not in ("value", "ms_per_step", "config", "e2e",
-                                                                     "gpu_launches")},
+                                                                     "gpu_launches", "trials", "dtype")},
             "extra": extra,
         }
-        for name, ex in extra.items():
-            b = _baseline_number(name, ctx.world)
-            if b and "value" in ex:
-                ex["vs_baseline"] = ex["value"] / b
         print(json.dumps(line))
         sys.stdout.flush()
-    ctx.control_barrier()
-    os._exit(0)   # skip CUDA IPC teardown ordering issues at interpreter exit
+    ctx.shutdown()
+    return 0
 
 
 if __name__ == "__main__":

@@ -113,8 +113,7 @@ def main():
     if ctx.rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
         json.dump(rows, open(f"gpurun_out/pushpull_sweep_n{N}.json", "w"), indent=1)
-    ctx.control_barrier()
-    os._exit(0)
+    ctx.shutdown()
 
 
 if __name__ == "__main__":

@@ -10,8 +10,35 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <climits>
+
 namespace {
 inline bool is_sep(char c) { return c == ' ' || c == '\t'; }
+
+// strtol / strtoll / strtof need a terminator and skip leading white space INCLUDING '\n'; a line is only a
+// (pointer, length) range of a buffer that may be an mmap or a C caller's array.  So every line is parsed from a
+// NUL-terminated copy: short lines on the stack, long ones in a reusable heap block.
+struct LineCopy {
+  char stack[4096];
+  char* heap = nullptr;
+  size_t heap_cap = 0;
+  ~LineCopy() { free(heap); }
+  const char* copy(const char* p, size_t n) {
+    char* dst = stack;
+    if (n + 1 > sizeof(stack)) {
+      if (n + 1 > heap_cap) {
+        free(heap);
+        heap_cap = (n + 1) * 2;
+        heap = static_cast<char*>(malloc(heap_cap));
+        if (!heap) { heap_cap = 0; return nullptr; }
+      }
+      dst = heap;
+    }
+    memcpy(dst, p, n);
+    dst[n] = 0;
+    return dst;
+  }
+};
 }
 
 // Pass 1: count rows and non-zeros so the caller can size the arrays.
@@ -41,15 +68,19 @@ extern "C" int64_t b200ps_libsvm_parse(const char* buf, uint64_t len, float* lab
   int64_t line_no = 0;
   const char* p = buf;
   const char* end = buf + len;
+  LineCopy lc;
   row_ptr[0] = 0;
   while (p < end) {
     const char* nl = static_cast<const char*>(memchr(p, '\n', end - p));
-    const char* le = nl ? nl : end;
+    const char* line_end = nl ? nl : end;
     ++line_no;
-    if (le - p >= 2) {
+    if (line_end - p >= 2) {
       if (r >= max_rows) return -line_no;
-      const char* q = p;
+      const char* q = lc.copy(p, static_cast<size_t>(line_end - p));   // NUL-terminated: no strto* call can leave it
+      if (!q) return -line_no;
+      const char* le = q + (line_end - p);
       char* e = nullptr;
+      if (is_sep(*q) || *q == '\r') return -line_no;      // the label starts the line
       const long lab = strtol(q, &e, 10);
       if (e == q) return -line_no;
       labels[r] = static_cast<float>(lab);
@@ -60,10 +91,11 @@ extern "C" int64_t b200ps_libsvm_parse(const char* buf, uint64_t len, float* lab
         const long long idx = strtoll(q, &e, 10);
         if (e == q || e >= le || *e != ':') return -line_no;
         q = e + 1;
+        if (q >= le || is_sep(*q) || *q == '\r') return -line_no;   // "idx:" with no value
         const float val = strtof(q, &e);
-        if (e == q) return -line_no;
+        if (e == q || e > le) return -line_no;
         q = e;
-        if (z >= max_nnz) return -line_no;
+        if (z >= max_nnz || z >= static_cast<uint64_t>(INT32_MAX)) return -line_no;   // row_ptr is int32
         fid[z] = idx;
         fval[z] = val;
         ++z;

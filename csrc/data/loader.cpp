@@ -108,9 +108,12 @@ inline bool parse_float(const char*& q, const char* le, float* out) {
   }
   const bool simple = (p > d0) && (nd + nf > 0) && (p >= le || *p == ' ' || *p == '\t' || *p == '\r');
   if (!simple) {
+    // strtof skips leading white space (new lines included) and needs a terminator: refuse an empty value
+    // here, and a result that ran past the line; every line handed to add_line ends in '\n' or NUL
+    if (q >= le || *q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') return false;
     char* e = nullptr;
     const float v = strtof(q, &e);
-    if (e == q) return false;
+    if (e == q || e > le) return false;
     *out = v;
     q = e;
     return true;
@@ -171,8 +174,9 @@ void publish(Loader& L, Builder& b, int epoch, int tid) {
 // the row would overflow the non-zero capacity of the buffer.
 bool add_line(Loader& L, Builder& b, const char* p, const char* le) {
   char* e = nullptr;
+  if (p >= le || *p == ' ' || *p == '\t' || *p == '\r') { L.malformed.fetch_add(1); return false; }
   const long lab = strtol(p, &e, 10);
-  if (e == p) { L.malformed.fetch_add(1); return false; }
+  if (e == p || e > le) { L.malformed.fetch_add(1); return false; }
   const char* q = e;
   int64_t z = b.nnz;
   while (q < le) {

@@ -191,8 +191,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                   __trap();
                 }
               }
-              // (the panel was written by bulk-async stores and is read by TMA: same proxy, so the
-              //  acquire on the flag is all the ordering the consumer side needs)
+              // the flag acquire is a generic-proxy read; the panel it guards was written by bulk-async stores
+              // and is read next by TMA (async proxy): order the two proxies before the first load of the panel
+              fence_proxy_async_all();
               seen[kb >> 5] |= 1u << (kb & 31);
             }
           }
@@ -564,10 +565,12 @@ static int launch_gemm(const b200ps_gemm_args& a, cudaStream_t stream) {
   p.vec_ok = vec ? 1 : 0;
 
   auto kern = gemm_tcgen05_kernel<kTf32, BLOCK_N, kStages>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {false};      // per template instantiation AND per device
+  int dev = 0;
+  B200PS_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
     B200PS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    attr_set = true;
+    attr_set[dev & 63] = true;
   }
   const int total_tiles = p.num_m_blocks * p.num_n_blocks * p.split_k;
   int ctas = a.max_ctas > 0 ? a.max_ctas : sm_count();

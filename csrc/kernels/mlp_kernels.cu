@@ -712,7 +712,7 @@ constexpr size_t kTailStaticFloats = 256 * 1024;
 constexpr size_t kTailStaticCounterWords = 64;
 // In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
 static __device__ __align__(256) float g_tail_static_scratch[kTailStaticFloats + kTailStaticCounterWords];
-static float* g_tail_static_addr[64] = {nullptr};   // per-device result of the symbol look-up
+static std::atomic<float*> g_tail_static_addr[64];   // per-device result of the symbol look-up (zero-initialised)
 
 extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const float* w2, const float* b2,
                                       const int32_t* labels, float* a2_out, float* dz2, float* dw2,
@@ -748,14 +748,15 @@ extern "C" int b200ps_mlp_tail_static(const float* z2, const float* b1, const fl
   int dev = 0;
   B200PS_CUDA_CHECK(cudaGetDevice(&dev));
   B200PS_REQUIRE(dev >= 0 && dev < 64, "mlp_tail_static: device index %d out of range", dev);
-  float* scratch = g_tail_static_addr[dev];
+  float* scratch = g_tail_static_addr[dev].load(std::memory_order_acquire);
   if (scratch == nullptr) {
     float* ptr = nullptr;
     cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_tail_static_scratch);
     if (e != cudaSuccess || ptr == nullptr)
       return set_error(B200PS_ERR_CUDA, "mlp_tail_static: cudaGetSymbolAddress failed on device %d: %s", dev,
                        cudaGetErrorString(e));
-    g_tail_static_addr[dev] = scratch = ptr;
+    scratch = ptr;
+    g_tail_static_addr[dev].store(ptr, std::memory_order_release);
   }
   unsigned int* counter = reinterpret_cast<unsigned int*>(scratch + kTailStaticFloats);
   cudaStream_t s = as_stream(stream);

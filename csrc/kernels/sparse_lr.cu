@@ -11,6 +11,7 @@
 //   loss_i = max(z,0) - z*y + log1p(exp(-|z|))      (tf.nn.sigmoid_cross_entropy_with_logits)
 //   dz_i = (p_i - y_i) * grad_scale
 #include "../common.h"
+#include "../workspace.h"
 #include "ptx.cuh"
 
 namespace b200ps {
@@ -30,6 +31,8 @@ struct SparseParams {
   unsigned long long* global_step;  // += 1 (by one thread) or null
   int B;
   int64_t rows_per_shard;
+  int64_t features;        // valid ids are [0, features); anything else is skipped and counted
+  unsigned long long* bad_ids;
   int shard_shift;         // >= 0 when rows_per_shard is a power of two
   int do_forward, do_update;
   const float* dz_in;      // [B] (update-only launches)
@@ -49,6 +52,18 @@ __device__ __forceinline__ float* w_addr(const SparseParams& p, int64_t id) {
   return p.w_shards[owner] + local;
 }
 
+// An id outside [0, features) must never reach w_addr(): its owner index would run off the pointer table
+// (embedding_lookup_sparse raises InvalidArgument there, lr2.py:390).  Such non-zeros contribute nothing and
+// are counted; the host raises when it next looks at the counter (b200ps_sparse_bad_ids).
+__device__ __forceinline__ bool id_ok(const SparseParams& p, int64_t id) {
+  return (unsigned long long)id < (unsigned long long)p.features;
+}
+__device__ __forceinline__ float w_load(const SparseParams& p, int64_t id, int& bad) {
+  if (id_ok(p, id)) return __ldcg(w_addr(p, id));
+  ++bad;
+  return 0.f;
+}
+
 __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseParams p) {
   __shared__ float s_loss[kSparseThreads / 32];
   __shared__ float s_dz[kSparseThreads / 32];
@@ -57,6 +72,7 @@ __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseP
   const int warps_total = gridDim.x * (kSparseThreads / 32);
   float loss_acc = 0.f, dz_acc = 0.f;
   float b = 0.f;
+  int bad = 0;
   if (p.do_forward) b = __ldcg(p.bias);  // one scalar from the owner (may be remote)
 
   for (int ex = blockIdx.x * (kSparseThreads / 32) + warp_in_cta; ex < p.B; ex += warps_total) {
@@ -67,12 +83,12 @@ __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseP
       // two loads in flight per lane: the gather is pure latency
       int j = beg + lane;
       for (; j + 32 < end; j += 64) {
-        const float w0 = __ldcg(w_addr(p, p.fid[j]));
-        const float w1 = __ldcg(w_addr(p, p.fid[j + 32]));
+        const float w0 = w_load(p, p.fid[j], bad);
+        const float w1 = w_load(p, p.fid[j + 32], bad);
         z = fmaf(w0, p.fval[j], z);
         z = fmaf(w1, p.fval[j + 32], z);
       }
-      if (j < end) z = fmaf(__ldcg(w_addr(p, p.fid[j])), p.fval[j], z);
+      if (j < end) z = fmaf(w_load(p, p.fid[j], bad), p.fval[j], z);
       z = warp_sum(z) + b;
       const float y = p.labels[ex];
       const float pr = 1.f / (1.f + __expf(-z));
@@ -87,10 +103,15 @@ __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseP
     }
     if (p.do_update) {
       const float s = -p.lr * dz;
-      for (int j = beg + lane; j < end; j += 32) red_add_f32_sys(w_addr(p, p.fid[j]), s * p.fval[j]);
+      for (int j = beg + lane; j < end; j += 32) {
+        const int64_t id = p.fid[j];
+        if (id_ok(p, id)) red_add_f32_sys(w_addr(p, id), s * p.fval[j]);
+        else if (!p.do_forward) ++bad;
+      }
       if (lane == 0) dz_acc += dz;
     }
   }
+  if (bad && p.bad_ids) atomicAdd(p.bad_ids, (unsigned long long)bad);
   if (lane == 0) { s_loss[warp_in_cta] = loss_acc; s_dz[warp_in_cta] = dz_acc; }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -142,16 +163,17 @@ using namespace b200ps;
 extern "C" int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, const float* fval,
                                 const float* labels, float* const* w_shards, float* bias, float* pred,
                                 float* dz_out, const float* dz_in, float* loss_sum,
-                                uint64_t* global_step, int32_t B, int64_t rows_per_shard,
+                                uint64_t* global_step, int32_t B, int64_t rows_per_shard, int64_t features,
                                 int32_t do_forward, int32_t do_update, float lr, float grad_scale,
                                 float loss_scale, b200ps_stream_t stream) {
-  B200PS_REQUIRE(B > 0 && rows_per_shard > 0, "sparse_lr: bad shape");
+  B200PS_REQUIRE(B > 0 && rows_per_shard > 0 && features > 0, "sparse_lr: bad shape");
   B200PS_REQUIRE(do_forward || (do_update && dz_in), "sparse_lr: update-only needs dz_in");
   SparseParams p;
   p.row_ptr = row_ptr; p.fid = fid; p.fval = fval; p.labels = labels; p.w_shards = w_shards;
   p.bias = bias; p.pred = pred; p.dz_out = dz_out; p.dz_in = dz_in; p.loss_sum = loss_sum;
   p.global_step = reinterpret_cast<unsigned long long*>(global_step);
-  p.B = B; p.rows_per_shard = rows_per_shard;
+  p.B = B; p.rows_per_shard = rows_per_shard; p.features = features;
+  p.bad_ids = bad_id_counter();
   p.shard_shift = -1;
   if ((rows_per_shard & (rows_per_shard - 1)) == 0) {
     int s = 0;
@@ -164,6 +186,17 @@ extern "C" int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, cons
   int ctas = std::min((B + warps_per_cta - 1) / warps_per_cta, sm_count() * 8);
   sparse_lr_kernel<<<ctas, kSparseThreads, 0, as_stream(stream)>>>(p);
   B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ps_sparse_bad_ids(uint64_t* count, int32_t reset) {
+  B200PS_REQUIRE(count, "sparse_bad_ids: null output");
+  unsigned long long* ctr = bad_id_counter();
+  B200PS_REQUIRE(ctr, "sparse_bad_ids: no workspace");
+  unsigned long long v = 0;
+  B200PS_CUDA_CHECK(cudaMemcpy(&v, ctr, sizeof(v), cudaMemcpyDeviceToHost));
+  if (reset && v) B200PS_CUDA_CHECK(cudaMemset(ctr, 0, sizeof(v)));
+  *count = v;
   return 0;
 }
 

@@ -29,6 +29,7 @@
 // Remote traffic per non-zero drops from 516 to 4 bytes, and the update pass of this kernel from a
 // serialised row-by-row scatter to one coalesced pass over the non-zeros.
 #include "../common.h"
+#include "../workspace.h"
 #include "ptx.cuh"
 
 namespace b200ps {
@@ -73,6 +74,8 @@ struct WdParams {
   int B;
   int do_forward, do_update;
   float lr, grad_scale, loss_scale;
+  int64_t features;        // valid ids are [0, features); others are skipped (weight 0) and counted
+  unsigned long long* bad_ids;
 };
 
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
@@ -96,6 +99,7 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
   }
   const float b = p.do_forward ? __ldcg(p.bias) : 0.f;
   float loss_acc = 0.f, dz_acc = 0.f;
+  int bad = 0;
 
   for (int ex = blockIdx.x * kWdWarps + warp_in_cta; ex < p.B; ex += warps_total) {
     const int beg = p.row_ptr[ex], end = p.row_ptr[ex + 1];
@@ -106,8 +110,9 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
     // ---- gather: lanes fetch 32 (id, value) pairs, then the warp walks them FL rows at a time
     for (int base = beg; base < end; base += 32) {
       const int j = base + lane;
-      const bool live = j < end;
-      const int64_t id = live ? p.fid[j] : 0;          // dead lanes name row 0 with weight 0
+      bool live = j < end;
+      int64_t id = live ? p.fid[j] : 0;                // dead lanes name row 0 with weight 0
+      if (live && (unsigned long long)id >= (unsigned long long)p.features) { live = false; id = 0; ++bad; }
       const float v = live ? p.fval[j] : 0.f;
       if (has_wide && live && p.do_forward) zw = fmaf(__ldcg(p.wide.row(id, 1)), v, zw);
       const unsigned long long rowp = reinterpret_cast<unsigned long long>(p.emb.row(id, D));
@@ -163,13 +168,17 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
         g2[c].w = fmaf(dz, h[c].w, g2[c].w);
       }
       if (p.pend.shards) {                            // deferred: one scalar per non-zero, lane-parallel
-        for (int j = beg + lane; j < end; j += 32) red_add_f32_sys(p.pend.row(p.fid[j], 1), s * p.fval[j]);
+        for (int j = beg + lane; j < end; j += 32) {
+          const int64_t id = p.fid[j];
+          if ((unsigned long long)id < (unsigned long long)p.features) red_add_f32_sys(p.pend.row(id, 1), s * p.fval[j]);
+        }
       } else {
         for (int base = beg; base < end; base += 32) {
           const int j = base + lane;
-          const bool live = j < end;
-          const int64_t id = live ? p.fid[j] : 0;
-          const float v = live ? p.fval[j] : 0.f;
+          bool live = j < end;
+          int64_t id = live ? p.fid[j] : 0;
+          if (live && (unsigned long long)id >= (unsigned long long)p.features) { live = false; id = 0; }
+          const float v = live ? p.fval[j] : 0.f;      // a refused id adds 0 to row 0
           if (has_wide && live) red_add_f32_sys(p.wide.row(id, 1), s * v);
           const unsigned long long rowp = reinterpret_cast<unsigned long long>(p.emb.row(id, D));
           const int n = min(32, end - base);
@@ -187,6 +196,7 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
     }
   }
 
+  if (bad && p.bad_ids) atomicAdd(p.bad_ids, (unsigned long long)bad);
   if (p.do_update) {
 #pragma unroll
     for (int c = 0; c < NCH; ++c)
@@ -297,8 +307,9 @@ extern "C" int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, cons
                                 const float* dz_in, float* loss_sum, uint64_t* global_step, int32_t B,
                                 int32_t do_forward, int32_t do_update, float lr, float grad_scale,
                                 float loss_scale, float* const* pend_shards, int64_t pend_rows_per_shard,
-                                float* const* pend2_shards, int64_t pend2_rows_per_shard, b200ps_stream_t stream) {
-  B200PS_REQUIRE(B > 0 && emb_shards && w2_shards && bias, "sparse_wd: bad arguments");
+                                float* const* pend2_shards, int64_t pend2_rows_per_shard, int64_t features,
+                                b200ps_stream_t stream) {
+  B200PS_REQUIRE(B > 0 && emb_shards && w2_shards && bias && features > 0, "sparse_wd: bad arguments");
   B200PS_REQUIRE((pend_shards == nullptr) == (pend2_shards == nullptr), "sparse_wd: pend and pend2 go together");
   B200PS_REQUIRE(!pend_shards || (pend_rows_per_shard == emb_rows_per_shard && pend2_rows_per_shard == w2_rows_per_shard),
                  "sparse_wd: pending tables must be sharded like the embedding / w2");
@@ -318,6 +329,7 @@ extern "C" int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, cons
   p.global_step = reinterpret_cast<unsigned long long*>(global_step);
   p.B = B; p.do_forward = do_forward; p.do_update = do_update;
   p.lr = lr; p.grad_scale = grad_scale; p.loss_scale = loss_scale;
+  p.features = features; p.bad_ids = bad_id_counter();
   const int ctas = std::min((B + kWdWarps - 1) / kWdWarps, sm_count() * 4);
   cudaStream_t s = as_stream(stream);
   if (dim == 128) sparse_wd_kernel<1><<<ctas, kWdThreads, 0, s>>>(p);

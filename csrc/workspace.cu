@@ -1,11 +1,15 @@
 #include "workspace.h"
 
 #include <mutex>
+#include <vector>
 
 namespace b200ps {
 
 static Workspace g_ws[64];
 static std::mutex g_ws_mu;
+// Blocks that were outgrown.  Kernel nodes of already captured CUDA graphs keep their addresses, so they stay
+// allocated until the process exits (a few MiB at most: the workspace only ever grows).
+static std::vector<void*> g_ws_retired;
 
 int get_workspace(size_t bytes, Workspace* out) {
   int dev = 0;
@@ -28,12 +32,18 @@ int get_workspace(size_t bytes, Workspace* out) {
                        "workspace: cudaMalloc(%zu) failed: %s (size the workspace with an eager call "
                        "before CUDA-graph capture)", want, cudaGetErrorString(e));
     }
-    if (w.data) cudaFree(w.data);
+    if (w.data) g_ws_retired.push_back(w.data);   // never freed: captured graphs may still point into it
     w.data = p;
     w.capacity = want;
   }
   *out = w;
   return 0;
+}
+
+unsigned long long* bad_id_counter() {
+  Workspace w;
+  if (get_workspace(0, &w) != 0) return nullptr;
+  return reinterpret_cast<unsigned long long*>(w.counters + 62);   // 8-byte aligned tail of the counter block
 }
 
 }  // namespace b200ps

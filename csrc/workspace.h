@@ -4,7 +4,8 @@
 // arrival counters).  The workspace is allocated with cudaMalloc on first use and grown on
 // demand, one per device; it is NOT keyed by stream, so launches that use it must not overlap
 // on the GPU (they do not in this framework: one training stream per process).  Growth is an
-// allocation and therefore must happen in an eager call before any CUDA-graph capture.
+// allocation and therefore must happen in an eager call before any CUDA-graph capture; a block that
+// was outgrown is kept allocated (never freed), so graphs captured against it stay valid.
 #pragma once
 #include "common.h"
 
@@ -18,5 +19,8 @@ struct Workspace {
 
 // Returns the current device's workspace with at least `bytes` of scratch.
 int get_workspace(size_t bytes, Workspace* out);
+
+// Device counter of feature ids that the sparse kernels refused (id < 0 or id >= features); counters[62..63].
+unsigned long long* bad_id_counter();
 
 }  // namespace b200ps

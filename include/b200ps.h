@@ -235,13 +235,17 @@ int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* 
  * at w_shards[f / rows_per_shard][f % rows_per_shard].  do_forward computes z, p, loss, dz;
  * do_update scatters -lr*dz*fval with red.global.add (and -lr*sum(dz) into *bias, and
  * *global_step += 1).  Both set = one fused Hogwild step.  Update-only launches read dz_in.
+ * Ids outside [0, features) are refused inside the kernel (they contribute nothing and never
+ * touch memory) and counted per device; b200ps_sparse_bad_ids reads (and optionally clears) the
+ * count — the host-side analogue of embedding_lookup_sparse's InvalidArgument (it synchronises).
  * K10: streaming-AUC histograms (lr2.py:400): bucket = #thresholds strictly below pred.
  * ---------------------------------------------------------------------------------- */
 int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, const float* fval,
                      const float* labels, float* const* w_shards, float* bias, float* pred,
                      float* dz_out, const float* dz_in, float* loss_sum, uint64_t* global_step,
-                     int32_t B, int64_t rows_per_shard, int32_t do_forward, int32_t do_update,
-                     float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+                     int32_t B, int64_t rows_per_shard, int64_t features, int32_t do_forward,
+                     int32_t do_update, float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
+int b200ps_sparse_bad_ids(uint64_t* count, int32_t reset);
 /* K4w/K5w: the wide & deep extension sketched at lr2_debug.py:423-428 —
  *   z = sum_j W[fid_j]*val_j + (sum_j val_j*E[fid_j,:]) . w2 + b
  * over row-sharded tables W [F,1] (optional: wide_shards may be NULL), E [F,dim] (dim 128/256/512) and
@@ -255,7 +259,7 @@ int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, const float* fv
                      float* loss_sum, uint64_t* global_step, int32_t B, int32_t do_forward, int32_t do_update,
                      float lr, float grad_scale, float loss_scale, float* const* pend_shards,
                      int64_t pend_rows_per_shard, float* const* pend2_shards, int64_t pend2_rows_per_shard,
-                     b200ps_stream_t stream);
+                     int64_t features, b200ps_stream_t stream);
 /* Deferred mode (pend_shards != NULL above): the embedding update of a step is rank one, dE[fid,:] = c[fid]*w2,
  * so workers add only the scalar c into a pending table P (sharded like W: 4 bytes of remote atomic per
  * non-zero instead of 516) and the w2 gradient into P2; the OWNER of a shard folds them in with

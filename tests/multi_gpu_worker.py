@@ -124,7 +124,8 @@ def main():
         json.dump(res, open(os.path.join(out_dir, "result.json"), "w"))
     print("rank", rank, json.dumps(res), flush=True)
     ctx.control_barrier()
-    os._exit(0)
+    del tr, tr_sep, tr_chain, tr2, tw, ts, st
+    ctx.shutdown()
 
 
 if __name__ == "__main__":

@@ -497,3 +497,30 @@ def test_barrier_virtual_ranks(native_lib):
         ops.barrier(t, world=world, rank_base=0, local_ranks=world)
     torch.cuda.synchronize()
     assert all(p[97].item() == 3 for p in pads)
+
+
+def test_sparse_kernels_refuse_out_of_range_ids(native_lib):
+    """Ids outside [0, features) never touch memory: they contribute nothing, are counted on the device and
+    surface as a ValueError at the next check (embedding_lookup_sparse's InvalidArgument, lr2.py:390)."""
+    from b200ps import ops
+    F, B = 1000, 4                      # 2 shards x 512 rows: ids 1000..1023 fall into shard padding
+    rows = 512
+    shards = [torch.ones(rows, device=DEV) for _ in range(2)]
+    table = ops.device_ptr_table([s.data_ptr() for s in shards], DEV)
+    bias = torch.zeros(1, device=DEV)
+    rp = torch.tensor([0, 2, 4, 6, 8], device=DEV, dtype=torch.int32)
+    fid = torch.tensor([1, 2, 999, 1000, 5, -7, 6, 1 << 40], device=DEV, dtype=torch.int64)
+    fv = torch.ones(8, device=DEV)
+    y = torch.zeros(B, device=DEV)
+    pred = torch.empty(B, device=DEV); loss = torch.zeros(1, device=DEV)
+    ops.sparse_bad_ids(reset=True)
+    ops.sparse_lr(rp, fid, fv, y, table, bias, rows_per_shard=rows, features=F, pred=pred, loss_sum=loss,
+                  forward=True, update=True, lr=1.0)
+    torch.cuda.synchronize()
+    z = torch.tensor([2.0, 1.0, 1.0, 1.0], device=DEV)      # the refused non-zeros contribute nothing
+    assert torch.allclose(pred, torch.sigmoid(z), atol=1e-6)
+    assert torch.cat(shards)[1000:].eq(1.0).all()            # padding rows untouched
+    assert ops.sparse_bad_ids(reset=False) == 3
+    with pytest.raises(ValueError):
+        ops.check_sparse_ids()
+    ops.check_sparse_ids()                                   # counter was cleared

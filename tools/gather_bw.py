@@ -32,4 +32,4 @@ for G in (4, 8, 12, 16, 24, 32, 48):
     if r == 0:
         print(json.dumps({"gather_ctas": G, "us": round(us, 1), "remote_MB": round(remote / 1e6, 1), "GBs": round(remote / us / 1e3, 1)}), flush=True)
     ctx.control_barrier()
-os._exit(0)
+ctx.shutdown()
