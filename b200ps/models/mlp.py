@@ -139,6 +139,29 @@ class SigmoidMLP:
                            cursor_wrap=cursor_wrap)
         return loss, correct
 
+    def supports_cluster(self, batch: int) -> bool:
+        """Shapes (and devices) the resident-cluster kernel (K14, csrc/kernels/mlp_cluster.cu) covers."""
+        return ops.mlp_cluster_supported(batch, self.in_dim, self.hidden, self.classes)
+
+    def cluster_train_steps(self, store, x: torch.Tensor, labels: torch.Tensor, lr: float, steps: int = 1,
+                            rank: Optional[int] = None, row_offset: Optional[torch.Tensor] = None,
+                            batch: Optional[int] = None, stats_out=None, stat_stride: int = 0,
+                            cursor: Optional[torch.Tensor] = None, cursor_step: Optional[int] = None,
+                            cursor_wrap: Optional[int] = None):
+        """``steps`` consecutive single-replica steps in ONE launch of K14 (one 16-CTA cluster, parameters resident
+        in shared memory, tensor-core products, DSMEM exchanges): what ``steps`` ``sess.run(train_op)`` calls of
+        example.py:168 do.  ``x``/``labels`` hold the batches back to back (or a whole dataset walked through
+        ``row_offset``); step ``s`` writes ``stats_out[0][s*stat_stride]`` / ``stats_out[1][s*stat_stride]``."""
+        B = x.shape[0] if (row_offset is None and steps == 1 and batch is None) else batch
+        bufs = self._buffers(B, x.device, 0 if rank is None else rank)
+        loss, correct = stats_out if stats_out is not None else (bufs["loss"], bufs["correct"])
+        ops.mlp_cluster_steps(x, labels, store.var(self.W1, rank), store.var(self.B1, rank), store.var(self.W2, rank),
+                              store.var(self.B2, rank), loss=loss, correct=correct, stat_stride=stat_stride,
+                              steps=steps, lr=lr, batch=B, cursor=row_offset,
+                              global_step=store.global_step_tensor(rank), cursor_rw=cursor,
+                              cursor_step=cursor_step, cursor_wrap=cursor_wrap)
+        return loss, correct
+
     def supports_fused_push(self, store) -> bool:
         """Can the synchronous push run inside K13?  One rank per process, all four variables alone in one
         fp32 group that has low-latency landing buffers."""

@@ -16,7 +16,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
                      GemmArgs, check, ptr, stream_ptr)
 
 __all__ = [
-    "gemm", "mlp_tail", "mlp_fused_step", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
+    "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
     "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
@@ -171,6 +171,36 @@ def mlp_fused_step(x, labels, w1, b1, w2, b2, *, loss, correct=None, grads=None,
         ptr(x), ptr(labels), ptr(cursor), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(g[0]), ptr(g[1]), ptr(g[2]),
         ptr(g[3]), ptr(loss), ptr(correct), ptr(global_step), ptr(cursor_rw), cursor_step, cursor_wrap, B, D, H, Cn,
         mode, lr, gs, ls, ctypes.addressof(push) if push is not None else None, stream_ptr(stream)), "mlp_fused_step")
+
+
+def mlp_cluster_supported(batch: int, in_dim: int, hidden: int, classes: int) -> bool:
+    """Does the resident-cluster step kernel (K14, csrc/kernels/mlp_cluster.cu) cover this shape on this device?"""
+    ok = C.c_int32(0)
+    check(native.load().b200ps_mlp_cluster_supported(batch, in_dim, hidden, classes, C.byref(ok)), "mlp_cluster_supported")
+    return bool(ok.value)
+
+
+def mlp_cluster_steps(x, labels, w1, b1, w2, b2, *, loss, correct=None, stat_stride=0, steps=1, lr, batch=None,
+                      cursor=None, global_step=None, cursor_rw=None, cursor_step=None, cursor_wrap=None,
+                      grad_scale=None, loss_scale=None, plain_tf32=False, stream=None):
+    """``steps`` consecutive single-replica training steps of the narrow MLP in ONE launch of one 16-CTA cluster
+    (K14): step s reads rows ``[(cursor + s*cursor_step) % cursor_wrap, +batch)`` of ``x`` / ``labels`` and writes
+    its loss / correct count to ``loss[s*stat_stride]`` / ``correct[s*stat_stride]``; parameters are updated in
+    place (SGD), ``global_step += steps``, ``cursor_rw`` receives the advanced cursor."""
+    _cuda(x, labels, w1, b1, w2, b2)
+    B = x.shape[0] if batch is None else batch
+    D, H = w1.shape
+    Cn = w2.shape[1]
+    if labels.dtype != torch.int32:
+        raise TypeError("mlp_cluster_steps: labels must be int32 class ids")
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    cstep = B if cursor_step is None else cursor_step
+    cwrap = max(x.shape[0], steps * cstep) if cursor_wrap is None else cursor_wrap
+    check(native.load().b200ps_mlp_cluster_steps(
+        ptr(x), ptr(labels), ptr(cursor), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(loss), ptr(correct), stat_stride,
+        ptr(global_step), ptr(cursor_rw), cstep, cwrap, B, D, H, Cn, steps, lr, gs, ls, int(plain_tf32),
+        stream_ptr(stream)), "mlp_cluster_steps")
 
 
 def softmax_ce(logits, labels, *, dlogits=None, loss_sum=None, correct=None, grad_scale=None,

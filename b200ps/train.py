@@ -142,6 +142,12 @@ class MLPTrainer(_TrainerBase):
             fused_step = os.environ.get("B200PS_FUSED_STEP", "1") != "0"
         self.fused = bool(fused_step) and self.device.type == "cuda" and self.model.supports_fused(batch_size)
         self.fused_apply = self.fused and mode == "sync" and ctx.world == 1 and (replicas_to_aggregate in (None, 1))
+        # K14: the single-replica step on one resident thread-block cluster (tensor cores, DSMEM bulk copies); many
+        # steps per launch over a resident dataset or a host chunk.  Opt-in (B200PS_CLUSTER_STEP=1): measured at
+        # 21 us/step against 13.4 us for K13 — 16 SMs x 8 warps cannot hide the latency that 98 CTAs hide
+        # (profiles/EXPERIMENTS.md, profiles/ncu_cluster.txt).
+        self.cluster = (self.fused_apply and os.environ.get("B200PS_CLUSTER_STEP", "0") == "1"
+                        and self.model.supports_cluster(batch_size))
         self._want_fused_push = (self.fused and mode == "sync" and ctx.world > 1 and
                                  replicas_to_aggregate in (None, ctx.world) and
                                  os.environ.get("B200PS_FUSED_PUSH", "1") != "0")
@@ -166,6 +172,13 @@ class MLPTrainer(_TrainerBase):
     def _one_step(self, r, x, labels, row_offset=None, stats_out=None, **cursor_kw):
         """One replica step on rank ``r``'s batch: returns (loss, correct) device/host words."""
         st = self.store
+        if self.cluster:
+            with nvtx_range("cluster_step"):
+                return self.model.cluster_train_steps(st, x, labels, self.lr, steps=1, rank=r, row_offset=row_offset,
+                                                      batch=self.batch_size, stats_out=stats_out,
+                                                      cursor=cursor_kw.get("cursor"),
+                                                      cursor_step=cursor_kw.get("cursor_step") or self.batch_size,
+                                                      cursor_wrap=cursor_kw.get("cursor_wrap") or max(x.shape[0], 1))
         if self.fused_apply:
             ck = dict(cursor=cursor_kw.get("cursor"), cursor_step=cursor_kw.get("cursor_step", 0),
                       cursor_wrap=cursor_kw.get("cursor_wrap", 1))
@@ -235,8 +248,19 @@ class MLPTrainer(_TrainerBase):
                                                             cursor_wrap=n)
 
     def _body_resident_multi(self):
+        if self.cluster:
+            self._resident_launch(self._spg)
+            return
         for _ in range(self._spg):
             self._body_resident()
+
+    def _resident_launch(self, steps: int) -> None:
+        """K14: ``steps`` steps over the attached dataset in one launch (the cluster stays resident)."""
+        data, labels, n = self._ds
+        r = self.local_ranks[0]
+        self._losses[r], self._corrects[r] = self.model.cluster_train_steps(
+            self.store, data, labels, self.lr, steps=steps, rank=r, row_offset=self._cursor, batch=self.batch_size,
+            cursor=self._cursor, cursor_step=self.batch_size, cursor_wrap=n)
 
     def step_resident(self) -> None:
         """One step on the next batch of the attached dataset."""
@@ -246,6 +270,10 @@ class MLPTrainer(_TrainerBase):
     def run_resident(self, steps: int) -> None:
         """``steps`` consecutive steps over the attached dataset (multi-step graph replays + remainder)."""
         n = steps
+        if self.cluster and steps > 0:
+            self._resident_launch(steps)         # one launch, however many steps
+            self.local_step += steps
+            return
         while n >= self._spg and self._spg > 1:
             self._step_res_multi()
             n -= self._spg
@@ -307,6 +335,11 @@ class MLPTrainer(_TrainerBase):
             correct_words = words.view(torch.int32)
 
             def body():
+                if trainer.cluster:              # K steps of the chunk in ONE launch, one (loss, correct) pair per step
+                    trainer.model.cluster_train_steps(trainer.store, x, y, trainer.lr, steps=K, rank=r, batch=B,
+                                                      stats_out=(words[0, 0:1], correct_words[0, 1:2]),
+                                                      stat_stride=2, cursor_step=B, cursor_wrap=K * B)
+                    return
                 for i in range(K):
                     trainer._prepare()
                     trainer._one_step(r, x[i * B:(i + 1) * B], y[i * B:(i + 1) * B],

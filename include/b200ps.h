@@ -229,6 +229,22 @@ int b200ps_mlp_fused_step(const float* x, const int32_t* labels, const int32_t* 
                           float lr, float grad_scale, float loss_scale, const b200ps_fused_push* push,
                           b200ps_stream_t stream);
 
+/* K14: the same narrow-MLP step (example.py:95-118, single replica: SGD applied in place) as a RESIDENT
+ * thread-block cluster: one launch of 16 CTAs runs `steps` consecutive steps; W1 / W2 / b1 / b2 stay in shared
+ * memory between steps (written back on the last one), the products run on the tensor cores (mma.sync tf32 with
+ * the 3xTF32 split = fp32-grade accuracy; flags bit 0 selects plain tf32) and all cross-CTA exchange is
+ * distributed shared memory + barrier.cluster.  Step s reads rows [(cursor + s*cursor_step) % cursor_wrap, +B)
+ * of x / labels (cursor = *cursor, or 0 when null) and writes loss[s*stat_stride], correct[s*stat_stride];
+ * *global_step += steps; *cursor_rw = advanced cursor.  Uses no scratch memory.  b200ps_mlp_cluster_supported
+ * reports whether shape and device (a schedulable 16-CTA cluster with ~200 KB shared memory per CTA) qualify. */
+int b200ps_mlp_cluster_supported(int32_t B, int32_t D, int32_t H, int32_t C, int32_t* ok);
+int b200ps_mlp_cluster_steps(const float* x, const int32_t* labels, const int32_t* cursor, float* w1, float* b1,
+                             float* w2, float* b2, float* loss, int32_t* correct, int32_t stat_stride,
+                             uint64_t* global_step, int32_t* cursor_rw, int32_t cursor_step, int32_t cursor_wrap,
+                             int32_t B, int32_t D, int32_t H, int32_t C, int32_t steps, float lr, float grad_scale,
+                             float loss_scale, int32_t flags, b200ps_stream_t stream);
+int b200ps_mlp_cluster_set_timing(void* buf);
+
 /* ------------------------------------------------------------------------------------
  * K4/K5: sparse logistic regression over a row-sharded [F,1] weight (lr2.py:390-396).
  * w_shards: device array of `world` shard base pointers (peer-mapped); feature id f lives

@@ -524,3 +524,63 @@ def test_sparse_kernels_refuse_out_of_range_ids(native_lib):
     with pytest.raises(ValueError):
         ops.check_sparse_ids()
     ops.check_sparse_ids()                                   # counter was cleared
+
+
+@pytest.mark.parametrize("B,D,H,Cn", [(100, 784, 100, 10), (37, 48, 20, 3), (128, 64, 128, 16), (8, 32, 4, 2),
+                                      (100, 1024, 128, 16)])
+def test_mlp_cluster_steps_match_float64_reference(native_lib, B, D, H, Cn):
+    """K14 (resident 16-CTA cluster, tensor-core products with the 3xTF32 split, DSMEM exchanges): three steps
+    in ONE launch over a resident dataset == three float64 SGD steps; one launch of 3 == three launches of 1
+    bit for bit; plain-tf32 mode stays within tf32 rounding."""
+    from b200ps import ops
+    if not ops.mlp_cluster_supported(B, D, H, Cn):
+        pytest.skip("16-CTA clusters with ~200 KB shared memory are not schedulable on this device")
+    g = torch.Generator(device=DEV).manual_seed(4)
+    rows = 4 * B
+    x = torch.rand(rows, D, device=DEV, generator=g)
+    labels = torch.randint(0, Cn, (rows,), device=DEV, generator=g, dtype=torch.int32)
+    init = [torch.randn(D, H, device=DEV, generator=g) * 0.2, torch.randn(H, device=DEV, generator=g) * 0.1,
+            torch.randn(H, Cn, device=DEV, generator=g) * 0.5, torch.randn(Cn, device=DEV, generator=g) * 0.1]
+    lr, steps, start = 0.1, 3, 2 * B
+
+    # float64 oracle: rows [2B,3B), [3B,4B), then wrap to [0,B)
+    W1, B1, W2, B2 = (t.double().clone() for t in init)
+    ref_loss, ref_corr = [], []
+    for s in range(steps):
+        r0 = (start + s * B) % rows
+        xb, yb = x[r0:r0 + B].double(), labels[r0:r0 + B].long()
+        ps = [t.clone().requires_grad_(True) for t in (W1, B1, W2, B2)]
+        logits = torch.sigmoid(xb @ ps[0] + ps[1]) @ ps[2] + ps[3]
+        loss = torch.nn.functional.cross_entropy(logits, yb)
+        loss.backward()
+        ref_loss.append(loss.item()); ref_corr.append(int((logits.argmax(1) == yb).sum()))
+        W1, B1, W2, B2 = (t - lr * q.grad for t, q in zip((W1, B1, W2, B2), ps))
+
+    def run(nlaunch, plain=False):
+        w = [t.clone() for t in init]
+        cursor = torch.tensor([start], device=DEV, dtype=torch.int32)
+        gstep = torch.zeros(1, device=DEV, dtype=torch.int64)
+        loss = torch.zeros(steps, 2, device=DEV); corr = torch.zeros(steps, 2, device=DEV, dtype=torch.int32)
+        per = steps // nlaunch
+        for l in range(nlaunch):
+            ops.mlp_cluster_steps(x, labels, *w, loss=loss[l * per:, 0], correct=corr[l * per:, 1], stat_stride=2,
+                                  steps=per, lr=lr, batch=B, cursor=cursor, global_step=gstep, cursor_rw=cursor,
+                                  cursor_step=B, cursor_wrap=rows, plain_tf32=plain)
+        torch.cuda.synchronize()
+        return w, loss[:, 0].tolist(), corr[:, 1].tolist(), cursor.item(), gstep.item()
+
+    w, losses, corrs, cur, gs = run(1)
+    assert cur == (start + steps * B) % rows and gs == steps
+    for got, want in zip(losses, ref_loss):
+        assert abs(got - want) < 2e-5 * max(1.0, abs(want)), (losses, ref_loss)
+    assert corrs == ref_corr
+    for t, want in zip(w, (W1, B1, W2, B2)):
+        assert torch.allclose(t.double(), want, atol=5e-6, rtol=2e-5), (t.double() - want).abs().max()
+    w3, losses3, corrs3, _, _ = run(3)                       # three launches of one step: same bytes
+    for a, b in zip(w, w3):
+        assert torch.equal(a, b)
+    assert losses == losses3 and corrs == corrs3
+    wp, lossp, _, _, _ = run(1, plain=True)                  # one tf32 product per tile
+    for t, want in zip(wp, (W1, B1, W2, B2)):
+        assert torch.allclose(t.double(), want, atol=5e-3, rtol=5e-3)
+    assert abs(lossp[0] - ref_loss[0]) < 5e-3 * max(1.0, abs(ref_loss[0]))

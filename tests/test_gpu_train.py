@@ -342,3 +342,35 @@ def test_native_loader_feeds_sparse_trainer(native_lib, tmp_path):
     wa, wb = a.store.state_dict()[a.model.W], b.store.state_dict()[b.model.W]
     assert torch.allclose(wa, wb, rtol=1e-4, atol=1e-5)
     loader.close()
+
+
+def test_cluster_step_trainer_matches_default_path(native_lib, monkeypatch):
+    """The opt-in resident-cluster step (K14, B200PS_CLUSTER_STEP=1) drives the same trainer APIs — single steps,
+    multi-step resident launches, chunked host feeding — and lands within fp32 rounding of the default K13 path."""
+    from b200ps import ops
+    from b200ps.parallel.context import init_from_env
+    from b200ps.train import MLPTrainer
+    if not ops.mlp_cluster_supported(100, 784, 100, 10):
+        pytest.skip("16-CTA clusters are not schedulable on this device")
+    xs, ys = _mnist_batches(7)
+    a = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    monkeypatch.setenv("B200PS_CLUSTER_STEP", "1")
+    b = MLPTrainer(init_from_env(virtual_world=1), batch_size=100, lr=0.01, mode="sync", use_graph=True)
+    assert b.cluster and not a.cluster
+    for tr in (a, b):
+        tr.attach_dataset(xs.reshape(-1, 784), ys.reshape(-1))
+        for i in range(3):
+            tr.step(xs[i], ys[i])
+        tr.run_resident(11)
+        tr.step_resident()
+    torch.cuda.synchronize()
+    assert a.global_step == b.global_step == 15 and a._cursor.item() == b._cursor.item()
+    sa, sb = a.store.state_dict(), b.store.state_dict()
+    for name in a.model.names():
+        assert torch.allclose(sa[name], sb[name], atol=2e-5, rtol=1e-4), name
+    assert abs(a.read_loss() - b.read_loss()) < 1e-4
+    hx, hy = xs.reshape(-1, 784)[:400].cpu().pin_memory(), ys.reshape(-1)[:400].cpu().pin_memory()
+    la, lb = [], []
+    a.fit_from_host(hx, hy, steps_per_call=4, on_loss=lambda i, v: la.append(v))
+    b.fit_from_host(hx, hy, steps_per_call=4, on_loss=lambda i, v: lb.append(v))
+    assert len(la) == len(lb) == 4 and max(abs(p - q) for p, q in zip(la, lb)) < 1e-4
