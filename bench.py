@@ -502,6 +502,11 @@ def main():
     if not torch.cuda.is_available():
         print(json.dumps({"error": "no CUDA device: bench.py measures the GPU path only"}))
         return 1
+    # stdout carries exactly ONE line (the JSON).  Native libraries write there too (NCCL prints its version banner
+    # when the baseline arm creates its communicator), so fd 1 points at stderr until the line is ready.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import build as _build
     if int(os.environ.get("LOCAL_RANK", "0")) == 0:
         _build.build(quiet=True)
@@ -562,8 +567,8 @@ def main():
                                                                      "gpu_launches", "trials", "dtype")},
             "extra": extra,
         }
-        print(json.dumps(line))
         sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     ctx.shutdown()
     return 0
 
