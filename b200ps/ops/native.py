@@ -10,8 +10,12 @@ import ctypes as C
 import os
 import threading
 
+# B200PS_CHECKED=1 selects the build with device-side protocol assertions (build.py --checked)
+_CHECKED = os.environ.get("B200PS_CHECKED", "0") == "1"
 _LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib",
-                         "libb200ps.so")
+                         "libb200ps_checked.so" if _CHECKED else "libb200ps.so")
+if _CHECKED:
+    os.environ["B200PS_FASTFEED"] = "0"      # the CPython fast path is linked against the release library
 _lib = None
 _lock = threading.Lock()
 

@@ -22,6 +22,10 @@ import torch
 from .symm import SymmPool
 
 
+class PeerLost(RuntimeError):
+    """A rank of the job stopped answering on the control plane (see ``Context.check_peers``)."""
+
+
 @dataclass
 class Context:
     rank: int
@@ -56,6 +60,44 @@ class Context:
         t = torch.tensor([float(value)], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return float(t.item())
+
+    def check_peers(self, timeout_s: float = 5.0) -> None:
+        """Liveness check over the control plane: returns once every rank has answered, raises ``PeerLost`` when
+        one has not within ``timeout_s``.  On the NVLink backend every worker is also a parameter-server shard, so
+        a dead worker takes its shard with it (the dead ps task of the reference, lr2.py:223-229): a synchronous
+        step launched after that would spin on the dead rank's packets until its bounded in-kernel wait traps.
+        Calling this between steps (apps: ``--heartbeat_steps``) turns the loss of a peer into an exception on
+        the host BEFORE the next launch; recovery is the reference's — restart, the chief restores the newest
+        checkpoint."""
+        if self.group is None:
+            return
+        import torch.distributed as dist
+        try:
+            dist.monitored_barrier(group=self.group, timeout=datetime.timedelta(seconds=timeout_s),
+                                   wait_all_ranks=False)
+        except Exception as e:           # gloo reports the silent rank(s) in the message
+            raise PeerLost(f"rank {self.rank}: a peer stopped answering within {timeout_s:.1f} s: "
+                           f"{str(e).splitlines()[0][:200]}") from None
+
+    def abandon(self) -> None:
+        """Leave a job that lost a rank: no barriers (they cannot complete any more) — unmap what we mapped, free
+        what we own, drop the process group.  The interpreter then exits normally."""
+        if self.device.type == "cuda":
+            try:
+                torch.cuda.synchronize(self.device)
+            except Exception:
+                pass
+        group, self.pool.group, self.group = self.group, None, None
+        try:
+            self.pool.close()
+        except Exception:
+            pass
+        if group is not None:
+            import torch.distributed as dist
+            try:
+                dist.destroy_process_group()
+            except Exception:
+                pass
 
     def close(self) -> None:
         """Release the symmetric memory: unmap the peers' buffers, control barrier, free our own."""

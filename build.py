@@ -67,24 +67,29 @@ def headers_digest():
     return h.hexdigest()
 
 
-def compile_one(src, obj, verbose):
-    cmd = [NVCC, *ARCH, *COMMON, "-c", src, "-o", obj]
+def compile_one(src, obj, verbose, extra=()):
+    cmd = [NVCC, *ARCH, *COMMON, *extra, "-c", src, "-o", obj]
     if src.endswith(".cpp"):
-        cmd = [NVCC, *ARCH, *COMMON, "-x", "cu", "-c", src, "-o", obj]
+        cmd = [NVCC, *ARCH, *COMMON, *extra, "-x", "cu", "-c", src, "-o", obj]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
     return src, r.returncode, r.stdout + r.stderr
 
 
-def build(force=False, verbose=False, quiet=False):
+def build(force=False, verbose=False, quiet=False, checked=False):
+    """``checked=True`` builds the same sources with -DB200PS_CHECKED (device-side protocol assertions) into
+    ``libb200ps_checked.so`` (loaded instead of the release library when B200PS_CHECKED=1)."""
+    obj_dir = OBJ_DIR + ("_checked" if checked else "")
+    LIB = os.path.join(OUT_DIR, "libb200ps_checked.so" if checked else "libb200ps.so")
+    extra = ("-DB200PS_CHECKED",) if checked else ()
     os.makedirs(OUT_DIR, exist_ok=True)
-    os.makedirs(OBJ_DIR, exist_ok=True)
+    os.makedirs(obj_dir, exist_ok=True)
     hdig = headers_digest()
     jobs, objs = [], []
     for src in sources():
         rel = os.path.relpath(src, CSRC).replace(os.sep, "_")
-        obj = os.path.join(OBJ_DIR, rel + ".o")
+        obj = os.path.join(obj_dir, rel + ".o")
         stamp = obj + ".stamp"
         key = hashlib.sha1(open(src, "rb").read() + hdig.encode()).hexdigest()
         objs.append(obj)
@@ -94,7 +99,7 @@ def build(force=False, verbose=False, quiet=False):
             jobs.append((src, obj, stamp, key))
     failed = False
     with cf.ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
-        futs = {ex.submit(compile_one, s, o, verbose): (s, o, st, k) for s, o, st, k in jobs}
+        futs = {ex.submit(compile_one, s, o, verbose, extra): (s, o, st, k) for s, o, st, k in jobs}
         for fut in cf.as_completed(futs):
             src, rc, log = fut.result()
             s, o, st, k = futs[fut]
@@ -117,7 +122,8 @@ def build(force=False, verbose=False, quiet=False):
             raise RuntimeError("link failed")
         if not quiet:
             print(f"[build] linked {os.path.relpath(LIB, ROOT)}")
-    build_python_ext(quiet)
+    if not checked:
+        build_python_ext(quiet)
     return LIB
 
 
@@ -125,5 +131,6 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--checked", action="store_true", help="build libb200ps_checked.so (-DB200PS_CHECKED)")
     a = ap.parse_args()
-    build(force=a.force, verbose=a.verbose)
+    build(force=a.force, verbose=a.verbose, checked=a.checked)

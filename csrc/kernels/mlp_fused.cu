@@ -86,7 +86,18 @@ struct FusedParams {
   uint2* const* ll_grads; uint2* const* ll_params; unsigned long long* const* global_steps;
   long long max_shard, off_w1, off_b1, off_w2, off_b2;
   int world, rank;
+  int skew_ns;               // debug: random per-CTA delay (< skew_ns) at entry and before the push phases
 };
+
+__device__ __forceinline__ void fs_skew(const FusedParams& p, uint32_t salt) {
+  if (p.skew_ns > 0) {       // stress knob (b200ps_debug_set_skew_ns): shakes the arrival order of CTAs and ranks
+    if (threadIdx.x == 0) {
+      const uint32_t h = (salt * 2654435761u) ^ ((uint32_t)p.rank * 40503u) ^ (blockIdx.x * 9973u) ^ (uint32_t)clock64();
+      __nanosleep(h % (uint32_t)p.skew_ns);
+    }
+    __syncthreads();
+  }
+}
 
 __device__ __forceinline__ float fs_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
 
@@ -142,7 +153,10 @@ __device__ __forceinline__ void fs_tile_fma(const float* __restrict__ xs, int xp
 // gradient element(s) of flat index i -> the owner's landing buffer as {value, epoch} packets
 __device__ __forceinline__ int fs_owner(const long long* s_bounds, long long i) {
   int o = 0;
-  while (i >= s_bounds[o + 1]) ++o;
+  while (i >= s_bounds[o + 1]) {
+    ++o;
+    B200PS_DEV_CHECK(o < kMaxWorld, "flat index %lld has no owner\n", i);
+  }
   return o;
 }
 __device__ __forceinline__ void fs_send1(const FusedParams& p, const long long* s_bounds, long long i, float v, uint32_t epoch) {
@@ -198,6 +212,7 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
     if (p.apply == 2) epoch = __ldcg(p.pads[p.rank] + kSlotEpoch) + 1;
     __syncthreads();
   }
+  fs_skew(p, epoch);
   if (cta == 0 && tid == 0) p.bar[1] = 0;         // nobody can reach barrier 2 before we reach barrier 1
 
   // ---------------------------------------------------------------- operand fetch: three cp.async groups
@@ -626,6 +641,7 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
   if (p.apply != 2) return;
 
   // ---------------------------------------------------------------- phases D / E: the in-kernel push
+  fs_skew(p, epoch + 77u);
   {
     const int world = p.world, rank = p.rank;
     {   // alignment gaps of the flat layout belong to somebody's range too: they travel as zeros
@@ -699,6 +715,13 @@ __global__ void __launch_bounds__(kFsThreads) mlp_fused_step_kernel(const FusedP
 using namespace b200ps;
 
 static long long* g_fs_timing = nullptr;
+static int g_fs_skew_ns = 0;
+// Debug hook: every following fused-step launch delays each CTA by a pseudo-random time below `ns` nanoseconds at
+// entry and before its push phases (0 switches it off).  Used by the multi-GPU skew stress test.
+extern "C" int b200ps_debug_set_skew_ns(int32_t ns) {
+  g_fs_skew_ns = ns > 0 ? ns : 0;
+  return 0;
+}
 // Debug hook: SM-clock stamps of CTA 0 at the 9 phase boundaries of every following fused-step launch
 // are written to `buf` (device memory, 24 x int64); null switches it off.
 extern "C" int b200ps_mlp_fused_step_set_timing(void* buf) {
@@ -733,6 +756,7 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   p.global_step = reinterpret_cast<unsigned long long*>(global_step);
   p.cursor_rw = cursor_rw; p.cursor_step = cursor_step; p.cursor_wrap = cursor_wrap > 0 ? cursor_wrap : 1;
   p.timing = g_fs_timing;
+  p.skew_ns = g_fs_skew_ns;
   p.pads = nullptr; p.masters = nullptr; p.bounds = nullptr; p.ll_grads = nullptr; p.ll_params = nullptr;
   p.global_steps = nullptr; p.max_shard = 0; p.off_w1 = p.off_b1 = p.off_w2 = p.off_b2 = 0; p.world = 1; p.rank = 0;
   if (apply >= 2) {

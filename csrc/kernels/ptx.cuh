@@ -39,6 +39,24 @@ __device__ __forceinline__ bool elect_one() {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Checked build (build.py --checked, -DB200PS_CHECKED -> libb200ps_checked.so, selected with B200PS_CHECKED=1):
+// protocol invariants that the release build takes for granted — epochs only move forward, a packet slot is
+// written once per epoch, owner indices stay inside the shard table — are verified on the device and trap with a
+// message.  compute-sanitizer's racecheck cannot see cross-GPU traffic; these checks plus the skew stress test
+// (tests/multi_gpu_stress_worker.py) are the race-detection story of the NVLink backend.
+#ifdef B200PS_CHECKED
+#define B200PS_DEV_CHECK(cond, ...)                                   \
+  do {                                                                \
+    if (!(cond)) {                                                    \
+      printf("b200ps CHECKED (block %d thread %d): ", blockIdx.x, threadIdx.x); \
+      printf(__VA_ARGS__);                                            \
+      __trap();                                                       \
+    }                                                                 \
+  } while (0)
+#else
+#define B200PS_DEV_CHECK(cond, ...) do { } while (0)
+#endif
+
 // Every in-kernel wait in this library is bounded: a protocol bug must become a trap
 // (which the host sees as an error) instead of a hung GPU.
 #ifndef B200PS_WAIT_TIMEOUT_NS

@@ -244,6 +244,8 @@ int b200ps_mlp_cluster_steps(const float* x, const int32_t* labels, const int32_
                              int32_t B, int32_t D, int32_t H, int32_t C, int32_t steps, float lr, float grad_scale,
                              float loss_scale, int32_t flags, b200ps_stream_t stream);
 int b200ps_mlp_cluster_set_timing(void* buf);
+/* Debug: random per-CTA delays (< ns nanoseconds) inside every following b200ps_mlp_fused_step launch; 0 = off. */
+int b200ps_debug_set_skew_ns(int32_t ns);
 
 /* ------------------------------------------------------------------------------------
  * K4/K5: sparse logistic regression over a row-sharded [F,1] weight (lr2.py:390-396).
