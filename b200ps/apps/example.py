@@ -122,6 +122,8 @@ def main(argv=None) -> int:
                     log.error("fault injection: worker exiting abruptly")
                     os._exit(17)
                 if gpu:
+                    if FLAGS.heartbeat_steps > 0 and local_step % FLAGS.heartbeat_steps == 0:
+                        ctx.check_peers(min(FLAGS.barrier_timeout_secs, 10.0))     # raises PeerLost (restart + restore)
                     trainer.step(batch_x, batch_y)
                     want_host = (local_step % FLAGS.summary_every == 0) or count + 1 == frequency or i + 1 == batch_count
                     if want_host:

@@ -147,6 +147,9 @@ class _GpuRunner:
         self.tr = trainer
 
     def train_step(self, samples):
+        hb = FLAGS.heartbeat_steps
+        if hb > 0 and self.tr.local_step % hb == 0:
+            self.tr.ctx.check_peers(min(FLAGS.barrier_timeout_secs, 10.0))      # raises PeerLost (restart + restore)
         self.tr.step(_to_device_batch(samples, self.tr.device))
         return None
 

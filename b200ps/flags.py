@@ -145,4 +145,6 @@ def define_role_flags(job_name_default: str = "worker"):
     DEFINE_integer("seed", 1, "graph-level random seed (example.py:82 uses 1)")
     DEFINE_integer("fault_inject_step", -1, "test hook: the worker named by --fault_rank exits at this step")
     DEFINE_integer("fault_rank", -1, "test hook: task_index of the worker to kill")
+    DEFINE_integer("heartbeat_steps", 0, "NVLink backend: check every N local steps that all ranks still answer "
+                   "(0 = off); a silent rank raises PeerLost on the survivors before the next launch")
     DEFINE_float("barrier_timeout_secs", 120.0, "give up waiting for peers after this many seconds")
