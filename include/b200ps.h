@@ -290,6 +290,33 @@ int b200ps_auc_hist(const float* pred, const float* labels, int32_t B, const flo
                     int32_t T, uint64_t* hist_pos, uint64_t* hist_neg, b200ps_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * JPEG decode for the image input pipeline (input_pipeline.py:68-78: read_file + decode_jpeg(channels=3)).
+ * Host: b200ps_jpeg_parse entropy-decodes a baseline JPEG into quantised 8x8 coefficient blocks (natural order,
+ * component after component) and fills the descriptor.  GPU: b200ps_jpeg_idct_color dequantises, runs the inverse
+ * DCT (one CTA of 64 threads per block) into component planes, then one thread per output pixel upsamples the
+ * chroma (libjpeg's "fancy" triangle filters for 2x1 / 2x2), converts YCbCr -> RGB and — when out_h x out_w
+ * differs from the image size — resizes bilinearly.  out is uint8 [out_h, out_w, 3] (grey images are replicated
+ * to three channels, as decode_jpeg(channels=3) does).  coef_dev / planes_dev: device buffers of
+ * desc->total_coefs int16 / bytes.
+ * ---------------------------------------------------------------------------------- */
+typedef struct b200ps_jpeg_comp {
+  int32_t h, v;                 /* sampling factors */
+  int32_t blocks_w, blocks_h;   /* blocks per row / column (padded to whole MCUs) */
+  int64_t coef_offset;          /* first coefficient of this component in the coefficient buffer */
+  int64_t plane_offset;         /* first sample of this component's plane (blocks_h*8 rows of blocks_w*8) */
+  uint16_t quant[64];           /* quantisation table, natural order */
+} b200ps_jpeg_comp;
+typedef struct b200ps_jpeg_desc {
+  int32_t width, height, ncomp, hmax, vmax, mcus_x, mcus_y, total_blocks;
+  int64_t total_coefs;
+  b200ps_jpeg_comp comp[3];
+} b200ps_jpeg_desc;
+int b200ps_jpeg_info(const uint8_t* data, uint64_t len, int32_t* width, int32_t* height, int32_t* ncomp);
+int b200ps_jpeg_parse(const uint8_t* data, uint64_t len, int16_t* coef, uint64_t coef_cap, b200ps_jpeg_desc* desc);
+int b200ps_jpeg_idct_color(const int16_t* coef_dev, const b200ps_jpeg_desc* desc, uint8_t* planes_dev,
+                           uint8_t* out_dev, int32_t out_h, int32_t out_w, b200ps_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * K1/K3/K12 + pull: parameter-server traffic as kernels over peer-mapped memory.
  * All pointer tables are DEVICE arrays with `world` entries holding addresses valid in the
  * calling process (local or IPC-mapped).  bounds[world+1] are the owner ranges of the flat

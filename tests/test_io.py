@@ -5,6 +5,7 @@ import struct
 
 import numpy as np
 import pytest
+import torch
 from hypothesis import given, settings, strategies as st
 
 from b200ps.io import crc32c, events, exporter, log, proto as pb, saver, tf_bundle
@@ -217,3 +218,54 @@ def test_native_events_writer_matches_python_twin(tmp_path, monkeypatch):
     assert len(a) == len(b) and a[first:] == b[first:]
     got = list(events.read_events(paths["1"]))
     assert got[0][3] == "brain.Event:2" and got[1][1] == 0 and got[2][1] == 3 and abs(got[2][2]["cost"] - 0.25) < 1e-7
+
+
+def _jpeg_cases():
+    import io
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    out = []
+    for (h, w), sub, q, restart in [((28, 28), 0, 90, 0), ((28, 28), 2, 75, 0), ((33, 47), 1, 85, 0), ((64, 48), 2, 95, 0),
+                                    ((17, 23), 0, 50, 0), ((120, 97), 2, 30, 0), ((28, 28), None, 90, 0)]:
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = np.stack([128 + 100 * np.sin(xx / 5.0 + yy / 7.0), 128 + 100 * np.cos(xx / 3.0), (xx * 255 / w + yy * 255 / h) / 2], 2)
+        img = np.clip(img + rng.normal(0, 8, img.shape), 0, 255).astype(np.uint8)
+        buf = io.BytesIO()
+        if sub is None:
+            Image.fromarray(img[:, :, 0]).save(buf, format="JPEG", quality=q)          # greyscale
+        else:
+            Image.fromarray(img).save(buf, format="JPEG", quality=q, subsampling=sub)
+        data = buf.getvalue()
+        ref = np.array(Image.open(io.BytesIO(data)).convert("RGB"))
+        out.append((data, ref))
+    return out
+
+
+def test_jpeg_decoder_host_path_matches_pil(native_lib):
+    """Native Huffman front end + the numpy restatement of the device stage (libjpeg's integer IDCT, fancy chroma
+    upsampling, fixed-point colour conversion) against PIL: within +-1 LSB everywhere (in fact equal), for
+    4:4:4 / 4:2:2 / 4:2:0 / greyscale files of odd sizes."""
+    from b200ps.io.jpeg import decode_jpeg, decode_jpeg_numpy, jpeg_info
+    for data, ref in _jpeg_cases():
+        assert jpeg_info(data)[:2] == ref.shape[:2]
+        got = decode_jpeg_numpy(data)
+        assert got.shape == ref.shape and np.abs(got.astype(int) - ref.astype(int)).max() <= 1
+        assert torch.equal(decode_jpeg(data, device="cpu"), torch.from_numpy(got))
+    with pytest.raises(Exception):
+        jpeg_info(b"not a jpeg at all")
+
+
+@pytest.mark.gpu
+def test_jpeg_decoder_gpu_matches_pil(native_lib):
+    """The CUDA stage (inverse DCT, chroma upsampling, YCbCr->RGB) against PIL, +-1 LSB (decode_jpeg(channels=3),
+    input_pipeline.py:70); the fused bilinear resize against torch's on the decoded image."""
+    from b200ps.io.jpeg import decode_jpeg
+    for data, ref in _jpeg_cases():
+        got = decode_jpeg(data, device="cuda")
+        assert got.dtype == torch.uint8 and tuple(got.shape) == ref.shape
+        assert (got.cpu().int() - torch.from_numpy(ref).int()).abs().max().item() <= 1
+    data, ref = _jpeg_cases()[3]
+    small = decode_jpeg(data, device="cuda", size=(28, 28))
+    want = torch.nn.functional.interpolate(torch.from_numpy(ref).permute(2, 0, 1)[None].float(), size=(28, 28),
+                                           mode="bilinear", align_corners=False)[0].permute(1, 2, 0)
+    assert tuple(small.shape) == (28, 28, 3) and (small.cpu().float() - want).abs().max().item() <= 1.0
