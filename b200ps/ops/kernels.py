@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -288,6 +288,17 @@ def cast_f32_bf16(src, dst, stream=None):
 def device_ptr_table(ptrs: Sequence[int], device) -> torch.Tensor:
     """int64 device tensor holding raw addresses (the pointer tables the comm kernels take)."""
     return torch.tensor([int(p) for p in ptrs], dtype=torch.int64, device=device)
+
+
+def store_nvls(pads, mc_grads: int, mc_work: int, work_local: int, master: int, lo: int, hi: int, *, dtype, world: int,
+               rank: int, lr: float, reduce: bool, broadcast: bool = True, global_step: Optional[int] = None, cursor=None,
+               cursor_step: int = 0, cursor_wrap: int = 1, stream=None) -> None:
+    """The ParameterStore's NVLS push (``reduce``) / collective pull through NVSwitch multicast: raw multicast and
+    unicast ADDRESSES of buffers from ``SymmPool.alloc(..., multicast=True)`` (csrc/kernels/ps_nvls.cu)."""
+    check(native.load().b200ps_store_nvls(ptr(pads), mc_grads or None, mc_work, work_local, master, lo, hi,
+                                          DT_F32 if dtype == torch.float32 else DT_BF16, world, rank, lr, int(reduce),
+                                          int(broadcast), global_step or None, ptr(cursor) or None, cursor_step, cursor_wrap,
+                                          stream_ptr(stream)), "store_nvls")
 
 
 def sparse_bad_ids(reset: bool = True) -> int:

@@ -48,6 +48,7 @@ class SymmBuffer:
     ptrs: List[int]                 # address of every rank's copy, valid in THIS process
     local: List[torch.Tensor]       # uint8 views of the copies this process owns (1 per local rank)
     local_ranks: List[int]
+    mc_ptr: int = 0                 # NVSwitch multicast address of the buffer (0: not bound to a multicast object)
 
     def view(self, rank: int, dtype: torch.dtype, offset_bytes: int = 0, numel: Optional[int] = None):
         """Typed tensor over the copy of local rank ``rank``."""
@@ -71,13 +72,54 @@ class SymmPool:
         self.virtual = virtual or world == 1
         self.local_ranks = list(range(world)) if self.virtual else [rank]
         self._buffers = []
+        import os
+        # NVLS: off with B200PS_NVLS=0; switched off for the rest of the run by the first allocation that fails
+        self.multicast_ok = os.environ.get("B200PS_NVLS", "1") != "0"
         self._opened: List[int] = []
         self._owned: List[int] = []
         if not self.virtual and group is None:
             raise ValueError("multi-process symmetric memory needs a control-plane process group")
 
-    def alloc(self, name: str, nbytes: int) -> SymmBuffer:
+    def _alloc_multicast(self, name: str, nbytes: int) -> Optional[SymmBuffer]:
+        """A symmetric buffer that is ALSO bound to an NVSwitch multicast object, so kernels can use
+        ``multimem.ld_reduce`` / ``multimem.st`` on it (csrc/kernels/ps_nvls.cu).  cudaMalloc + CUDA-IPC memory cannot be
+        bound, so these buffers come from torch's symmetric-memory allocator (cuMemCreate + cuMulticastBindMem under
+        the hood): one rendezvous over the control-plane group yields every rank's unicast address and the multicast
+        address.  Returns None when the platform has no multicast support (the caller falls back to the IPC pool).
+        All ranks take the same decision: the outcome is agreed on over the control plane."""
+        import torch.distributed as dist
+        ok, buf = 1, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            with torch.cuda.device(self.device):
+                t = symm_mem.empty(nbytes, dtype=torch.uint8, device=self.device)
+                hdl = symm_mem.rendezvous(t, self.group.group_name)
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            if not mc:
+                ok = 0
+            else:
+                t.zero_()
+                torch.cuda.synchronize(self.device)
+                buf = SymmBuffer(name, nbytes, [int(p) for p in hdl.buffer_ptrs], [t], [self.rank], mc_ptr=mc)
+                buf._handle = hdl                     # keeps the mapping alive with the buffer
+        except Exception as e:                        # no symmetric-memory support in this torch / on this box
+            ok = 0
+            self._mc_error = f"{type(e).__name__}: {e}"
+        flag = torch.tensor([ok], dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            self.multicast_ok = False
+            return None
+        self._buffers.append(buf)
+        dist.barrier(group=self.group)
+        return buf
+
+    def alloc(self, name: str, nbytes: int, multicast: bool = False) -> SymmBuffer:
         nbytes = (int(nbytes) + 255) // 256 * 256
+        if multicast and not self.virtual and self.multicast_ok:
+            buf = self._alloc_multicast(name, nbytes)
+            if buf is not None:
+                return buf
         if self.virtual:
             local = [torch.zeros(nbytes, dtype=torch.uint8, device=self.device) for _ in self.local_ranks]
             buf = SymmBuffer(name, nbytes, [t.data_ptr() for t in local], local, list(self.local_ranks))

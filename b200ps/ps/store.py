@@ -68,6 +68,7 @@ def _stream_id(name: str) -> int:
 
 class ParameterStore:
     LL_MAX_ELEMS = 1 << 19     # fp32 groups up to 2 MB use the low-latency packet push
+    NVLS_MIN_BYTES = 1 << 20   # dense groups of >= 1 MB live in multicast-bound memory and push through the switch
 
     def __init__(self, pool: SymmPool, placement: str = "flat_shard", seed: int = 1,
                  num_shards: Optional[int] = None):
@@ -87,6 +88,7 @@ class ParameterStore:
         self._built = False
         import os
         self.use_ll = os.environ.get("B200PS_LL_PUSH", "1") != "0"
+        self.use_nvls = os.environ.get("B200PS_NVLS", "1") != "0"
 
     # ------------------------------------------------------------------ registration
     def register(self, name: str, shape, *, group: str = "fp32", init: str = "zeros",
@@ -134,8 +136,12 @@ class ParameterStore:
                 continue
             layout = plan_layout(specs, self.world, self.placement, self._order)
             esz = 4 if dtype == torch.float32 else 2
-            work = pool.alloc(f"{gname}.work", layout.total * esz)
-            grads = pool.alloc(f"{gname}.grads", layout.total * esz)
+            # large dense groups: memory bound to an NVSwitch multicast object (when the box has one), so the
+            # synchronous push / collective pull run as multimem.ld_reduce / multimem.st (K1-NVLS)
+            mc = (self.world > 1 and layout.total * esz >= self.NVLS_MIN_BYTES
+                  and all(b % 8 == 0 for b in layout.bounds))
+            work = pool.alloc(f"{gname}.work", layout.total * esz, multicast=mc)
+            grads = pool.alloc(f"{gname}.grads", layout.total * esz, multicast=mc)
             if dtype == torch.bfloat16:
                 master = pool.alloc(f"{gname}.master", max(layout.max_shard, 8) * 4)
                 master_ptrs = [master.ptrs[r] - 4 * layout.bounds[r] for r in range(self.world)]
@@ -369,9 +375,27 @@ class ParameterStore:
             for r in self.pool.local_ranks:
                 g.grads.view(r, g.dtype).zero_()
 
-    def pull(self, groups=None, include_self: bool = False) -> None:
+    def _nvls(self, g: "_Group") -> bool:
+        return bool(g.work.mc_ptr and g.grads.mc_ptr and len(self.pool.local_ranks) == 1 and self.use_nvls)
+
+    def _store_nvls(self, g: "_Group", lr: float, reduce: bool, broadcast: bool, gs, cursor, cursor_step, cursor_wrap):
+        r = self.pool.local_ranks[0]
+        master = (g.work.ptrs[r] if g.master is None else g.master.ptrs[r] - 4 * g.layout.bounds[r])
+        ops.store_nvls(self.t_pads, g.grads.mc_ptr if reduce else 0, g.work.mc_ptr, g.work.ptrs[r], master,
+                       g.layout.bounds[r], g.layout.bounds[r + 1], dtype=g.dtype, world=self.world, rank=r, lr=lr,
+                       reduce=reduce, broadcast=broadcast, global_step=None if gs is None else self.gstep.ptrs[r],
+                       cursor=cursor, cursor_step=cursor_step, cursor_wrap=cursor_wrap)
+
+    def pull(self, groups=None, include_self: bool = False, collective: bool = False) -> None:
+        """Refresh the working copies from the owners' masters.  Default: every rank READS the owners' slices over
+        NVLink whenever it likes (what an asynchronous worker does before a step).  ``collective=True`` (all ranks
+        call it together): groups in multicast memory are broadcast by their OWNERS with ``multimem.st`` — every
+        byte leaves its owner once and the switch fans it out."""
         base, n = self._ranks()
         for g in self._iter_groups(groups):
+            if collective and self._nvls(g):
+                self._store_nvls(g, 0.0, False, True, None, None, 0, 1)
+                continue
             ops.pull(g.t_masters, g.t_outs, g.bounds, world=self.world, rank_base=base, local_ranks=n,
                      max_shard_elems=g.layout.max_shard, dtype=g.dtype,
                      include_self=include_self or g.master is not None)
@@ -385,6 +409,9 @@ class ParameterStore:
         for i, g in enumerate(gl):
             # one global_step per aggregated update: only the last group's launch counts it
             gs = self.t_gsteps if (count_step and i == len(gl) - 1) else None
+            if self._nvls(g) and R >= self.world:
+                self._store_nvls(g, lr, True, broadcast, gs, cursor if i == len(gl) - 1 else None, cursor_step, cursor_wrap)
+                continue
             if g.t_ll_grads is not None and R >= self.world and broadcast and self.use_ll:
                 ops.push_sync_ll(self.t_pads, g.t_masters, g.t_grads, g.bounds, gs, g.t_ll_grads, g.t_ll_params,
                                  world=self.world, rank_base=base, local_ranks=n,

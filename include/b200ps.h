@@ -353,6 +353,16 @@ int b200ps_push_sync_sgd(uint32_t* const* pads, float* const* masters, void* con
  * ("gradients written") and after ("parameters landed"). */
 int b200ps_push_sync_nvls(const float* mc_grads, float* mc_work, float* master, int64_t lo, int64_t hi, float step,
                           uint64_t* global_step, int32_t max_ctas, b200ps_stream_t stream);
+/* The ParameterStore's own NVLS path (both flag exchanges of the synchronous barrier inside the launch, like
+ * b200ps_push_sync_sgd): do_reduce = 1 is the synchronous push over ALL replicas — owner issues multimem.ld_reduce on
+ * the gradients' multicast address, applies mean-gradient SGD to its fp32 master and multimem.st's the fresh values to
+ * every replica (broadcast = 0: into its own copy only); do_reduce = 0 is the collective pull (owners broadcast their
+ * master slices).  fp32 groups pass master == work_local; bf16 groups (dtype B200PS_DT_BF16) reduce in the switch with
+ * fp32 accumulation.  [lo, hi) = the owned range, multiples of 8.  E1/E2 of SURVEY 2.5.3 (example.py:95-97,108,118). */
+int b200ps_store_nvls(uint32_t* const* pads, const void* mc_grads, void* mc_work, void* work_local, float* master,
+                      int64_t lo, int64_t hi, int32_t dtype, int32_t world, int32_t rank, float lr, int32_t do_reduce,
+                      int32_t broadcast, uint64_t* global_step, int32_t* cursor, int32_t cursor_step,
+                      int32_t cursor_wrap, b200ps_stream_t stream);
 int b200ps_push_sync_ll(uint32_t* const* pads, float* const* masters, const void* const* grads,
                         const int64_t* bounds, uint64_t* const* global_steps, void* const* ll_grads,
                         void* const* ll_params, int32_t world, int32_t rank_base, int32_t local_ranks,

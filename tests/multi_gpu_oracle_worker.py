@@ -129,6 +129,51 @@ def main():
         res["sparse_sync_bias_err"] = float((got_s[b_name].double().reshape(()) - b).abs())
         res["sparse_sync_global_step"] = ts.global_step
     ctx.control_barrier()
+    # ---- 5. large dense groups: the store's NVLS path (multimem.ld_reduce / multimem.st through the switch) against
+    #         a torch restatement of the synchronous update, fp32 and bf16 (+ fp32 master), then the collective pull
+    import torch.distributed as dist
+    for tag, dt, n_el in (("f32", "fp32", 3 << 19), ("bf16", "bf16:0", 1 << 21)):
+        sn = ParameterStore(ctx.pool)
+        sn.register("big", (n_el // 1024, 1024), group=dt, init="normal", stddev=0.5)
+        sn.build(); sn.initialize()
+        g = sn.groups[dt]
+        res[f"nvls_{tag}_used"] = bool(sn._nvls(g))
+        w0 = sn.state_dict()["big"].reshape(-1).clone()
+        ref = w0.double()
+        errs = []
+        for t in range(3):
+            gen = torch.Generator(device=dev).manual_seed(1000 * t + rank)
+            mine = torch.randn(n_el, device=dev, generator=gen) * 0.1
+            sn.grad("big").reshape(-1).copy_(mine)
+            allg = []
+            for r in range(world):          # every rank regenerates every rank's gradient (as stored: bf16-rounded for bf16)
+                gr = torch.Generator(device=dev).manual_seed(1000 * t + r)
+                v = torch.randn(n_el, device=dev, generator=gr) * 0.1
+                allg.append(v.to(sn.grad("big").dtype).double().cpu())
+            torch.cuda.synchronize(); ctx.control_barrier()
+            sn.push_sync(0.25)
+            torch.cuda.synchronize(); ctx.control_barrier()
+            ref = ref - 0.25 / world * torch.stack(allg).sum(0)
+            errs.append(float((sn.state_dict()["big"].reshape(-1).double() - ref).abs().max()))
+        work = sn.var("big").reshape(-1).double().cpu()
+        res[f"nvls_{tag}_master_err"] = max(errs)
+        res[f"nvls_{tag}_work_err"] = float((work - ref).abs().max())        # the broadcast reached this replica
+        res[f"nvls_{tag}_global_step"] = sn.global_step
+        lo_own, hi_own = g.layout.bounds[rank], g.layout.bounds[rank + 1]
+        flat = sn.flat_work(dt)
+        if g.master is None:                # fp32 group: the owned slice of the working copy IS the master — keep it
+            flat[:lo_own].zero_(); flat[hi_own:].zero_()
+        else:
+            flat.zero_()                    # collective pull restores everything from the owners' fp32 masters
+        torch.cuda.synchronize(); ctx.control_barrier()
+        sn.pull(collective=True)
+        torch.cuda.synchronize(); ctx.control_barrier()
+        res[f"nvls_{tag}_pull_err"] = float((sn.var("big").reshape(-1).double().cpu() - ref).abs().max())
+        allw = [None] * world
+        dist.all_gather_object(allw, float(sn.var("big").double().sum().item()), group=ctx.group)
+        res[f"nvls_{tag}_replicas_identical"] = len(set(allw)) == 1
+        del sn
+        ctx.control_barrier()
     if rank == 0:
         json.dump(res, open(os.path.join(out_dir, "oracle_result.json"), "w"))
     print("rank", rank, json.dumps(res), flush=True)

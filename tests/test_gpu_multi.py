@@ -95,6 +95,11 @@ def test_multi_gpu_results_match_independent_oracles(native_lib, tmp_path):
     assert res["async_conserved"] and res["async_global_step"] == 25 * n, res
     assert res["sparse_sync_max_abs_err"] < 1e-4 and res["sparse_sync_bias_err"] < 1e-5, res
     assert res["sparse_sync_global_step"] == 5, res
+    # large groups: through the switch when the box has NVLS (else the same numbers from the P2P kernels)
+    assert res["nvls_f32_master_err"] < 1e-5 and res["nvls_f32_work_err"] < 1e-5 and res["nvls_f32_pull_err"] < 1e-5, res
+    assert res["nvls_bf16_master_err"] < 2e-2 and res["nvls_bf16_work_err"] < 2e-2 and res["nvls_bf16_pull_err"] < 2e-2, res
+    assert res["nvls_f32_replicas_identical"] and res["nvls_bf16_replicas_identical"], res
+    assert res["nvls_f32_global_step"] == 3 and res["nvls_bf16_global_step"] == 3, res
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
