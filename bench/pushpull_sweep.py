@@ -2,10 +2,11 @@
 
 Run under torchrun (one rank per GPU).  For every size S (bytes of fp32 parameters) it times
 
-    push_sync : b200ps K1 (reduce-scatter + mean + SGD + broadcast, flags included)
-                vs NCCL reduce_scatter(AVG) + add_ + all_gather          (same result)
-    pull      : b200ps pull kernel (all-gather of owner slices)
-                vs NCCL all_gather_into_tensor
+    push_sync : the ParameterStore's push (reduce-scatter + mean + SGD + broadcast, flags included): LL packets for
+                small groups, K1 over peer loads/stores, and from 1 MB K1-NVLS (multimem.ld_reduce / multimem.st) —
+                both timed where both apply — vs NCCL reduce_scatter(AVG) + add_ + all_gather   (same result)
+    pull      : reader-driven pull kernel (all-gather of owner slices) and the collective owner-side multimem.st
+                broadcast vs NCCL all_gather_into_tensor
     push_async: b200ps K3 (peer red.add of -lr*g into the owners, no barrier)
                 vs NCCL reduce_scatter(SUM) + add_                        (closest library form)
 
@@ -61,7 +62,16 @@ def main():
         store.initialize()
         store.flat_grads("fp32").normal_()
         iters = 200 if S <= (1 << 20) else (30 if S <= (1 << 26) else 8)
-        t_push = timeit(lambda: store.push_sync(1e-3), iters, ctx)
+        g0 = store.groups["fp32"]
+        has_nvls = store._nvls(g0)                 # >= 1 MB groups live in multicast memory (when the box has NVLS)
+        t_push = timeit(lambda: store.push_sync(1e-3), iters, ctx)          # the store's default path for this size
+        t_push_p2p = t_push_nvls = t_pull_nvls = None
+        if has_nvls:
+            t_push_nvls = t_push
+            store.use_nvls = False
+            t_push_p2p = timeit(lambda: store.push_sync(1e-3), iters, ctx)  # K1 over peer loads / stores
+            store.use_nvls = True
+            t_pull_nvls = timeit(lambda: store.pull(collective=True), iters, ctx)   # owner-side multimem.st broadcast
         t_pull = timeit(lambda: store.pull(include_self=False), iters, ctx)
         t_async = timeit(lambda: store.push_async(1e-3, count_step=False), iters, ctx)
         # NCCL twin on plain tensors of the same padded size
@@ -79,25 +89,18 @@ def main():
             dist.reduce_scatter_tensor(sl, g, op=dist.ReduceOp.SUM)
             master.add_(sl, alpha=-1e-3)
 
-        # K1-NVLS: the same push through NVSwitch multicast (torch symmetric memory); skipped where unavailable
-        t_nvls = None
-        if N > 1 and os.environ.get("SWEEP_NVLS", "1") != "0":
-            try:
-                from b200ps.parallel.nvls import NvlsGroup
-                nv = NvlsGroup(total, 1e-3)
-                nv.grads.normal_()
-                t_nvls = timeit(nv.push_sync, iters, ctx)
-                del nv
-            except Exception as e:  # noqa: BLE001
-                if ctx.rank == 0 and S == sizes[0]:
-                    print("nvls push unavailable:", type(e).__name__, str(e)[:200], flush=True)
         n_push = timeit(nccl_push, iters, ctx)
         n_pull = timeit(lambda: dist.all_gather_into_tensor(w, master), iters, ctx)
         n_async = timeit(nccl_async, iters, ctx)
         f = (N - 1) / N
         rec = {"bytes": S, "n_gpus": N,
                "push_sync_us": round(t_push, 2), "nccl_push_us": round(n_push, 2),
-               "nvls_push_us": None if t_nvls is None else round(t_nvls, 2),
+               "push_sync_path": "nvls" if has_nvls else ("ll" if g0.t_ll_grads is not None and store.use_ll else "p2p"),
+               "push_sync_p2p_us": None if t_push_p2p is None else round(t_push_p2p, 2),
+               "push_sync_nvls_us": None if t_push_nvls is None else round(t_push_nvls, 2),
+               "pull_nvls_us": None if t_pull_nvls is None else round(t_pull_nvls, 2),
+               "push_vs_nccl": round(n_push / t_push, 3),
+               "pull_best_vs_nccl": round(n_pull / min(t_pull, t_pull_nvls or t_pull), 3),
                "pull_us": round(t_pull, 2), "nccl_allgather_us": round(n_pull, 2),
                "push_async_us": round(t_async, 2), "nccl_rs_apply_us": round(n_async, 2),
                "push_sync_GBs_per_dir": round(2 * f * S / t_push / 1e3, 1),

@@ -135,26 +135,43 @@ __global__ void __launch_bounds__(512) store_nvls_kernel(const NvlsArgs a) {
     if (tid < world) wait_flag_geq(pad + kFlagGradsReady + tid, epoch);
     __syncthreads();
   }
-  // -- phase 1
+  // -- phase 1 (kU independent 16-byte accesses per thread per trip: all switch reads are issued before any use)
   const long long nvec = (a.hi - a.lo) / P;
-  for (long long v = (long long)blockIdx.x * blockDim.x + tid; v < nvec; v += (long long)gridDim.x * blockDim.x) {
-    const long long i = a.lo + v * P;
-    float w[P];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kU = 4;
+  for (long long v0 = (long long)blockIdx.x * blockDim.x + tid; v0 < nvec; v0 += kU * stride) {
+    float g[kU][P], w[kU][P];
 #pragma unroll
-    for (int k = 0; k < P; k += 4) {
-      const float4 m = *reinterpret_cast<const float4*>(a.master + i + k);
-      w[k] = m.x; w[k + 1] = m.y; w[k + 2] = m.z; w[k + 3] = m.w;
+    for (int u = 0; u < kU; ++u) {
+      const long long v = v0 + u * stride;
+      if (v < nvec && a.do_reduce) Mm<G>::ld_reduce(reinterpret_cast<const G*>(a.mc_grads) + a.lo + v * P, g[u]);
     }
-    if (a.do_reduce) {
-      float g[P];
-      Mm<G>::ld_reduce(reinterpret_cast<const G*>(a.mc_grads) + i, g);
 #pragma unroll
-      for (int k = 0; k < P; ++k) w[k] = fmaf(-a.step, g[k], w[k]);
+    for (int u = 0; u < kU; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= nvec) continue;
+      const long long i = a.lo + v * P;
 #pragma unroll
-      for (int k = 0; k < P; k += 4) *reinterpret_cast<float4*>(a.master + i + k) = make_float4(w[k], w[k + 1], w[k + 2], w[k + 3]);
+      for (int k = 0; k < P; k += 4) {
+        const float4 m = __ldcs(reinterpret_cast<const float4*>(a.master + i + k));
+        w[u][k] = m.x; w[u][k + 1] = m.y; w[u][k + 2] = m.z; w[u][k + 3] = m.w;
+      }
     }
-    if (a.broadcast) Mm<O>::st(reinterpret_cast<O*>(a.mc_work) + i, w);
-    else Mm<O>::st_local(reinterpret_cast<O*>(a.work_local) + i, w);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= nvec) continue;
+      const long long i = a.lo + v * P;
+      if (a.do_reduce) {
+#pragma unroll
+        for (int k = 0; k < P; ++k) w[u][k] = fmaf(-a.step, g[u][k], w[u][k]);
+#pragma unroll
+        for (int k = 0; k < P; k += 4)
+          __stcs(reinterpret_cast<float4*>(a.master + i + k), make_float4(w[u][k], w[u][k + 1], w[u][k + 2], w[u][k + 3]));
+      }
+      if (a.broadcast) Mm<O>::st(reinterpret_cast<O*>(a.mc_work) + i, w[u]);
+      else Mm<O>::st_local(reinterpret_cast<O*>(a.work_local) + i, w[u]);
+    }
   }
   // -- phase 2: when every CTA of this rank is done, tell the peers and wait for theirs
   __syncthreads();
@@ -203,7 +220,8 @@ extern "C" int b200ps_store_nvls(uint32_t* const* pads, const void* mc_grads, vo
   const int per = dtype == B200PS_DT_F32 ? 4 : 8;
   const long long nvec = (hi - lo) / per;
   // every rank launches at least one CTA: the flag exchanges need all of them even when a slice is empty
-  const int ctas = (int)std::max<long long>(1, std::min<long long>((nvec + 511) / 512, (long long)sm_count() * 2));
+  static const int cta_mult = [] { const char* e = getenv("B200PS_NVLS_CTAS_PER_SM"); return e ? atoi(e) : 2; }();
+  const int ctas = (int)std::max<long long>(1, std::min<long long>((nvec + 2047) / 2048, (long long)sm_count() * cta_mult));
   cudaStream_t s = as_stream(stream);
   if (dtype == B200PS_DT_F32)
     B200PS_CUDA_CHECK(launch_pdl(store_nvls_kernel<float, float>, dim3(ctas), dim3(512), 0, s, a));
