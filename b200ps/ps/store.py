@@ -69,6 +69,7 @@ def _stream_id(name: str) -> int:
 class ParameterStore:
     LL_MAX_ELEMS = 1 << 19     # fp32 groups up to 2 MB use the low-latency packet push
     NVLS_MIN_BYTES = 1 << 20   # dense groups of >= 1 MB live in multicast-bound memory and push through the switch
+    NVLS_MAX_BYTES = 1 << 29   # ... up to 512 MB: at 1 GB the P2P kernel is faster again (profiles/pushpull_sweep_n8_r2.json)
 
     def __init__(self, pool: SymmPool, placement: str = "flat_shard", seed: int = 1,
                  num_shards: Optional[int] = None):
@@ -375,8 +376,15 @@ class ParameterStore:
             for r in self.pool.local_ranks:
                 g.grads.view(r, g.dtype).zero_()
 
-    def _nvls(self, g: "_Group") -> bool:
-        return bool(g.work.mc_ptr and g.grads.mc_ptr and len(self.pool.local_ranks) == 1 and self.use_nvls)
+    def _nvls(self, g: "_Group", prefer: Optional[bool] = None) -> bool:
+        """Does this group's push / collective pull go through the switch?  Needs multicast-bound buffers; by default
+        taken for 1 MB .. 512 MB groups (measured window in which it beats the P2P kernel on 8 GPUs); ``prefer``
+        overrides the size rule either way."""
+        if not (g.work.mc_ptr and g.grads.mc_ptr and len(self.pool.local_ranks) == 1 and self.use_nvls):
+            return False
+        if prefer is not None:
+            return bool(prefer)
+        return g.work.nbytes <= self.NVLS_MAX_BYTES
 
     def _store_nvls(self, g: "_Group", lr: float, reduce: bool, broadcast: bool, gs, cursor, cursor_step, cursor_wrap):
         r = self.pool.local_ranks[0]
@@ -393,7 +401,7 @@ class ParameterStore:
         byte leaves its owner once and the switch fans it out."""
         base, n = self._ranks()
         for g in self._iter_groups(groups):
-            if collective and self._nvls(g):
+            if collective and self._nvls(g, True):
                 self._store_nvls(g, 0.0, False, True, None, None, 0, 1)
                 continue
             ops.pull(g.t_masters, g.t_outs, g.bounds, world=self.world, rank_base=base, local_ranks=n,
@@ -402,14 +410,14 @@ class ParameterStore:
 
     def push_sync(self, lr: float, replicas_to_aggregate: Optional[int] = None, groups=None,
                   count_step: bool = True, cursor=None, cursor_step: int = 0, cursor_wrap: int = 1,
-                  broadcast: bool = True) -> None:
+                  broadcast: bool = True, nvls: Optional[bool] = None) -> None:
         base, n = self._ranks()
         R = replicas_to_aggregate or self.world
         gl = list(self._iter_groups(groups))
         for i, g in enumerate(gl):
             # one global_step per aggregated update: only the last group's launch counts it
             gs = self.t_gsteps if (count_step and i == len(gl) - 1) else None
-            if self._nvls(g) and R >= self.world:
+            if R >= self.world and self._nvls(g, nvls):
                 self._store_nvls(g, lr, True, broadcast, gs, cursor if i == len(gl) - 1 else None, cursor_step, cursor_wrap)
                 continue
             if g.t_ll_grads is not None and R >= self.world and broadcast and self.use_ll:

@@ -424,6 +424,11 @@ class WideMLPTrainer(_TrainerBase):
         # cheaper (measured 12.1 vs 13.3 ms/step on 8 GPUs)
         self.fused_pull = fused_pull and ctx.world > 1 and hidden % (64 * ctx.world) == 0
         self.overlap = overlap
+        # per-layer pushes that run on the side stream UNDER the backward GEMMs stay on the P2P kernel: measured on
+        # 8 GPUs, 11.6 ms/step against 12.0-13.3 ms through the switch (tools/wide_nvls_sweep.py); B200PS_WIDE_NVLS=1
+        # opts in.  Pushes that are not overlapped take the store's default (NVLS for 1 MB .. 512 MB groups).
+        import os
+        self._nvls_overlapped = True if os.environ.get("B200PS_WIDE_NVLS", "0") == "1" else False
         self._side = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
         self._step = _GraphedStep(self._body, dev, use_graph)
         if ctx.group is not None:
@@ -455,7 +460,8 @@ class WideMLPTrainer(_TrainerBase):
         def on_wgrad_done(l):
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                st.push_sync(self.lr, R, groups=(m.wgroup(l),), count_step=False, broadcast=not self.fused_pull)
+                st.push_sync(self.lr, R, groups=(m.wgroup(l),), count_step=False, broadcast=not self.fused_pull,
+                             nvls=self._nvls_overlapped)
 
         loss, correct = m.forward_backward(st, self.x[r], self.labels[r], rank=r, fused_pull=self.fused_pull,
                                            on_wgrad_done=on_wgrad_done)

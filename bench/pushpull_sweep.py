@@ -63,14 +63,13 @@ def main():
         store.flat_grads("fp32").normal_()
         iters = 200 if S <= (1 << 20) else (30 if S <= (1 << 26) else 8)
         g0 = store.groups["fp32"]
-        has_nvls = store._nvls(g0)                 # >= 1 MB groups live in multicast memory (when the box has NVLS)
+        has_mc = store._nvls(g0, True)             # >= 1 MB groups live in multicast memory (when the box has NVLS)
+        has_nvls = store._nvls(g0)                 # ... and push through the switch by default up to 512 MB
         t_push = timeit(lambda: store.push_sync(1e-3), iters, ctx)          # the store's default path for this size
         t_push_p2p = t_push_nvls = t_pull_nvls = None
-        if has_nvls:
-            t_push_nvls = t_push
-            store.use_nvls = False
-            t_push_p2p = timeit(lambda: store.push_sync(1e-3), iters, ctx)  # K1 over peer loads / stores
-            store.use_nvls = True
+        if has_mc:
+            t_push_nvls = timeit(lambda: store.push_sync(1e-3, nvls=True), iters, ctx)
+            t_push_p2p = timeit(lambda: store.push_sync(1e-3, nvls=False), iters, ctx)   # K1 over peer loads / stores
             t_pull_nvls = timeit(lambda: store.pull(collective=True), iters, ctx)   # owner-side multimem.st broadcast
         t_pull = timeit(lambda: store.pull(include_self=False), iters, ctx)
         t_async = timeit(lambda: store.push_async(1e-3, count_step=False), iters, ctx)

@@ -122,7 +122,7 @@ struct NvlsArgs {
 };
 
 template <typename G, typename O>
-__global__ void __launch_bounds__(512) store_nvls_kernel(const NvlsArgs a) {
+__global__ void __launch_bounds__(256) store_nvls_kernel(const NvlsArgs a) {
   constexpr int P = Mm<O>::kPer;
   const int tid = threadIdx.x, world = a.world, rank = a.rank;
   uint32_t* pad = a.pads[rank];
@@ -220,13 +220,16 @@ extern "C" int b200ps_store_nvls(uint32_t* const* pads, const void* mc_grads, vo
   const int per = dtype == B200PS_DT_F32 ? 4 : 8;
   const long long nvec = (hi - lo) / per;
   // every rank launches at least one CTA: the flag exchanges need all of them even when a slice is empty
-  static const int cta_mult = [] { const char* e = getenv("B200PS_NVLS_CTAS_PER_SM"); return e ? atoi(e) : 2; }();
-  const int ctas = (int)std::max<long long>(1, std::min<long long>((nvec + 2047) / 2048, (long long)sm_count() * cta_mult));
+  // as many CTAs as the P2P kernel by default (one per SM, 256 threads); B200PS_NVLS_CTAS caps it for pushes that
+  // run on a side stream under GEMMs (read per launch: an experiment knob)
+  const char* cap_env = getenv("B200PS_NVLS_CTAS");
+  const int cap = cap_env && atoi(cap_env) > 0 ? atoi(cap_env) : sm_count();
+  const int ctas = (int)std::max<long long>(1, std::min<long long>((nvec + 1023) / 1024, (long long)cap));
   cudaStream_t s = as_stream(stream);
   if (dtype == B200PS_DT_F32)
-    B200PS_CUDA_CHECK(launch_pdl(store_nvls_kernel<float, float>, dim3(ctas), dim3(512), 0, s, a));
+    B200PS_CUDA_CHECK(launch_pdl(store_nvls_kernel<float, float>, dim3(ctas), dim3(256), 0, s, a));
   else
-    B200PS_CUDA_CHECK(launch_pdl(store_nvls_kernel<__nv_bfloat16, __nv_bfloat16>, dim3(ctas), dim3(512), 0, s, a));
+    B200PS_CUDA_CHECK(launch_pdl(store_nvls_kernel<__nv_bfloat16, __nv_bfloat16>, dim3(ctas), dim3(256), 0, s, a));
   B200PS_LAUNCH_CHECK();
   return 0;
 }
