@@ -432,6 +432,65 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     }
 
 
+def verify_sparse(ctx):
+    """Correct-update evidence for the sparse path on a LEARNABLE problem (2^14 features, so ids repeat across
+    steps): 60 synchronous steps of SparseLRTrainer against the float64 restatement of the same steps (mean of the
+    replicas' gradients per step), then AUC of the trained model on the training batches.  The throughput configs
+    use 2^24 features, where almost no feature is seen twice and the loss cannot tell a right update from a wrong
+    one."""
+    import torch
+    from b200ps import ops
+    from b200ps.metrics.auc import StreamingAUC
+    from b200ps.models.sparse_lr import sparse_lr_reference
+    from b200ps.train import SparseLRTrainer
+    F, B, nnz, spread, T, lr = 1 << 14, 500, 50, 10, 60, 2.0
+    dev = ctx.device
+    tr = SparseLRTrainer(ctx, features=F, lr=lr, mode="sync", use_graph=False)
+    w_name, b_name = tr.model.W, tr.model.Bn
+    init = tr.store.state_dict()
+    batches = []
+    for r in range(ctx.world):
+        per = []
+        for t in range(3):
+            rp = torch.empty(B + 1, device=dev, dtype=torch.int32); fid = torch.empty(B * (nnz + spread), device=dev, dtype=torch.int64)
+            fv = torch.empty(B * (nnz + spread), device=dev); y = torch.empty(B, device=dev)
+            ops.synth_sparse(rp, fid, fv, y, nnz_mean=nnz, spread=spread, features=F, seed=21, offset=(r * 3 + t) * B)
+            per.append((rp, fid, fv, y))
+        batches.append(per)
+    losses = []
+    for t in range(T):
+        tr.step(batches[ctx.rank][t % 3])
+        if t in (0, T - 1):
+            losses.append(tr.read_loss())
+    torch.cuda.synchronize()
+    ctx.control_barrier()
+    got = tr.store.state_dict()
+    out = {"features": F, "steps": T, "loss_first": losses[0], "loss_last": losses[-1]}
+    auc = StreamingAUC(device=dev)
+    for t in range(3):
+        pred, _ = tr.predict(batches[ctx.rank][t])
+        auc.update(pred, batches[ctx.rank][t][3])
+    out["train_auc_rank0"] = float(auc.result())
+    if ctx.rank == 0:
+        W = init[w_name].double().reshape(-1).clone(); b = init[b_name].double().reshape(()).clone()
+        cpu = [[tuple(x.cpu() for x in bt) for bt in per] for per in batches]
+        ref_loss = None
+        for t in range(T):
+            dW = torch.zeros_like(W); db = 0.0
+            for r in range(ctx.world):
+                l, _, (ids, vals), g_b = sparse_lr_reference(W, b, *cpu[r][t % 3])
+                if r == 0:
+                    ref_loss = float(l)
+                dW.index_add_(0, ids, vals); db = db + g_b
+            W -= lr / ctx.world * dW; b = b - lr / ctx.world * db
+        out["max_abs_weight_err_vs_float64_oracle"] = float((got[w_name].double().reshape(-1) - W).abs().max())
+        out["oracle_loss_last"] = ref_loss
+        out["ok"] = bool(out["max_abs_weight_err_vs_float64_oracle"] < 1e-3 and losses[-1] < 0.9 * losses[0]
+                         and abs(losses[-1] - ref_loss) < 1e-3 * max(1.0, abs(ref_loss)) and out["train_auc_rank0"] > 0.6)
+    _release(tr)
+    return out
+
+
 def _measured_peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -529,6 +588,11 @@ def main():
     }
     primary = runners[primary_name]()
     extra = {}
+    if args.config in ("all", "sparse_lr"):
+        try:
+            extra["sparse_lr_verify"] = verify_sparse(ctx)
+        except Exception as e:
+            extra["sparse_lr_verify"] = {"error": f"{type(e).__name__}: {e}"}
     if args.config == "all":
         for name in ("mnist_mlp_async", "sparse_lr", "sparse_wide_deep", "wide_mlp"):
             try:

@@ -58,11 +58,6 @@ __device__ __forceinline__ float* w_addr(const SparseParams& p, int64_t id) {
 __device__ __forceinline__ bool id_ok(const SparseParams& p, int64_t id) {
   return (unsigned long long)id < (unsigned long long)p.features;
 }
-__device__ __forceinline__ float w_load(const SparseParams& p, int64_t id, int& bad) {
-  if (id_ok(p, id)) return __ldcg(w_addr(p, id));
-  ++bad;
-  return 0.f;
-}
 
 __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseParams p) {
   __shared__ float s_loss[kSparseThreads / 32];
@@ -77,18 +72,39 @@ __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseP
 
   for (int ex = blockIdx.x * (kSparseThreads / 32) + warp_in_cta; ex < p.B; ex += warps_total) {
     const int beg = p.row_ptr[ex], end = p.row_ptr[ex + 1];
-    float dz;
-    if (p.do_forward) {
-      float z = 0.f;
-      // two loads in flight per lane: the gather is pure latency
-      int j = beg + lane;
-      for (; j + 32 < end; j += 64) {
-        const float w0 = w_load(p, p.fid[j], bad);
-        const float w1 = w_load(p, p.fid[j + 32], bad);
-        z = fmaf(w0, p.fval[j], z);
-        z = fmaf(w1, p.fval[j + 32], z);
+    float dz = p.do_forward ? 0.f : p.dz_in[ex];
+    // Rows are walked in batches of 128 non-zeros (4 per lane): ids and values are fetched first so the four row
+    // gathers of a lane leave back to back — the gather is pure latency, 7 of 8 rows live on another GPU.  A row
+    // that fits one batch (the common case, ~100 non-zeros) keeps its ids / values / validity in registers for
+    // the scatter, so the fused step reads the CSR arrays once.
+    const bool one_batch = end - beg <= 128;
+    int64_t id[4];
+    float fv[4];
+    bool ok[4];
+    float z = 0.f;
+    for (int j0 = beg; j0 < end; j0 += 128) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + lane + 32 * u;
+        id[u] = j < end ? p.fid[j] : -1;
+        fv[u] = j < end ? p.fval[j] : 0.f;
+        ok[u] = id_ok(p, id[u]);
+        if (j < end && !ok[u]) ++bad;
       }
-      if (j < end) z = fmaf(w_load(p, p.fid[j], bad), p.fval[j], z);
+      if (p.do_forward) {
+        float w[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) w[u] = ok[u] ? __ldcg(w_addr(p, id[u])) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) z = fmaf(w[u], fv[u], z);
+      } else if (p.do_update) {        // update-only launch: scatter this batch right away
+        const float s = -p.lr * dz;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (ok[u]) red_add_f32_sys(w_addr(p, id[u]), s * fv[u]);
+      }
+    }
+    if (p.do_forward) {
       z = warp_sum(z) + b;
       const float y = p.labels[ex];
       const float pr = 1.f / (1.f + __expf(-z));
@@ -98,18 +114,21 @@ __global__ void __launch_bounds__(kSparseThreads) sparse_lr_kernel(const SparseP
         if (p.pred) p.pred[ex] = pr;
         if (p.dz_out) p.dz_out[ex] = dz;
       }
-    } else {
-      dz = p.dz_in[ex];
-    }
-    if (p.do_update) {
-      const float s = -p.lr * dz;
-      for (int j = beg + lane; j < end; j += 32) {
-        const int64_t id = p.fid[j];
-        if (id_ok(p, id)) red_add_f32_sys(w_addr(p, id), s * p.fval[j]);
-        else if (!p.do_forward) ++bad;
+      if (p.do_update) {
+        const float s = -p.lr * dz;
+        if (one_batch) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (ok[u]) red_add_f32_sys(w_addr(p, id[u]), s * fv[u]);
+        } else {
+          for (int j = beg + lane; j < end; j += 32) {
+            const int64_t f = p.fid[j];
+            if (id_ok(p, f)) red_add_f32_sys(w_addr(p, f), s * p.fval[j]);
+          }
+        }
       }
-      if (lane == 0) dz_acc += dz;
     }
+    if (p.do_update && lane == 0) dz_acc += dz;
   }
   if (bad && p.bad_ids) atomicAdd(p.bad_ids, (unsigned long long)bad);
   if (lane == 0) { s_loss[warp_in_cta] = loss_acc; s_dz[warp_in_cta] = dz_acc; }
