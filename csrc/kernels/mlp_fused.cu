@@ -783,7 +783,7 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   const int P = H * C + C + H + 2;
   const size_t slab_f = (size_t)p.KS * B * H, dz_f = (size_t)B * H, part_f = (size_t)p.NT * P;
   Workspace ws;
-  int rc = get_workspace(sizeof(float) * (slab_f + dz_f + part_f), &ws);
+  int rc = get_workspace(sizeof(float) * (slab_f + dz_f + part_f), &ws, as_stream(stream), true);
   if (rc) return rc;
   p.slabs = reinterpret_cast<float*>(ws.data);
   p.dz2 = p.slabs + slab_f;
@@ -806,7 +806,33 @@ extern "C" int b200ps_mlp_fused_step(const float* x, const int32_t* labels, cons
   // load path and FMA pipes (B200PS_FUSED_SMEM_KB overrides for experiments)
   static const size_t min_smem = [] { const char* e = getenv("B200PS_FUSED_SMEM_KB"); return (size_t)(e ? atoi(e) : 116) * 1024; }();
   const size_t smem_launch = std::max(smem, min_smem);
-  B200PS_CUDA_CHECK(launch_pdl(mlp_fused_step_kernel, dim3(G), dim3(kFsThreads), smem_launch, as_stream(stream), p));
+  // The two grid barriers need all G CTAs on the machine at once.  G <= #SMs was checked above; here the launch
+  // itself is checked: one CTA of this size must fit an SM (it does: 1 CTA/SM by construction), and the launch is
+  // marked cooperative (measured cost: none, 13.64 vs 13.61 us/step; B200PS_FUSED_COOP=0 switches it off) so that
+  // the driver schedules the grid only when every CTA can be resident, instead of letting a co-tenant kernel turn
+  // the barrier into a 4-second trap.
+  static int occ_ok[64] = {0};
+  if (occ_ok[dev & 63] == 0) {
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mlp_fused_step_kernel, kFsThreads, smem_launch);
+    occ_ok[dev & 63] = (e == cudaSuccess && per_sm >= 1) ? 1 : -1;
+    if (e != cudaSuccess) cudaGetLastError();
+  }
+  B200PS_REQUIRE(occ_ok[dev & 63] == 1, "mlp_fused_step: a CTA of %zu bytes of shared memory does not fit an SM of this device",
+                 smem_launch);
+  static const bool coop = [] { const char* e = getenv("B200PS_FUSED_COOP"); return !(e && e[0] == '0'); }();
+  if (coop) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(G); cfg.blockDim = dim3(kFsThreads); cfg.dynamicSmemBytes = smem_launch; cfg.stream = as_stream(stream);
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    B200PS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, mlp_fused_step_kernel, p));
+  } else {
+    B200PS_CUDA_CHECK(launch_pdl(mlp_fused_step_kernel, dim3(G), dim3(kFsThreads), smem_launch, as_stream(stream), p));
+  }
   B200PS_LAUNCH_CHECK();
+  workspace_mark_used(as_stream(stream));
   return 0;
 }

@@ -670,7 +670,7 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
   const int CP = C <= 16 ? 16 : 32;
   const int P = H * C + C + H + 2;
   Workspace ws;
-  int rc = get_workspace(sizeof(float) * (size_t)ctas * P, &ws);
+  int rc = get_workspace(sizeof(float) * (size_t)ctas * P, &ws, s, true);
   if (rc) return rc;
   const size_t smem = sizeof(float) * ((size_t)H * (CP + 4) + CP + ((H + 3) & ~3) + 2 * (size_t)kT2Rows * H +
                                        (size_t)kT2Rows * CP);
@@ -681,6 +681,7 @@ extern "C" int b200ps_mlp_tail(const float* z2, const float* b1, const float* w2
     B200PS_CUDA_CHECK(launch_pdl(mlp_tail2_kernel<32>, dim3(ctas), dim3(kT2Threads), smem, s, p,
                                  reinterpret_cast<float*>(ws.data), ws.counters));
   B200PS_LAUNCH_CHECK();
+  workspace_mark_used(s);
   return 0;
 }
 

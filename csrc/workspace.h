@@ -17,8 +17,13 @@ struct Workspace {
   unsigned int* counters = nullptr;  // 64 zero-initialised uint32 arrival counters (self-resetting)
 };
 
-// Returns the current device's workspace with at least `bytes` of scratch.
-int get_workspace(size_t bytes, Workspace* out);
+// Returns the current device's workspace with at least `bytes` of scratch.  With a stream (the one the kernel is
+// about to be launched on) the single-stream rule is CHECKED on eager launches: if the previous eager user ran on a
+// different stream and has not finished, the call fails instead of letting two kernels share the scratch.  (Launches
+// under stream capture are not tracked: a captured graph replays wherever its owner puts it.)
+int get_workspace(size_t bytes, Workspace* out, cudaStream_t stream = nullptr, bool check_stream = false);
+// Call right after the launch that uses the workspace (records "in use until here" for the check above).
+void workspace_mark_used(cudaStream_t stream);
 
 // Device counter of feature ids that the sparse kernels refused (id < 0 or id >= features); counters[62..63].
 unsigned long long* bad_id_counter();

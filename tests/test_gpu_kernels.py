@@ -584,3 +584,31 @@ def test_mlp_cluster_steps_match_float64_reference(native_lib, B, D, H, Cn):
     for t, want in zip(wp, (W1, B1, W2, B2)):
         assert torch.allclose(t.double(), want, atol=5e-3, rtol=5e-3)
     assert abs(lossp[0] - ref_loss[0]) < 5e-3 * max(1.0, abs(ref_loss[0]))
+
+
+def test_workspace_refuses_overlapping_streams(native_lib):
+    """The library workspace is one block per device: an eager launch that needs it while a launch on ANOTHER stream
+    may still be using it is refused (instead of two kernels sharing scratch); the same stream, or the other stream
+    once the first has finished, is fine."""
+    from b200ps import ops
+    from b200ps.ops.native import NativeError
+    B, H, C = 64, 32, 10
+    g = torch.Generator(device=DEV).manual_seed(2)
+    z2 = torch.randn(B, H, device=DEV, generator=g); b1 = torch.zeros(H, device=DEV)
+    w2 = torch.randn(H, C, device=DEV, generator=g); b2 = torch.zeros(C, device=DEV)
+    labels = torch.randint(0, C, (B,), device=DEV, generator=g, dtype=torch.int32)
+    loss = torch.zeros(1, device=DEV); correct = torch.zeros(1, device=DEV, dtype=torch.int32)
+    kw = dict(loss_sum=loss, correct=correct, train=False, loss_scale=1.0 / B)
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(sa):
+        torch.cuda._sleep(400_000_000)                      # ~0.2 s of GPU time queued ahead on stream A
+        ops.mlp_tail(z2, b1, w2, b2, labels, **kw)
+        ops.mlp_tail(z2, b1, w2, b2, labels, **kw)          # same stream: ordered, allowed
+    with torch.cuda.stream(sb):
+        with pytest.raises(NativeError, match="another stream"):
+            ops.mlp_tail(z2, b1, w2, b2, labels, **kw)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(sb):
+        ops.mlp_tail(z2, b1, w2, b2, labels, **kw)          # stream A has finished: fine
+    torch.cuda.synchronize()
