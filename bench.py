@@ -297,6 +297,14 @@ def bench_mnist(ctx, args, sampler, mode):
                 "blocking_value": B * ctx.world * args.steps / (ms_e2e_blocking / 1e3),
                 "blocking_api": "MLPTrainer.step_from_host (host blocks on every step's loss)"},
         "loss_first": loss0, "loss_last": loss1, "train_subset_accuracy": acc, "global_step": gstep,
+        # latency-bound step: 47.6 MFLOP (fwd 2*B*(784*100+100*10), bwd 2x) against the fp32-FFMA peak of the chip
+        "roofline": {"flop_per_step": 6.0 * B * (784 * 100 + 100 * 10),
+                     "achieved_tflops_per_gpu": 6.0 * B * (784 * 100 + 100 * 10) / (ms / args.steps / 1e3) / 1e12,
+                     "fraction_of_fp32_ffma_peak_72_tflops": 6.0 * B * (784 * 100 + 100 * 10) / (ms / args.steps / 1e3) / 72e12,
+                     "nvlink_bytes_per_rank_per_step": (0 if ctx.world == 1 else
+                                                        2 * 8 * 79510 * (ctx.world - 1) // ctx.world),
+                     "note": "bound by its dependency chain (two device-wide barriers, L2 round trips, two NVLink hops "
+                             "when world > 1), not by a throughput limit: see BASELINE.md"},
         "config": {"model": "mnist_sigmoid_mlp_784_100_10", "global_batch": B * ctx.world,
                    "per_gpu_batch": B, "seq_len": None, "mode": mode,
                    "parallelism": f"dp{ctx.world}+ps_shard{ctx.world}", "lr": 0.0005,
