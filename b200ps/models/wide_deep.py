@@ -52,7 +52,7 @@ class SparseWideDeep:
     P, P2 = "_pending/coefficients", "_pending/deep_weights_1"      # scratch tables of the deferred update
 
     def __init__(self, features: int, dim: int = 128, wide: bool = True, stddev: float = 0.01,
-                 deferred: Optional[bool] = None):
+                 deferred: Optional[bool] = None, owner: Optional[bool] = None):
         """``deferred`` (opt-in, also ``B200PS_WD_DEFERRED=1``): workers push one scalar coefficient
         per non-zero into a pending table and the owner of a shard folds them into W and E before its next
         step (the embedding update is rank one, dE[fid,:] = c[fid] * w2) — 4 instead of 516 bytes of remote
@@ -62,7 +62,14 @@ class SparseWideDeep:
             raise ValueError("SparseWideDeep: dim must be 128, 256 or 512")
         self.features, self.dim, self.wide, self.stddev = int(features), int(dim), wide, stddev
         self.deferred = (os.environ.get("B200PS_WD_DEFERRED", "0") != "0") if deferred is None else bool(deferred)
+        # owner-side step across GPUs (csrc/kernels/sparse_wd_owner.cu): rows never cross a link; the step is
+        # COLLECTIVE (request / serve / loss rounds separated by cross-rank barriers).  Default for synchronous
+        # replicas; for asynchronous workers it turns Hogwild into lockstep rounds of unaveraged updates, so there it
+        # is opt-in (``owner=True`` / B200PS_WD_OWNER=1) — every rank must then take the same number of steps.
+        env = os.environ.get("B200PS_WD_OWNER")
+        self.owner = (None if env is None else env != "0") if owner is None else bool(owner)
         self._bufs: Dict[int, dict] = {}
+        self._own: Dict[int, dict] = {}
 
     def register(self, store) -> None:
         if hasattr(store, "note_untracked_variable"):
@@ -72,7 +79,9 @@ class SparseWideDeep:
         store.register(self.E, (self.features, self.dim), group="sparse", init="normal", stddev=self.stddev)
         store.register(self.W2, (self.dim, 1), group="sparse", init="normal", stddev=self.stddev)
         store.register(self.Bn, (1,), group="fp32", init="zeros")
-        if self.deferred and hasattr(store, "sparse_shard") and store.placement == "flat_shard":
+        self._owner_capable = (hasattr(store, "sparse_shard") and store.placement == "flat_shard" and store.world > 1
+                               and self.owner is not False)
+        if (self.deferred or self._owner_capable) and hasattr(store, "sparse_shard") and store.placement == "flat_shard":
             # GPU store with row sharding only (the pending tables must be sharded exactly like W / E);
             # the gloo path and whole-variable placement apply their updates directly
             store.register(self.P, (self.features, 1), group="sparse", init="zeros", trainable=False)
@@ -104,6 +113,7 @@ class SparseWideDeep:
                 pe, p2 = store.sparse_var(self.P), store.sparse_var(self.P2)
                 self._tab.update(pend_table=pe.table, pend_rows_per_shard=pe.rows_per_shard,
                                  pend2_table=p2.table, pend2_rows_per_shard=p2.rows_per_shard)
+            self._has_pending = self.P in store.sparse
             self._gs0 = tensor_from_ptr(store.gstep.ptrs[0], 8, store.device).view(torch.int64)
         return self._tab
 
@@ -112,7 +122,7 @@ class SparseWideDeep:
         every rank of this process) into their rows of W / E (phase 1, all ranks) and then their slices of w2
         (phase 2), so that every row update used the w2 of before.  A no-op in direct mode."""
         tabs = self._tables(store)
-        if "pend_table" not in tabs:
+        if not getattr(self, "_has_pending", False) or not (self.deferred or getattr(self, "_owner_used", False)):
             return
         ranks = list(store.pool.local_ranks) if ranks is None else list(ranks)
         e, w2 = store.sparse_var(self.E), store.sparse_var(self.W2)
@@ -124,8 +134,87 @@ class SparseWideDeep:
                                     store.sparse_shard(self.E, r), hi - lo, self.dim, w2.table, w2.rows_per_shard,
                                     store.sparse_shard(self.P2, r), store.sparse_shard(self.W2, r), hi2 - lo2, ph)
 
+    # ---- owner-side step (collective): csrc/kernels/sparse_wd_owner.cu
+    def _owner_buffers(self, store, cap: int) -> dict:
+        if cap not in self._own:            # symmetric allocations: every rank gets here on its first (eager) step
+            w, dev = store.world, store.device
+            inbox = store.pool.alloc(f"wd.inbox.{cap}", w * cap * 8)
+            cnt = store.pool.alloc(f"wd.inbox_cnt.{cap}", 4 * max(w, 64))
+            resp = store.pool.alloc(f"wd.resp.{cap}", cap * 8)
+            pb = store.pool.alloc(f"wd.bias_pend.{cap}", 256)
+            g = store._group_of(self.Bn)
+            b_owner = g.layout.owner_of(g.layout.offsets[self.Bn])
+            from ..parallel.symm import tensor_from_ptr
+            self._own[cap] = dict(
+                inbox=inbox, cnt=cnt, resp=resp, bias_pend_buf=pb, bias_owner=b_owner,
+                bias_pend=tensor_from_ptr(pb.ptrs[b_owner], 4, dev).view(torch.float32),
+                t_inbox=ops.device_ptr_table(inbox.ptrs, dev), t_cnt=ops.device_ptr_table(cnt.ptrs, dev),
+                t_resp=ops.device_ptr_table(resp.ptrs, dev),
+                count={r: torch.zeros(w + 1, dtype=torch.int32, device=dev) for r in store.pool.local_ranks})
+        return self._own[cap]
+
+    def _step_owner(self, store, batches: dict, lr: float, sync: bool):
+        """``batches``: {local rank: (row_ptr, fid, fval, labels)}.  Request / serve / loss rounds with the cross-rank
+        barrier kernel in between, then the owners fold the pending coefficients (rows + dw2) and w2."""
+        ranks = list(batches)
+        self._owner_used = True
+        e, w2 = store.sparse_var(self.E), store.sparse_var(self.W2)
+        pe, p2 = store.sparse_var(self.P), store.sparse_var(self.P2)
+        self._tables(store)
+        N = store.world
+        out = {}
+        for r in ranks:
+            row_ptr, fid, fval, labels = batches[r]
+            ob = self._owner_buffers(store, fid.numel())
+            ops.wd_owner_request(row_ptr, fid, world=N, rank=r, cap=fid.numel(), rows_per_shard=e.rows_per_shard,
+                                 features=self.features, inbox_table=ob["t_inbox"], cnt_table=ob["t_cnt"],
+                                 resp_table=ob["t_resp"], count=ob["count"][r])
+        store.barrier()
+        for r in ranks:
+            ob = self._owner_buffers(store, batches[r][1].numel())
+            ops.wd_owner_serve(world=N, rank=r, cap=batches[r][1].numel(), inbox_table=ob["t_inbox"], cnt_table=ob["t_cnt"],
+                               resp_table=ob["t_resp"], emb_local=store.sparse_shard(self.E, r),
+                               wide_local=store.sparse_shard(self.W, r) if self.wide else None, dim=self.dim,
+                               w2_table=w2.table, w2_rows_per_shard=w2.rows_per_shard)
+        store.barrier()
+        for r in ranks:
+            row_ptr, fid, fval, labels = batches[r]
+            ob = self._owner_buffers(store, fid.numel())
+            bufs = self._buffers(labels.numel(), labels.device, r)
+            bufs["loss"].zero_()
+            ops.wd_owner_loss(row_ptr, fid, fval, labels, world=N, rank=r, cap=fid.numel(),
+                              rows_per_shard=e.rows_per_shard, features=self.features, resp_table=ob["t_resp"],
+                              pend_table=pe.table, bias=self._tab["bias"], bias_pend=ob["bias_pend"],
+                              pred=bufs["pred"], loss_sum=bufs["loss"],
+                              global_step=store.global_step_tensor(r) if sync else self._gs0, update=True,
+                              lr=lr / N if sync else lr)
+            out[r] = bufs["loss"]
+        store.barrier()                            # every coefficient has landed in its owner's pending table
+        for ph in (1, 2):
+            for r in ranks:
+                lo, hi = store._sparse_owned(e, r)
+                lo2, hi2 = store._sparse_owned(w2, r)
+                ops.sparse_wd_apply(store.sparse_shard(self.P, r), store.sparse_shard(self.W, r) if self.wide else None,
+                                    store.sparse_shard(self.E, r), hi - lo, self.dim, w2.table, w2.rows_per_shard,
+                                    store.sparse_shard(self.P2, r), store.sparse_shard(self.W2, r), hi2 - lo2, ph,
+                                    pend2_table=p2.table if ph == 1 else None)
+                if ph == 2 and r == ob["bias_owner"]:      # the bias owner folds the round's pending bias update
+                    ops.sparse_wd_apply(None, None, None, 0, self.dim, w2.table, w2.rows_per_shard,
+                                        ob["bias_pend_buf"].view(r, torch.float32), self._tab["bias"], 1, 2)
+            store.barrier()                        # rows used the old w2 everywhere; then w2 is final everywhere
+        return out
+
+    def uses_owner_step(self, store, sync: bool) -> bool:
+        if (not getattr(self, "_owner_capable", False) or store.device.type != "cuda"
+                or len(store.pool.local_ranks) != 1):      # virtual ranks: call _step_owner with every rank's batch
+            return False
+        return True if (sync or self.owner) else False
+
     def step_async(self, store, batch, lr: float, rank: Optional[int] = None):
         """One fused Hogwild step — gather, loss, four scatter-updates, global_step — one launch."""
+        if self.uses_owner_step(store, sync=False):
+            r = store.pool.local_ranks[0] if rank is None else rank
+            return self._step_owner(store, {r: batch}, lr, sync=False)[r]
         row_ptr, fid, fval, labels = batch
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
@@ -136,6 +225,9 @@ class SparseWideDeep:
 
     def step_sync(self, store, batch, lr: float, rank: Optional[int] = None, replicas: Optional[int] = None):
         """Synchronous replicas: all read the same tables (barrier), then the mean gradient is applied."""
+        if self.uses_owner_step(store, sync=True):
+            r = store.pool.local_ranks[0] if rank is None else rank
+            return self._step_owner(store, {r: batch}, lr, sync=True)[r]
         row_ptr, fid, fval, labels = batch
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()

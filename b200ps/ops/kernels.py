@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -358,11 +358,41 @@ def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, em
 
 
 def sparse_wd_apply(pend_local, wide_local, emb_local, rows_local, dim, w2_table, w2_rows_per_shard, pend2_local,
-                    w2_local, w2_rows_local, phase, stream=None):
-    """Owner-side fold of the deferred wide & deep updates (phase 1: rows, phase 2: w2)."""
+                    w2_local, w2_rows_local, phase, pend2_table=None, stream=None):
+    """Owner-side fold of the deferred wide & deep updates (phase 1: rows, phase 2: w2).  ``pend2_table`` (phase 1 of
+    the owner-side step): also accumulate the w2 gradient ``sum_f c_f * E_old[f]`` into the pending w2 vector."""
     check(native.load().b200ps_sparse_wd_apply(ptr(pend_local), ptr(wide_local), ptr(emb_local), rows_local, dim,
                                                ptr(w2_table), w2_rows_per_shard, ptr(pend2_local), ptr(w2_local),
-                                               w2_rows_local, phase, stream_ptr(stream)), "sparse_wd_apply")
+                                               w2_rows_local, phase, ptr(pend2_table), stream_ptr(stream)), "sparse_wd_apply")
+
+
+def wd_owner_request(row_ptr, fid, *, world, rank, cap, rows_per_shard, features, inbox_table, cnt_table, resp_table,
+                     count, stream=None):
+    """Phase 1 of the owner-side wide & deep step: post this rank's row requests (include/b200ps.h)."""
+    check(native.load().b200ps_wd_owner_request(ptr(row_ptr), ptr(fid), row_ptr.numel() - 1, world, rank, cap,
+                                                rows_per_shard, features, ptr(inbox_table), ptr(cnt_table),
+                                                ptr(resp_table), ptr(count), stream_ptr(stream)), "wd_owner_request")
+
+
+def wd_owner_serve(*, world, rank, cap, inbox_table, cnt_table, resp_table, emb_local, wide_local, dim, w2_table,
+                   w2_rows_per_shard, stream=None):
+    """Phase 2: serve the requests in this rank's inbox from its local shards."""
+    check(native.load().b200ps_wd_owner_serve(world, rank, cap, ptr(inbox_table), ptr(cnt_table), ptr(resp_table),
+                                              ptr(emb_local), ptr(wide_local), dim, ptr(w2_table), w2_rows_per_shard,
+                                              stream_ptr(stream)), "wd_owner_serve")
+
+
+def wd_owner_loss(row_ptr, fid, fval, labels, *, world, rank, cap, rows_per_shard, features, resp_table, pend_table,
+                  bias, bias_pend=None, pred=None, dz_out=None, loss_sum=None, global_step=None, update=True, lr=0.0, grad_scale=None,
+                  loss_scale=None, stream=None):
+    """Phase 3: loss / dz from the response array and the scalar coefficients into the owners' pending table."""
+    B = labels.numel()
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    check(native.load().b200ps_wd_owner_loss(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), B, world, rank, cap,
+                                             rows_per_shard, features, ptr(resp_table), ptr(pend_table), ptr(bias),
+                                             ptr(bias_pend), ptr(pred), ptr(dz_out), ptr(loss_sum), ptr(global_step), int(update), lr,
+                                             gs, ls, stream_ptr(stream)), "wd_owner_loss")
 
 
 def auc_hist(pred, labels, thresholds, hist_pos, hist_neg, stream=None):

@@ -622,10 +622,11 @@ class SparseWideDeepTrainer(SparseLRTrainer):
 
     def __init__(self, ctx, features: int, dim: int = 128, wide: bool = True, lr: float = 0.001,
                  mode: str = "async", placement: str = "flat_shard", seed: int = 1, use_graph: bool = True,
-                 deferred: Optional[bool] = None):
+                 deferred: Optional[bool] = None, owner: Optional[bool] = None):
         from .models.wide_deep import SparseWideDeep
         super().__init__(ctx, features, lr=lr, mode=mode, placement=placement, seed=seed, use_graph=use_graph,
-                         model=SparseWideDeep(features, dim=dim, wide=wide, deferred=deferred))
+                         model=SparseWideDeep(features, dim=dim, wide=wide, deferred=deferred, owner=owner))
+        self.owner_step = self.model.uses_owner_step(self.store, sync=(mode == "sync"))
 
     def flush(self) -> None:
         """Fold pending (deferred) updates of this process's shards into the tables — before checkpoints and

@@ -379,7 +379,10 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     from b200ps.train import SparseLRTrainer, SparseWideDeepTrainer
     F, B, nnz, spread = (1 << 22 if deep_dim else 1 << 24), args.sparse_batch, 100, 20
     if deep_dim:
-        tr = SparseWideDeepTrainer(ctx, features=F, dim=deep_dim, lr=0.05, mode=mode)
+        # across GPUs: owner-side rows (request / serve / loss rounds, no embedding row crosses a link); the
+        # asynchronous updates are then applied in lockstep rounds (unaveraged, every worker's update lands)
+        tr = SparseWideDeepTrainer(ctx, features=F, dim=deep_dim, lr=0.05, mode=mode,
+                                   owner=(ctx.world > 1 and os.environ.get("B200PS_WD_OWNER", "1") != "0"))
     else:
         tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
     dev = ctx.device
@@ -438,7 +441,8 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
         "row_traffic_GBps_per_gpu": (2 * nnz * B * 4 * max(deep_dim, 1) / (ms / args.steps / 1e3) / 1e9),
         "config": {"model": (f"sparse_wide_deep_2^22_features_dim{deep_dim}_~100nnz" if deep_dim
                              else "sparse_lr_2^24_features_~100nnz"), "global_batch": B * ctx.world,
-                   "per_gpu_batch": B, "mode": mode, "parallelism": f"dp{ctx.world}+row_shard{ctx.world}",
+                   "per_gpu_batch": B, "mode": mode + (" (lockstep rounds, owner-side rows)" if getattr(tr, "owner_step", False) else ""),
+                   "parallelism": f"dp{ctx.world}+row_shard{ctx.world}",
                    "inputs": (f"ring of {ring} device CSR batches; {F * max(deep_dim, 1) * 4 >> 20} MB table, random rows")},
     }
 

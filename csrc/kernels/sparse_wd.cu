@@ -226,15 +226,20 @@ __global__ void __launch_bounds__(kWdThreads) sparse_wd_kernel(const WdParams p)
 // Owner-side fold of the pending coefficients (deferred mode).  phase 1: rows of this rank's shard;
 // phase 2: this rank's slice of w2.  One lane looks at one row of P; the warp then visits the touched rows
 // of its 32 together (ballot), every lane updating 4 columns of each 128-column chunk.
+// With `pend2` (owner-side step, sparse_wd_owner.cu) the fold also accumulates the gradient of w2 that the workers
+// could not form (they never saw the rows): dw2 = sum_f c_f * E_old[f], added into the pending w2 vector.
 template <int NCH>
 __global__ void __launch_bounds__(256) sparse_wd_apply_kernel(float* __restrict__ pend, float* __restrict__ wide,
                                                               float* __restrict__ emb, long long rows,
-                                                              const ShardedTable w2) {
+                                                              const ShardedTable w2, const ShardedTable pend2) {
   constexpr int D = 128 * NCH;
   const int lane = threadIdx.x & 31;
-  float4 w2r[NCH];
+  float4 w2r[NCH], g2[NCH];
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) w2r[c] = ldcg4(w2.row((c * 32 + lane) * 4, 1));
+  for (int c = 0; c < NCH; ++c) {
+    w2r[c] = ldcg4(w2.row((c * 32 + lane) * 4, 1));
+    g2[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
   // 128 rows of P per warp iteration (one float4 per lane): the scan is a plain streaming read, ~1 % of the
@@ -268,11 +273,26 @@ __global__ void __launch_bounds__(256) sparse_wd_apply_kernel(float* __restrict_
         for (int ch = 0; ch < NCH; ++ch) {
           float4* q = reinterpret_cast<float4*>(row + (ch * 32 + lane) * 4);
           float4 e = *q;
+          g2[ch].x = fmaf(cv, e.x, g2[ch].x); g2[ch].y = fmaf(cv, e.y, g2[ch].y);
+          g2[ch].z = fmaf(cv, e.z, g2[ch].z); g2[ch].w = fmaf(cv, e.w, g2[ch].w);
           e.x = fmaf(cv, w2r[ch].x, e.x); e.y = fmaf(cv, w2r[ch].y, e.y);
           e.z = fmaf(cv, w2r[ch].z, e.z); e.w = fmaf(cv, w2r[ch].w, e.w);
           *q = e;
         }
       }
+    }
+  }
+  if (pend2.shards) {                  // one red per column per CTA into the owners of the pending w2 vector
+    __shared__ float s_g2[8][D];
+    const int wic = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) *reinterpret_cast<float4*>(&s_g2[wic][(c * 32 + lane) * 4]) = g2[c];
+    __syncthreads();
+    for (int col = threadIdx.x; col < D; col += 256) {
+      float g = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) g += s_g2[w][col];
+      if (g != 0.f) red_add_f32_sys(pend2.row(col, 1), g);
     }
   }
 }
@@ -344,17 +364,18 @@ extern "C" int b200ps_sparse_wd(const int32_t* row_ptr, const int64_t* fid, cons
 extern "C" int b200ps_sparse_wd_apply(float* pend_local, float* wide_local, float* emb_local, int64_t rows_local,
                                       int32_t dim, float* const* w2_shards, int64_t w2_rows_per_shard,
                                       float* pend2_local, float* w2_local, int64_t w2_rows_local, int32_t phase,
-                                      b200ps_stream_t stream) {
+                                      float* const* pend2_shards, b200ps_stream_t stream) {
   B200PS_REQUIRE(dim == 128 || dim == 256 || dim == 512, "sparse_wd_apply: dim must be 128, 256 or 512");
   cudaStream_t s = as_stream(stream);
   if (phase == 1) {
     if (rows_local <= 0) return 0;
     B200PS_REQUIRE(pend_local && emb_local && w2_shards && w2_rows_per_shard > 0, "sparse_wd_apply: bad arguments");
     const ShardedTable w2 = make_table(w2_shards, w2_rows_per_shard);
+    const ShardedTable p2 = make_table(pend2_shards, w2_rows_per_shard);   // null shards: no w2-gradient accumulation
     const int ctas = (int)std::min<long long>((rows_local + 1023) / 1024, (long long)sm_count() * 8);
-    if (dim == 128) sparse_wd_apply_kernel<1><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2);
-    else if (dim == 256) sparse_wd_apply_kernel<2><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2);
-    else sparse_wd_apply_kernel<4><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2);
+    if (dim == 128) sparse_wd_apply_kernel<1><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2, p2);
+    else if (dim == 256) sparse_wd_apply_kernel<2><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2, p2);
+    else sparse_wd_apply_kernel<4><<<ctas, 256, 0, s>>>(pend_local, wide_local, emb_local, rows_local, w2, p2);
   } else {
     if (w2_rows_local <= 0) return 0;
     B200PS_REQUIRE(pend2_local && w2_local, "sparse_wd_apply: bad arguments");

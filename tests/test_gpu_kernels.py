@@ -612,3 +612,50 @@ def test_workspace_refuses_overlapping_streams(native_lib):
     with torch.cuda.stream(sb):
         ops.mlp_tail(z2, b1, w2, b2, labels, **kw)          # stream A has finished: fine
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("world,dim,wide,sync", [(4, 128, True, True), (2, 256, False, False), (8, 128, True, False)])
+def test_wide_deep_owner_side_step_matches_float64_reference(native_lib, world, dim, wide, sync):
+    """K4o/K5o on virtual ranks (all ranks of each phase on one GPU): request / serve / loss / fold rounds leave the
+    tables where the float64 oracle puts them — sync: mean of the replicas' gradients; async rounds: their sum."""
+    from b200ps import ops
+    from b200ps.models.wide_deep import SparseWideDeep, wide_deep_reference
+    from b200ps.parallel.context import init_from_env
+    from b200ps.ps.store import ParameterStore
+    ctx = init_from_env(virtual_world=world)
+    F, B = 1 << 13, 120
+    store = ParameterStore(ctx.pool)
+    model = SparseWideDeep(F, dim=dim, wide=wide, stddev=0.1, owner=True)
+    model.register(store)
+    store.build(); store.initialize()
+    init = {k: v.clone() for k, v in store.state_dict().items()}
+    batches = {r: _sparse_batch(B=B, nnz=30, spread=8, F=F, seed=40 + r) for r in range(world)}
+    lr = 0.5
+    losses = model._step_owner(store, batches, lr, sync=sync)
+    torch.cuda.synchronize()
+    got = store.state_dict()
+    W0 = init[model.W].reshape(-1) if wide else None
+    E0, w20, b0 = init[model.E], init[model.W2].reshape(-1), init[model.Bn].reshape(())
+    acc = {"E": torch.zeros_like(E0, dtype=torch.float64), "w2": torch.zeros(dim, dtype=torch.float64), "b": 0.0,
+           "W": torch.zeros(F, dtype=torch.float64)}
+    for r in range(world):
+        rp, fid, fv, y = (t.cpu() for t in batches[r])
+        loss_ref, _, gr = wide_deep_reference(W0, E0, w20, b0, rp, fid, fv, y)
+        assert abs(losses[r].item() - loss_ref.item()) < 2e-5
+        for k in gr:
+            acc[k] = acc[k] + gr[k]
+    scale = lr / world if sync else lr
+    assert (got[model.E].double() - (E0.double() - scale * acc["E"])).abs().max().item() < 2e-5
+    assert (got[model.W2].reshape(-1).double() - (w20.double() - scale * acc["w2"])).abs().max().item() < 5e-5
+    if wide:
+        assert (got[model.W].reshape(-1).double() - (W0.double() - scale * acc["W"])).abs().max().item() < 2e-5
+    assert abs(got[model.Bn].item() - (b0.item() - scale * float(acc["b"]))) < 2e-5
+    assert store.sparse_shard(model.P, 0).abs().sum().item() == 0.0          # pending table folded and cleared
+    assert store.global_step == (1 if sync else world)
+    # a second round from the updated tables still agrees with the oracle's loss at those tables
+    losses2 = model._step_owner(store, batches, lr, sync=sync)
+    torch.cuda.synchronize()
+    rp, fid, fv, y = (t.cpu() for t in batches[0])
+    l2, _, _ = wide_deep_reference(got[model.W].reshape(-1) if wide else None, got[model.E], got[model.W2].reshape(-1),
+                                   got[model.Bn].reshape(()), rp, fid, fv, y, train=False)
+    assert abs(losses2[0].item() - l2.item()) < 2e-5
