@@ -190,19 +190,27 @@ class SparseWideDeep:
                               lr=lr / N if sync else lr)
             out[r] = bufs["loss"]
         store.barrier()                            # every coefficient has landed in its owner's pending table
-        for ph in (1, 2):
-            for r in ranks:
-                lo, hi = store._sparse_owned(e, r)
-                lo2, hi2 = store._sparse_owned(w2, r)
-                ops.sparse_wd_apply(store.sparse_shard(self.P, r), store.sparse_shard(self.W, r) if self.wide else None,
-                                    store.sparse_shard(self.E, r), hi - lo, self.dim, w2.table, w2.rows_per_shard,
-                                    store.sparse_shard(self.P2, r), store.sparse_shard(self.W2, r), hi2 - lo2, ph,
-                                    pend2_table=p2.table if ph == 1 else None)
-                if ph == 2 and r == ob["bias_owner"]:      # the bias owner folds the round's pending bias update
+        for r in ranks:                            # rows: driven by the inbox (the rows requested this round)
+            ob = self._owner_buffers(store, batches[r][1].numel())
+            ops.wd_owner_fold(world=N, rank=r, cap=batches[r][1].numel(), inbox_table=ob["t_inbox"], cnt_table=ob["t_cnt"],
+                              pend_local=store.sparse_shard(self.P, r), emb_local=store.sparse_shard(self.E, r),
+                              wide_local=store.sparse_shard(self.W, r) if self.wide else None, dim=self.dim,
+                              w2_table=w2.table, pend2_table=p2.table, w2_rows_per_shard=w2.rows_per_shard)
+        store.barrier()                            # every row used the old w2; every dw2 partial has landed
+        self._fold_small(store, ranks)             # w2 and the bias; the next round's first barrier publishes them
+        return out
+
+    def _fold_small(self, store, ranks) -> None:
+        """Owner-side step: fold the pending w2 vector (every rank its slice) and the pending bias (its owner)."""
+        w2 = store.sparse_var(self.W2)
+        for r in ranks:
+            lo2, hi2 = store._sparse_owned(w2, r)
+            ops.sparse_wd_apply(None, None, None, 0, self.dim, w2.table, w2.rows_per_shard,
+                                store.sparse_shard(self.P2, r), store.sparse_shard(self.W2, r), hi2 - lo2, 2)
+            for ob in self._own.values():
+                if r == ob["bias_owner"]:
                     ops.sparse_wd_apply(None, None, None, 0, self.dim, w2.table, w2.rows_per_shard,
                                         ob["bias_pend_buf"].view(r, torch.float32), self._tab["bias"], 1, 2)
-            store.barrier()                        # rows used the old w2 everywhere; then w2 is final everywhere
-        return out
 
     def uses_owner_step(self, store, sync: bool) -> bool:
         if (not getattr(self, "_owner_capable", False) or store.device.type != "cuda"

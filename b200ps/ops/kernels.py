@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "wd_owner_fold", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -380,6 +380,14 @@ def wd_owner_serve(*, world, rank, cap, inbox_table, cnt_table, resp_table, emb_
     check(native.load().b200ps_wd_owner_serve(world, rank, cap, ptr(inbox_table), ptr(cnt_table), ptr(resp_table),
                                               ptr(emb_local), ptr(wide_local), dim, ptr(w2_table), w2_rows_per_shard,
                                               stream_ptr(stream)), "wd_owner_serve")
+
+
+def wd_owner_fold(*, world, rank, cap, inbox_table, cnt_table, pend_local, emb_local, wide_local, dim, w2_table,
+                  pend2_table, w2_rows_per_shard, stream=None):
+    """Phase 4: fold the round's coefficients into this rank's rows (inbox-driven) and dw2 into the pending w2."""
+    check(native.load().b200ps_wd_owner_fold(world, rank, cap, ptr(inbox_table), ptr(cnt_table), ptr(pend_local),
+                                             ptr(emb_local), ptr(wide_local), dim, ptr(w2_table), ptr(pend2_table),
+                                             w2_rows_per_shard, stream_ptr(stream)), "wd_owner_fold")
 
 
 def wd_owner_loss(row_ptr, fid, fval, labels, *, world, rank, cap, rows_per_shard, features, resp_table, pend_table,

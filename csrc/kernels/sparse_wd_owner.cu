@@ -115,35 +115,46 @@ __global__ void __launch_bounds__(kOwnThreads) wd_serve_kernel(const OwnerParams
   const unsigned total = s_pref[p.world];
   const uint2* inbox = p.inbox[p.rank];
   const unsigned warp = (blockIdx.x * kOwnThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kOwnThreads) >> 5;
-  constexpr int FL = 4;                               // rows in flight per warp
-  for (unsigned t0 = warp * FL; t0 < total; t0 += nwarps * FL) {
-    uint2 rq[FL];
-    int src[FL];
-    float4 e[FL][NCH];
+  constexpr int FL = NCH == 1 ? 8 : 4;                // rows in flight per warp
+  // A warp takes 32 consecutive requests: lane l fetches request l (one coalesced load for the chunk — a row load
+  // per request behind its own dependent request load would serialise 8 L2 latencies), the rows are then visited
+  // FL at a time, and lane l finally posts the answer of request l (32 stores in one instruction).
+  for (unsigned t0 = warp * 32; t0 < total; t0 += nwarps * 32) {
+    const unsigned t = t0 + lane;
+    uint2 rq = make_uint2(0u, 0u);
+    int src = -1;
+    if (t < total) {
+      int r = 0;
+      while (t >= s_pref[r + 1]) ++r;
+      src = r;
+      rq = __ldcg(inbox + (size_t)r * p.cap + (t - s_pref[r]));
+    }
+    const int n = (int)min(32u, total - t0);
+    float mine = 0.f;
+    for (int k0 = 0; k0 < n; k0 += FL) {
+      float4 e[FL][NCH];
 #pragma unroll
-    for (int u = 0; u < FL; ++u) {
-      const unsigned t = t0 + u;
-      src[u] = -1;
-      if (t < total) {
-        int r = 0;
-        while (t >= s_pref[r + 1]) ++r;
-        src[u] = r;
-        rq[u] = __ldcg(inbox + (size_t)r * p.cap + (t - s_pref[r]));
-        const float* row = emb + (size_t)rq[u].x * D;
+      for (int u = 0; u < FL; ++u) {
+        const unsigned row = __shfl_sync(0xffffffffu, rq.x, (k0 + u) & 31);
+        if (k0 + u < n) {
+          const float* rp = emb + (size_t)row * D;
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) e[u][c] = __ldcg(reinterpret_cast<const float4*>(row + (c * 32 + lane) * 4));
+          for (int c = 0; c < NCH; ++c) e[u][c] = __ldcg(reinterpret_cast<const float4*>(rp + (c * 32 + lane) * 4));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < FL; ++u) {
+        float part = 0.f;
+        if (k0 + u < n) {
+#pragma unroll
+          for (int c = 0; c < NCH; ++c)
+            part += e[u][c].x * w2r[c].x + e[u][c].y * w2r[c].y + e[u][c].z * w2r[c].z + e[u][c].w * w2r[c].w;
+        }
+        const float sdot = warp_sum(part);
+        if (lane == k0 + u) mine = sdot;
       }
     }
-#pragma unroll
-    for (int u = 0; u < FL; ++u) {
-      if (src[u] < 0) continue;                       // warp-uniform
-      float part = 0.f;
-#pragma unroll
-      for (int c = 0; c < NCH; ++c)
-        part += e[u][c].x * w2r[c].x + e[u][c].y * w2r[c].y + e[u][c].z * w2r[c].z + e[u][c].w * w2r[c].w;
-      const float s = warp_sum(part);
-      if (lane == 0) p.resp[src[u]][rq[u].y] = make_float2(s, wide ? __ldcg(wide + rq[u].x) : 0.f);
-    }
+    if (src >= 0) p.resp[src][rq.y] = make_float2(mine, wide ? __ldcg(wide + rq.x) : 0.f);
   }
 }
 
@@ -207,6 +218,93 @@ __global__ void __launch_bounds__(kOwnThreads) wd_loss_kernel(const OwnerParams 
       red_add_f32_sys(q.bias_pend ? q.bias_pend : q.bias, -q.lr * d);
       if (blockIdx.x == 0 && q.global_step) atomicAdd_system(q.global_step, 1ull);
     }
+  }
+}
+
+// ---- phase 4: the owner folds the round's coefficients into its rows — driven by the inbox (exactly the rows
+// that were requested this round), not by a scan of the whole pending table.  The first visitor of a row claims its
+// coefficient (local atomicExch; later duplicates read 0 and skip): W[row] += c, dw2 += c * E_old[row],
+// E[row] += c * w2.  One red per column per CTA adds dw2 into the pending w2 vector.
+template <int NCH>
+__global__ void __launch_bounds__(kOwnThreads) wd_fold_kernel(const OwnerParams p, float* __restrict__ pend,
+                                                             float* __restrict__ emb, float* __restrict__ wide,
+                                                             float* const* w2_shards, float* const* pend2_shards,
+                                                             int64_t w2_rows_per_shard) {
+  constexpr int D = 128 * NCH;
+  __shared__ float s_g2[kOwnThreads / 32][D];
+  __shared__ unsigned s_pref[kMaxWorldOwn + 1];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  float4 w2r[NCH], g2[NCH];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int col = (c * 32 + lane) * 4;
+    w2r[c] = __ldcg(reinterpret_cast<const float4*>(w2_shards[col / w2_rows_per_shard] + col % w2_rows_per_shard));
+    g2[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (threadIdx.x == 0) {
+    unsigned acc = 0;
+    for (int r = 0; r < p.world; ++r) { s_pref[r] = acc; acc += __ldcg(p.inbox_cnt[p.rank] + r); }
+    s_pref[p.world] = acc;
+  }
+  __syncthreads();
+  const unsigned total = s_pref[p.world];
+  const uint2* inbox = p.inbox[p.rank];
+  const unsigned warp = (blockIdx.x * kOwnThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kOwnThreads) >> 5;
+  constexpr int FL = 4;
+  for (unsigned t0 = warp * 32; t0 < total; t0 += nwarps * 32) {     // lane l claims the row of request l
+    const unsigned t = t0 + lane;
+    unsigned row = 0;
+    float cmine = 0.f;
+    if (t < total) {
+      int r = 0;
+      while (t >= s_pref[r + 1]) ++r;
+      row = __ldcg(inbox + (size_t)r * p.cap + (t - s_pref[r])).x;
+      cmine = atomicExch(pend + row, 0.f);                            // duplicates of a row read 0 and skip
+      if (wide && cmine != 0.f) wide[row] += cmine;
+    }
+    unsigned live = __ballot_sync(0xffffffffu, cmine != 0.f);
+    while (live) {
+      unsigned rows[FL];
+      float cv[FL];
+      float4 e[FL][NCH];
+#pragma unroll
+      for (int u = 0; u < FL; ++u) {
+        cv[u] = 0.f;
+        rows[u] = 0;
+        if (live) {
+          const int srcl = __ffs(live) - 1;
+          live &= live - 1;
+          rows[u] = __shfl_sync(0xffffffffu, row, srcl);
+          cv[u] = __shfl_sync(0xffffffffu, cmine, srcl);
+          const float* er = emb + (size_t)rows[u] * D;
+#pragma unroll
+          for (int c = 0; c < NCH; ++c) e[u][c] = *reinterpret_cast<const float4*>(er + (c * 32 + lane) * 4);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < FL; ++u) {
+        if (cv[u] == 0.f) continue;                                    // warp-uniform
+        float* er = emb + (size_t)rows[u] * D;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float4 v = e[u][c];
+          g2[c].x = fmaf(cv[u], v.x, g2[c].x); g2[c].y = fmaf(cv[u], v.y, g2[c].y);
+          g2[c].z = fmaf(cv[u], v.z, g2[c].z); g2[c].w = fmaf(cv[u], v.w, g2[c].w);
+          v.x = fmaf(cv[u], w2r[c].x, v.x); v.y = fmaf(cv[u], w2r[c].y, v.y);
+          v.z = fmaf(cv[u], w2r[c].z, v.z); v.w = fmaf(cv[u], w2r[c].w, v.w);
+          *reinterpret_cast<float4*>(er + (c * 32 + lane) * 4) = v;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) *reinterpret_cast<float4*>(&s_g2[wic][(c * 32 + lane) * 4]) = g2[c];
+  __syncthreads();
+  for (int col = threadIdx.x; col < D; col += kOwnThreads) {
+    float g = 0.f;
+#pragma unroll
+    for (int w = 0; w < kOwnThreads / 32; ++w) g += s_g2[w][col];
+    if (g != 0.f) red_add_f32_sys(pend2_shards[col / w2_rows_per_shard] + col % w2_rows_per_shard, g);
   }
 }
 
@@ -295,6 +393,30 @@ extern "C" int b200ps_wd_owner_loss(const int32_t* row_ptr, const int64_t* fid, 
   const int wpc = kOwnThreads / 32;
   const int ctas = std::min((B + wpc - 1) / wpc, sm_count() * 4);
   wd_loss_kernel<<<ctas, kOwnThreads, 0, as_stream(stream)>>>(p, q);
+  B200PS_LAUNCH_CHECK();
+  return 0;
+}
+
+// phase 4: fold the round's coefficients into this rank's rows, driven by its inbox (the rows requested this round);
+// adds dw2 into the pending w2 vector (pend2_shards, sharded like w2).  After a barrier, b200ps_sparse_wd_apply
+// phase 2 folds the pending w2 vector.
+extern "C" int b200ps_wd_owner_fold(int32_t world, int32_t rank, int32_t cap, void* const* inbox, uint32_t* const* inbox_cnt,
+                                    float* pend_local, float* emb_local, float* wide_local, int32_t dim,
+                                    float* const* w2_shards, float* const* pend2_shards, int64_t w2_rows_per_shard,
+                                    b200ps_stream_t stream) {
+  B200PS_REQUIRE(world >= 1 && world <= kMaxWorldOwn && rank >= 0 && rank < world && cap > 0 && inbox && inbox_cnt &&
+                     pend_local && emb_local && w2_shards && pend2_shards && w2_rows_per_shard > 0 && w2_rows_per_shard % 4 == 0,
+                 "wd_owner_fold: bad arguments");
+  B200PS_REQUIRE(dim == 128 || dim == 256 || dim == 512, "wd_owner_fold: dim must be 128, 256 or 512");
+  OwnerParams p{};
+  p.world = world; p.rank = rank; p.cap = cap;
+  p.inbox = reinterpret_cast<uint2* const*>(inbox);
+  p.inbox_cnt = reinterpret_cast<unsigned int* const*>(inbox_cnt);
+  const int ctas = sm_count() * 2;
+  cudaStream_t s = as_stream(stream);
+  if (dim == 128) wd_fold_kernel<1><<<ctas, kOwnThreads, 0, s>>>(p, pend_local, emb_local, wide_local, w2_shards, pend2_shards, w2_rows_per_shard);
+  else if (dim == 256) wd_fold_kernel<2><<<ctas, kOwnThreads, 0, s>>>(p, pend_local, emb_local, wide_local, w2_shards, pend2_shards, w2_rows_per_shard);
+  else wd_fold_kernel<4><<<ctas, kOwnThreads, 0, s>>>(p, pend_local, emb_local, wide_local, w2_shards, pend2_shards, w2_rows_per_shard);
   B200PS_LAUNCH_CHECK();
   return 0;
 }

@@ -302,6 +302,9 @@ int b200ps_wd_owner_request(const int32_t* row_ptr, const int64_t* fid, int32_t 
 int b200ps_wd_owner_serve(int32_t world, int32_t rank, int32_t cap, void* const* inbox, uint32_t* const* inbox_cnt,
                           void* const* resp, const float* emb_local, const float* wide_local, int32_t dim,
                           float* const* w2_shards, int64_t w2_rows_per_shard, b200ps_stream_t stream);
+int b200ps_wd_owner_fold(int32_t world, int32_t rank, int32_t cap, void* const* inbox, uint32_t* const* inbox_cnt,
+                         float* pend_local, float* emb_local, float* wide_local, int32_t dim, float* const* w2_shards,
+                         float* const* pend2_shards, int64_t w2_rows_per_shard, b200ps_stream_t stream);
 int b200ps_wd_owner_loss(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels, int32_t B,
                          int32_t world, int32_t rank, int32_t cap, int64_t rows_per_shard, int64_t features,
                          void* const* resp, float* const* pend_shards, float* bias, float* bias_pend /* pending bias

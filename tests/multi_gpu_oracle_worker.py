@@ -174,6 +174,43 @@ def main():
         res[f"nvls_{tag}_replicas_identical"] = len(set(allw)) == 1
         del sn
         ctx.control_barrier()
+    # ---- 6. sparse wide & deep, synchronous, owner-side rows (request / serve / loss / fold rounds): table VALUES
+    #         after 3 steps against the float64 oracle (mean of the replicas' gradients per step)
+    from b200ps.models.wide_deep import wide_deep_reference
+    from b200ps.train import SparseWideDeepTrainer
+    FW, BW = 1 << 13, 160
+    tw = SparseWideDeepTrainer(ctx, features=FW, dim=128, lr=0.5, mode="sync", use_graph=False)
+    res["wd_owner_step"] = bool(tw.owner_step)
+    mw = tw.model
+    w_init = {k: v.clone() for k, v in tw.store.state_dict().items()}
+    wb = []
+    for r in range(world):
+        rp = torch.empty(BW + 1, device=dev, dtype=torch.int32); fid = torch.empty(BW * 40, device=dev, dtype=torch.int64)
+        fv = torch.empty(BW * 40, device=dev); yy = torch.empty(BW, device=dev)
+        ops.synth_sparse(rp, fid, fv, yy, nnz_mean=32, spread=8, features=FW, seed=17, offset=r * BW)
+        wb.append((rp, fid, fv, yy))
+    for _ in range(3):
+        tw.step(wb[rank])
+    torch.cuda.synchronize(); ctx.control_barrier()
+    got_w = tw.store.state_dict()
+    if rank == 0:
+        W = w_init[mw.W].double().reshape(-1); E = w_init[mw.E].double(); w2v = w_init[mw.W2].double().reshape(-1)
+        bb = w_init[mw.Bn].double().reshape(())
+        cpu = [tuple(t.cpu() for t in b) for b in wb]
+        for _ in range(3):
+            acc = None
+            for r in range(world):
+                _, _, gr = wide_deep_reference(W, E, w2v, bb, *cpu[r])
+                acc = gr if acc is None else {k: acc[k] + gr[k] for k in gr}
+            W = W - 0.5 / world * acc["W"]; E = E - 0.5 / world * acc["E"]
+            w2v = w2v - 0.5 / world * acc["w2"]; bb = bb - 0.5 / world * acc["b"]
+        res["wd_sync_E_err"] = float((got_w[mw.E].double() - E).abs().max())
+        res["wd_sync_W_err"] = float((got_w[mw.W].double().reshape(-1) - W).abs().max())
+        res["wd_sync_w2_err"] = float((got_w[mw.W2].double().reshape(-1) - w2v).abs().max())
+        res["wd_sync_b_err"] = float((got_w[mw.Bn].double().reshape(()) - bb).abs())
+        res["wd_sync_global_step"] = tw.global_step
+    ctx.control_barrier()
+    del tw
     if rank == 0:
         json.dump(res, open(os.path.join(out_dir, "oracle_result.json"), "w"))
     print("rank", rank, json.dumps(res), flush=True)

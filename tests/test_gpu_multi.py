@@ -100,6 +100,9 @@ def test_multi_gpu_results_match_independent_oracles(native_lib, tmp_path):
     assert res["nvls_bf16_master_err"] < 2e-2 and res["nvls_bf16_work_err"] < 2e-2 and res["nvls_bf16_pull_err"] < 2e-2, res
     assert res["nvls_f32_replicas_identical"] and res["nvls_bf16_replicas_identical"], res
     assert res["nvls_f32_global_step"] == 3 and res["nvls_bf16_global_step"] == 3, res
+    # wide & deep, synchronous, owner-side rows: no embedding row crossed a link, the tables match the oracle
+    assert res["wd_owner_step"] and res["wd_sync_global_step"] == 3, res
+    assert max(res["wd_sync_E_err"], res["wd_sync_W_err"], res["wd_sync_b_err"]) < 2e-5 and res["wd_sync_w2_err"] < 1e-4, res
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
