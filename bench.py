@@ -379,10 +379,11 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     from b200ps.train import SparseLRTrainer, SparseWideDeepTrainer
     F, B, nnz, spread = (1 << 22 if deep_dim else 1 << 24), args.sparse_batch, 100, 20
     if deep_dim:
-        # across GPUs: owner-side rows (request / serve / loss rounds, no embedding row crosses a link); the
-        # asynchronous updates are then applied in lockstep rounds (unaveraged, every worker's update lands)
+        # from 4 GPUs on: owner-side rows (request / serve / loss rounds, no embedding row crosses a link; measured
+        # 121 vs 115 us/step on 2 GPUs, 182 vs 399 on 8); the asynchronous updates are then applied in lockstep rounds
+        # (unaveraged, every worker's update lands)
         tr = SparseWideDeepTrainer(ctx, features=F, dim=deep_dim, lr=0.05, mode=mode,
-                                   owner=(ctx.world > 1 and os.environ.get("B200PS_WD_OWNER", "1") != "0"))
+                                   owner=(ctx.world >= 4 and os.environ.get("B200PS_WD_OWNER", "1") != "0"))
     else:
         tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
     dev = ctx.device
