@@ -22,3 +22,9 @@ python tools/profile_step.py --config wd --steps 6 > gpurun_out/plain_wd2.log 2>
 ncu --set full --clock-control none --import-source on -k regex:'sparse_wd' -s 2 -c 2 -o gpurun_out/prof_wd -f python tools/profile_step.py --config wd --steps 6 > gpurun_out/ncu_wd.log 2>&1
 echo "ncu wd: $?"
 ls -la gpurun_out/*.ncu-rep
+python tools/prof_wd_owner.py > gpurun_out/plain_wd_owner.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'wd_' -s 15 -c 5 -o gpurun_out/prof_wd_owner -f python tools/prof_wd_owner.py > gpurun_out/ncu_wd_owner.log 2>&1
+echo "ncu wd owner: $?"
+python tools/prof_cluster.py > gpurun_out/plain_cluster.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'mlp_cluster' -s 2 -c 1 -o gpurun_out/prof_cluster -f python tools/prof_cluster.py > gpurun_out/ncu_cluster.log 2>&1
+echo "ncu cluster: $?"

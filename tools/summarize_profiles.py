@@ -60,10 +60,15 @@ def main():
           "All captures: `ncu --set full --clock-control none --import-source on` on ONE GPU, after the same command "
           "had exited 0 without ncu (`tools/gpu_profiles.sh`).  Durations under ncu are cold-cache and serialised: "
           "compare shares, not absolutes; the timed numbers are the CUDA-event ones in `bench_*.json`.",
-          "`compute-sanitizer` is closed on this pool (the tool answered so; `gpurun_out/sanitizer_memcheck.log`), "
+          "`compute-sanitizer` is closed on this pool (the tool answered so; `profiles/sanitizer_refusal.log`), "
           "so memory safety rests on the bounded-wait traps, shape/alignment checks and the reference-comparison tests.",
-          "The launch lists of `mnist` and `wd` predate the last tuning step of their kernels (their ncu captures do not).  The bench JSON files are from the final tree.", ""]
-    for cfg in ("mnist", "mnist_chain", "wide", "sparse", "wd"):
+          "Round 2: every capture below was retaken on the final tree (`cluster` = the opt-in resident-cluster step K14, "
+          "50 steps per launch; `wd_owner` = the owner-side wide & deep phases on 2 virtual ranks of one GPU).  Other "
+          "evidence here: `bench_{b200ps,baseline}_n{1,2,4,8}_r2.json` (both arms, same box, back to back), "
+          "`pushpull_sweep_n{2,8}_r2.json`, `ncu_cluster.txt`, `cluster_probe.txt`, `multi_gpu/` (2- and 8-GPU test logs: "
+          "oracle comparisons, dead-rank detection, skew stress on the checked build), `sanitizer_refusal.log`, "
+          "`EXPERIMENTS.md`.", ""]
+    for cfg in ("mnist", "mnist_chain", "cluster", "wide", "sparse", "wd", "wd_owner"):
         rep = os.path.join(GP, f"prof_{cfg}.ncu-rep")
         if os.path.exists(rep):
             rows = ncu_raw(rep)
@@ -94,11 +99,12 @@ def main():
             json.dump(rows, open(os.path.join(OUT, f), "w"), indent=1)
             n = rows[0]["n_gpus"]
             md += [f"## push/pull sweep, {n} GPUs (`bench/pushpull_sweep.py`; us = CUDA events, max over ranks)", "",
-                   "| bytes | push_sync us | NCCL rs+add+ag us | pull us | NCCL all_gather us | push_async us | NCCL rs+add us | "
-                   "push_sync GB/s/dir | fraction of 770 GB/s |", "|---|---|---|---|---|---|---|---|---|"]
+                   "| bytes | push path | push_sync us | push P2P us | push NVLS us | NCCL rs+add+ag us | pull us | pull NVLS us | "
+                   "NCCL all_gather us | push_async us | NCCL rs+add us |", "|---|---|---|---|---|---|---|---|---|---|---|"]
             for r in rows:
-                md.append(f"| {r['bytes']} | {r['push_sync_us']} | {r['nccl_push_us']} | {r['pull_us']} | {r['nccl_allgather_us']} | "
-                          f"{r['push_async_us']} | {r['nccl_rs_apply_us']} | {r['push_sync_GBs_per_dir']} | {r['push_sync_frac_of_link']} |")
+                md.append(f"| {r['bytes']} | {r.get('push_sync_path', '')} | {r['push_sync_us']} | {r.get('push_sync_p2p_us') or ''} | "
+                          f"{r.get('push_sync_nvls_us') or ''} | {r['nccl_push_us']} | {r['pull_us']} | {r.get('pull_nvls_us') or ''} | "
+                          f"{r['nccl_allgather_us']} | {r['push_async_us']} | {r['nccl_rs_apply_us']} |")
             md.append("")
     md += ["## SASS evidence", "",
            "`profiles/sass_mnemonics.txt` (from `tools/sass_summary.sh`, cuobjdump of libb200ps.so) lists per kernel the "
