@@ -69,7 +69,7 @@ def _stream_id(name: str) -> int:
 class ParameterStore:
     LL_MAX_ELEMS = 1 << 19     # fp32 groups up to 2 MB use the low-latency packet push
     NVLS_MIN_BYTES = 1 << 20   # dense groups of >= 1 MB live in multicast-bound memory and push through the switch
-    NVLS_MAX_BYTES = 1 << 29   # ... up to 512 MB: at 1 GB the P2P kernel is faster again (profiles/pushpull_sweep_n8_r2.json)
+    NVLS_MAX_BYTES = 1 << 29   # ... up to 512 MB: at 1 GB the P2P kernel is faster again (profiles/pushpull_sweep_n8.json)
 
     def __init__(self, pool: SymmPool, placement: str = "flat_shard", seed: int = 1,
                  num_shards: Optional[int] = None):

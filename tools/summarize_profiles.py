@@ -65,7 +65,7 @@ def main():
           "Round 2: every capture below was retaken on the final tree (`cluster` = the opt-in resident-cluster step K14, "
           "50 steps per launch; `wd_owner` = the owner-side wide & deep phases on 2 virtual ranks of one GPU).  Other "
           "evidence here: `bench_{b200ps,baseline}_n{1,2,4,8}_r2.json` (both arms, same box, back to back), "
-          "`pushpull_sweep_n{2,8}_r2.json`, `ncu_cluster.txt`, `cluster_probe.txt`, `multi_gpu/` (2- and 8-GPU test logs: "
+          "`pushpull_sweep_n{2,8}.json`, `ncu_cluster.txt`, `cluster_probe.txt`, `multi_gpu/` (2- and 8-GPU test logs: "
           "oracle comparisons, dead-rank detection, skew stress on the checked build), `sanitizer_refusal.log`, "
           "`EXPERIMENTS.md`.", ""]
     for cfg in ("mnist", "mnist_chain", "cluster", "wide", "sparse", "wd", "wd_owner"):
