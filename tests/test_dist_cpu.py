@@ -192,3 +192,17 @@ def test_shell_launchers(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     assert "train data: data/train/part-00000,data/train/part-00001,data/train/part-00002" in r.stdout
     assert "Finish evaluate, auc:" in r.stdout
+
+
+def test_control_plane_liveness_check_detects_a_dead_rank(tmp_path):
+    """Context.check_peers over gloo: all ranks answer -> returns; one has died -> PeerLost on the survivor within the
+    timeout; Context.abandon leaves without barriers and the interpreter exits normally (the GPU twin of this test is
+    tests/test_gpu_multi.py::test_nvlink_backend_detects_a_dead_rank)."""
+    import json
+    out = tmp_path / "liveness.json"
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29711", os.path.join(os.path.dirname(__file__), "cpu_liveness_worker.py"),
+                        str(out)], env=ENV, capture_output=True, text=True, timeout=180)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    res = json.load(open(out))
+    assert res.get("lost") and res["checks_ok"] == 3 and res["seconds"] < 10.0 and "stopped answering" in res["message"], res
