@@ -140,7 +140,7 @@ class SparseWideDeep:
             w, dev = store.world, store.device
             inbox = store.pool.alloc(f"wd.inbox.{cap}", w * cap * 8)
             cnt = store.pool.alloc(f"wd.inbox_cnt.{cap}", 4 * max(w, 64))
-            resp = store.pool.alloc(f"wd.resp.{cap}", cap * 8)
+            resp = store.pool.alloc(f"wd.resp.{cap}", w * cap * 8)        # answers land in inbox order per owner
             pb = store.pool.alloc(f"wd.bias_pend.{cap}", 256)
             g = store._group_of(self.Bn)
             b_owner = g.layout.owner_of(g.layout.offsets[self.Bn])
@@ -150,7 +150,8 @@ class SparseWideDeep:
                 bias_pend=tensor_from_ptr(pb.ptrs[b_owner], 4, dev).view(torch.float32),
                 t_inbox=ops.device_ptr_table(inbox.ptrs, dev), t_cnt=ops.device_ptr_table(cnt.ptrs, dev),
                 t_resp=ops.device_ptr_table(resp.ptrs, dev),
-                count={r: torch.zeros(w + 1, dtype=torch.int32, device=dev) for r in store.pool.local_ranks})
+                count={r: torch.zeros(w + 1, dtype=torch.int32, device=dev) for r in store.pool.local_ranks},
+                slot_tab={r: torch.zeros(cap, dtype=torch.int32, device=dev) for r in store.pool.local_ranks})
         return self._own[cap]
 
     def _step_owner(self, store, batches: dict, lr: float, sync: bool):
@@ -168,7 +169,7 @@ class SparseWideDeep:
             ob = self._owner_buffers(store, fid.numel())
             ops.wd_owner_request(row_ptr, fid, world=N, rank=r, cap=fid.numel(), rows_per_shard=e.rows_per_shard,
                                  features=self.features, inbox_table=ob["t_inbox"], cnt_table=ob["t_cnt"],
-                                 resp_table=ob["t_resp"], count=ob["count"][r])
+                                 resp_table=ob["t_resp"], count=ob["count"][r], slot_tab=ob["slot_tab"][r])
         store.barrier()
         for r in ranks:
             ob = self._owner_buffers(store, batches[r][1].numel())
@@ -184,7 +185,7 @@ class SparseWideDeep:
             bufs["loss"].zero_()
             ops.wd_owner_loss(row_ptr, fid, fval, labels, world=N, rank=r, cap=fid.numel(),
                               rows_per_shard=e.rows_per_shard, features=self.features, resp_table=ob["t_resp"],
-                              pend_table=pe.table, bias=self._tab["bias"], bias_pend=ob["bias_pend"],
+                              slot_tab=ob["slot_tab"][r], pend_table=pe.table, bias=self._tab["bias"], bias_pend=ob["bias_pend"],
                               pred=bufs["pred"], loss_sum=bufs["loss"],
                               global_step=store.global_step_tensor(r) if sync else self._gs0, update=True,
                               lr=lr / N if sync else lr)

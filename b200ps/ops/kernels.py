@@ -367,11 +367,12 @@ def sparse_wd_apply(pend_local, wide_local, emb_local, rows_local, dim, w2_table
 
 
 def wd_owner_request(row_ptr, fid, *, world, rank, cap, rows_per_shard, features, inbox_table, cnt_table, resp_table,
-                     count, stream=None):
+                     count, slot_tab, stream=None):
     """Phase 1 of the owner-side wide & deep step: post this rank's row requests (include/b200ps.h)."""
     check(native.load().b200ps_wd_owner_request(ptr(row_ptr), ptr(fid), row_ptr.numel() - 1, world, rank, cap,
                                                 rows_per_shard, features, ptr(inbox_table), ptr(cnt_table),
-                                                ptr(resp_table), ptr(count), stream_ptr(stream)), "wd_owner_request")
+                                                ptr(resp_table), ptr(count), ptr(slot_tab), stream_ptr(stream)),
+          "wd_owner_request")
 
 
 def wd_owner_serve(*, world, rank, cap, inbox_table, cnt_table, resp_table, emb_local, wide_local, dim, w2_table,
@@ -390,15 +391,15 @@ def wd_owner_fold(*, world, rank, cap, inbox_table, cnt_table, pend_local, emb_l
                                              w2_rows_per_shard, stream_ptr(stream)), "wd_owner_fold")
 
 
-def wd_owner_loss(row_ptr, fid, fval, labels, *, world, rank, cap, rows_per_shard, features, resp_table, pend_table,
-                  bias, bias_pend=None, pred=None, dz_out=None, loss_sum=None, global_step=None, update=True, lr=0.0, grad_scale=None,
+def wd_owner_loss(row_ptr, fid, fval, labels, *, world, rank, cap, rows_per_shard, features, resp_table, slot_tab,
+                  pend_table, bias, bias_pend=None, pred=None, dz_out=None, loss_sum=None, global_step=None, update=True, lr=0.0, grad_scale=None,
                   loss_scale=None, stream=None):
     """Phase 3: loss / dz from the response array and the scalar coefficients into the owners' pending table."""
     B = labels.numel()
     gs = (1.0 / B) if grad_scale is None else grad_scale
     ls = (1.0 / B) if loss_scale is None else loss_scale
     check(native.load().b200ps_wd_owner_loss(ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), B, world, rank, cap,
-                                             rows_per_shard, features, ptr(resp_table), ptr(pend_table), ptr(bias),
+                                             rows_per_shard, features, ptr(resp_table), ptr(slot_tab), ptr(pend_table), ptr(bias),
                                              ptr(bias_pend), ptr(pred), ptr(dz_out), ptr(loss_sum), ptr(global_step), int(update), lr,
                                              gs, ls, stream_ptr(stream)), "wd_owner_loss")
 

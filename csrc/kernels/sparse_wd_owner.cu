@@ -15,7 +15,8 @@
 //   request   every rank buckets its batch's non-zeros by owner (warp-aggregated slot allocation) and writes
 //             {local row, non-zero index} into the owner's inbox; the last CTA publishes the per-owner counts
 //   serve     every rank walks its inbox: a warp reads one LOCAL row (coalesced 512 B), dots it with w2, adds the
-//             wide weight and writes the scalar into the requester's response array at the non-zero's index
+//             wide weight and writes the scalar into the requester's response array in INBOX order (a warp's 32
+//             answers are one contiguous 256-B remote write; the requester kept non-zero -> slot in slot_tab)
 //   loss      warp per example: z, sigmoid, logistic loss, dz; c = -lr*dz*v goes as a scalar red.add into the
 //             owner's pending table (the deferred-update table of sparse_wd.cu); bias and global_step as before
 //   fold      (b200ps_sparse_wd_apply, phase 1 extended) the owner folds the pending scalars into W and E and
@@ -38,7 +39,8 @@ struct OwnerParams {
   int shift;                               // >= 0 when rows_per_shard is a power of two
   uint2* const* inbox;                     // [world] peer-mapped: inbox[o] + src*cap + slot = {local row, nz index}
   unsigned int* const* inbox_cnt;          // [world] peer-mapped: inbox_cnt[o][src]
-  float2* const* resp;                     // [world] peer-mapped: resp[r][nz index] = {E[f].w2, W[f]}
+  float2* const* resp;                     // [world] peer-mapped: resp[r][owner*cap + slot] = {E[f].w2, W[f]} (inbox order)
+  int* slot_tab;                           // [cap] local: non-zero index -> owner*cap + slot (-1: refused id)
   unsigned int* count;                     // [world + 1] local: slots handed out per owner | CTA arrival counter
   unsigned long long* bad_ids;
 };
@@ -48,6 +50,16 @@ __device__ __forceinline__ int own_owner(const OwnerParams& p, int64_t id, int64
   if (p.shift >= 0) { o = (int)(id >> p.shift); local = id & (p.rows_per_shard - 1); }
   else { o = (int)(id / p.rows_per_shard); local = id - (int64_t)o * p.rows_per_shard; }
   return o;
+}
+
+// The (sharded, mostly remote) w2 vector into shared memory: D/4 threads of the CTA fetch one float4 each.
+template <int D>
+__device__ __forceinline__ void stage_w2(float* s_w2, float* const* w2_shards, int64_t w2_rows_per_shard) {
+  for (int q = threadIdx.x; q < D / 4; q += kOwnThreads) {
+    const int col = q * 4;                             // a 4-aligned group never straddles w2 shards
+    *reinterpret_cast<float4*>(s_w2 + col) =
+        __ldcg(reinterpret_cast<const float4*>(w2_shards[col / w2_rows_per_shard] + col % w2_rows_per_shard));
+  }
 }
 
 // ---- phase 1: bucket the batch's non-zeros by owner and post the requests
@@ -62,7 +74,7 @@ __global__ void __launch_bounds__(kOwnThreads) wd_request_kernel(const OwnerPara
     if (j < nnz) {
       const int64_t id = p.fid[j];
       if ((unsigned long long)id < (unsigned long long)p.features) o = own_owner(p, id, local);
-      else ++bad;
+      else { ++bad; p.slot_tab[j] = -1; }
     }
     // warp-aggregated slot allocation: one atomic per (warp, owner)
     const unsigned peers = __match_any_sync(0xffffffffu, o);
@@ -73,6 +85,7 @@ __global__ void __launch_bounds__(kOwnThreads) wd_request_kernel(const OwnerPara
     if (o >= 0) {
       const unsigned slot = base + (unsigned)__popc(peers & ((1u << lane) - 1u));
       p.inbox[o][(size_t)p.rank * p.cap + slot] = make_uint2((unsigned)local, (unsigned)j);
+      p.slot_tab[j] = o * p.cap + (int)slot;       // the answer comes back at the same (owner, slot): coalesced remote writes
     }
   }
   if (bad && p.bad_ids) atomicAdd(p.bad_ids, (unsigned long long)bad);
@@ -98,20 +111,21 @@ __global__ void __launch_bounds__(kOwnThreads) wd_serve_kernel(const OwnerParams
                                                               int64_t w2_rows_per_shard) {
   constexpr int D = 128 * NCH;
   const int lane = threadIdx.x & 31;
-  float4 w2r[NCH];
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const int col = (c * 32 + lane) * 4;             // a 4-aligned group never straddles w2 shards
-    w2r[c] = __ldcg(reinterpret_cast<const float4*>(w2_shards[col / w2_rows_per_shard] + col % w2_rows_per_shard));
-  }
+  // w2 lives on world shards: ONE remote read of it per CTA (staged in shared memory), not one per warp — remote reads
+  // are round trips, 2368 warps x 7 peers of them were a visible part of the kernel at 8 GPUs
+  __shared__ __align__(16) float s_w2[D];
+  stage_w2<D>(s_w2, w2_shards, w2_rows_per_shard);
   // flattened request space: [src 0 requests | src 1 requests | ...]
   __shared__ unsigned s_pref[kMaxWorldOwn + 1];
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == kOwnThreads - 1) {
     unsigned acc = 0;
     for (int r = 0; r < p.world; ++r) { s_pref[r] = acc; acc += __ldcg(p.inbox_cnt[p.rank] + r); }
     s_pref[p.world] = acc;
   }
   __syncthreads();
+  float4 w2r[NCH];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) w2r[c] = *reinterpret_cast<const float4*>(&s_w2[(c * 32 + lane) * 4]);
   const unsigned total = s_pref[p.world];
   const uint2* inbox = p.inbox[p.rank];
   const unsigned warp = (blockIdx.x * kOwnThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kOwnThreads) >> 5;
@@ -154,7 +168,8 @@ __global__ void __launch_bounds__(kOwnThreads) wd_serve_kernel(const OwnerParams
         if (lane == k0 + u) mine = sdot;
       }
     }
-    if (src >= 0) p.resp[src][rq.y] = make_float2(mine, wide ? __ldcg(wide + rq.x) : 0.f);
+    if (src >= 0)
+      p.resp[src][(size_t)p.rank * p.cap + (t - s_pref[src])] = make_float2(mine, wide ? __ldcg(wide + rq.x) : 0.f);
   }
 }
 
@@ -177,9 +192,9 @@ __global__ void __launch_bounds__(kOwnThreads) wd_loss_kernel(const OwnerParams 
     const int beg = p.row_ptr[ex], end = p.row_ptr[ex + 1];
     float z = 0.f;
     for (int j = beg + lane; j < end; j += 32) {
-      const int64_t id = p.fid[j];
-      if ((unsigned long long)id < (unsigned long long)p.features) {
-        const float2 r = __ldcg(resp + j);
+      const int st = p.slot_tab[j];
+      if (st >= 0) {
+        const float2 r = __ldcg(resp + st);
         z = fmaf(p.fval[j], r.x + r.y, z);
       }
     }
@@ -234,19 +249,20 @@ __global__ void __launch_bounds__(kOwnThreads) wd_fold_kernel(const OwnerParams 
   __shared__ float s_g2[kOwnThreads / 32][D];
   __shared__ unsigned s_pref[kMaxWorldOwn + 1];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
-  float4 w2r[NCH], g2[NCH];
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const int col = (c * 32 + lane) * 4;
-    w2r[c] = __ldcg(reinterpret_cast<const float4*>(w2_shards[col / w2_rows_per_shard] + col % w2_rows_per_shard));
-    g2[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  if (threadIdx.x == 0) {
+  __shared__ __align__(16) float s_w2[D];
+  stage_w2<D>(s_w2, w2_shards, w2_rows_per_shard);
+  if (threadIdx.x == kOwnThreads - 1) {
     unsigned acc = 0;
     for (int r = 0; r < p.world; ++r) { s_pref[r] = acc; acc += __ldcg(p.inbox_cnt[p.rank] + r); }
     s_pref[p.world] = acc;
   }
   __syncthreads();
+  float4 w2r[NCH], g2[NCH];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    w2r[c] = *reinterpret_cast<const float4*>(&s_w2[(c * 32 + lane) * 4]);
+    g2[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const unsigned total = s_pref[p.world];
   const uint2* inbox = p.inbox[p.rank];
   const unsigned warp = (blockIdx.x * kOwnThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kOwnThreads) >> 5;
@@ -310,7 +326,8 @@ __global__ void __launch_bounds__(kOwnThreads) wd_fold_kernel(const OwnerParams 
 
 static void fill_params(OwnerParams& p, const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                         int32_t B, int32_t world, int32_t rank, int32_t cap, int64_t rows_per_shard, int64_t features,
-                        void* const* inbox, uint32_t* const* inbox_cnt, void* const* resp, uint32_t* count) {
+                        void* const* inbox, uint32_t* const* inbox_cnt, void* const* resp, uint32_t* count,
+                        int32_t* slot_tab) {
   p.row_ptr = row_ptr; p.fid = fid; p.fval = fval; p.labels = labels;
   p.B = B; p.world = world; p.rank = rank; p.cap = cap; p.rows_per_shard = rows_per_shard; p.features = features;
   p.shift = -1;
@@ -323,6 +340,7 @@ static void fill_params(OwnerParams& p, const int32_t* row_ptr, const int64_t* f
   p.inbox_cnt = reinterpret_cast<unsigned int* const*>(inbox_cnt);
   p.resp = reinterpret_cast<float2* const*>(resp);
   p.count = count;
+  p.slot_tab = slot_tab;
   p.bad_ids = bad_id_counter();
 }
 
@@ -339,10 +357,12 @@ using namespace b200ps;
 extern "C" int b200ps_wd_owner_request(const int32_t* row_ptr, const int64_t* fid, int32_t B, int32_t world, int32_t rank,
                                        int32_t cap, int64_t rows_per_shard, int64_t features, void* const* inbox,
                                        uint32_t* const* inbox_cnt, void* const* resp, uint32_t* count,
-                                       b200ps_stream_t stream) {
+                                       int32_t* slot_tab, b200ps_stream_t stream) {
   OWN_COMMON_CHECKS("wd_owner_request");
+  B200PS_REQUIRE(slot_tab, "wd_owner_request: null slot table");
   OwnerParams p;
-  fill_params(p, row_ptr, fid, nullptr, nullptr, B, world, rank, cap, rows_per_shard, features, inbox, inbox_cnt, resp, count);
+  fill_params(p, row_ptr, fid, nullptr, nullptr, B, world, rank, cap, rows_per_shard, features, inbox, inbox_cnt, resp, count,
+              slot_tab);
   const int ctas = std::min((cap + kOwnThreads - 1) / kOwnThreads, sm_count() * 2);
   wd_request_kernel<<<ctas, kOwnThreads, 0, as_stream(stream)>>>(p);
   B200PS_LAUNCH_CHECK();
@@ -375,7 +395,7 @@ extern "C" int b200ps_wd_owner_serve(int32_t world, int32_t rank, int32_t cap, v
 // phase 3: loss, dz and (do_update) the scalar coefficients into the owners' pending tables, bias, global_step.
 extern "C" int b200ps_wd_owner_loss(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                                     int32_t B, int32_t world, int32_t rank, int32_t cap, int64_t rows_per_shard,
-                                    int64_t features, void* const* resp, float* const* pend_shards, float* bias,
+                                    int64_t features, void* const* resp, const int32_t* slot_tab, float* const* pend_shards, float* bias,
                                     float* bias_pend, float* pred, float* dz_out, float* loss_sum, uint64_t* global_step,
                                     int32_t do_update, float lr, float grad_scale, float loss_scale, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && world >= 1 && world <= kMaxWorldOwn && rank >= 0 && rank < world && rows_per_shard > 0 && features > 0 &&
@@ -383,7 +403,9 @@ extern "C" int b200ps_wd_owner_loss(const int32_t* row_ptr, const int64_t* fid, 
                  "wd_owner_loss: bad arguments");
   OwnerParams p;
   uint32_t dummy = 0;
-  fill_params(p, row_ptr, fid, fval, labels, B, world, rank, cap, rows_per_shard, features, resp /* unused */, nullptr, resp, &dummy);
+  B200PS_REQUIRE(slot_tab, "wd_owner_loss: null slot table");
+  fill_params(p, row_ptr, fid, fval, labels, B, world, rank, cap, rows_per_shard, features, resp /* unused */, nullptr, resp, &dummy,
+              const_cast<int32_t*>(slot_tab));
   p.count = nullptr; p.inbox = nullptr; p.inbox_cnt = nullptr;
   OwnerLoss q;
   q.pend = pend_shards; q.pend_rows_per_shard = rows_per_shard; q.pend_shift = p.shift;

@@ -7,7 +7,7 @@ from b200ps.models.wide_deep import SparseWideDeep
 from b200ps.parallel.context import init_from_env
 from b200ps.ps.store import ParameterStore
 
-world = 2
+world = int(os.environ.get("WD_WORLD", "2"))
 ctx = init_from_env(virtual_world=world)
 F, B, nnz, spread = 1 << 22, 500, 100, 20
 store = ParameterStore(ctx.pool)
