@@ -379,11 +379,12 @@ def bench_sparse(ctx, args, sampler, mode="async", deep_dim=0):
     from b200ps.train import SparseLRTrainer, SparseWideDeepTrainer
     F, B, nnz, spread = (1 << 22 if deep_dim else 1 << 24), args.sparse_batch, 100, 20
     if deep_dim:
-        # from 4 GPUs on: owner-side rows (request / serve / loss rounds, no embedding row crosses a link; measured
-        # 121 vs 115 us/step on 2 GPUs, 182 vs 399 on 8); the asynchronous updates are then applied in lockstep rounds
-        # (unaveraged, every worker's update lands)
+        # across GPUs: owner-side rows (request / serve / loss rounds, no embedding row crosses a link; measured
+        # 78 vs 116 us/step on 2 GPUs, 96 vs 399 on 8); the asynchronous updates are then applied in lockstep rounds
+        # (unaveraged, every worker's update lands).  B200PS_WD_OWNER=0 or B200PS_WD_OWNER_MIN=<world> pick the direct kernel.
         tr = SparseWideDeepTrainer(ctx, features=F, dim=deep_dim, lr=0.05, mode=mode,
-                                   owner=(ctx.world >= 4 and os.environ.get("B200PS_WD_OWNER", "1") != "0"))
+                                   owner=(ctx.world >= int(os.environ.get("B200PS_WD_OWNER_MIN", "2"))
+                                          and os.environ.get("B200PS_WD_OWNER", "1") != "0"))
     else:
         tr = SparseLRTrainer(ctx, features=F, lr=0.05, mode=mode)
     dev = ctx.device
