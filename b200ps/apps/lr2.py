@@ -63,6 +63,8 @@ flags.DEFINE_float("init_stddev", 0.0, "stddev of the weight initialiser; 0 = th
 flags.DEFINE_boolean("native_loader", False, "GPU backend: read, sample and batch the train files with the native loader "
                      "threads (packed pinned batches -> one H2D copy + one graph launch per step) instead of the "
                      "Python DataProvider")
+flags.DEFINE_boolean("unique_ids", False, "GPU backend, plain LR: make each batch's ids unique on the device first (one read and "
+                     "one update per distinct id, as embedding_lookup_sparse / IndexedSlices do); pays when ids repeat")
 flags.DEFINE_integer("synthetic_rows", 4000, "rows per synthetic file when --train/--test is 'synthetic'")
 
 
@@ -218,7 +220,7 @@ def main(argv=None) -> int:
     if deep:
         model = SparseWideDeep(FLAGS.features, dim=FLAGS.deep_dim, stddev=FLAGS.init_stddev or 0.01)
     else:
-        model = SparseLR(FLAGS.features, stddev=FLAGS.init_stddev or 1.0)
+        model = SparseLR(FLAGS.features, stddev=FLAGS.init_stddev or 1.0, dedupe=True if FLAGS.unique_ids else None)
     sync = bool(FLAGS.sync)
     if gpu:
         from ..train import SparseLRTrainer

@@ -41,9 +41,15 @@ def sparse_lr_reference(W: torch.Tensor, b: torch.Tensor, row_ptr, fid, fval, la
 class SparseLR:
     W, Bn = "weights/Variable", "bias/Variable"
 
-    def __init__(self, features: int, stddev: float = 1.0):
+    def __init__(self, features: int, stddev: float = 1.0, dedupe: Optional[bool] = None):
+        import os
         self.features, self.stddev = int(features), float(stddev)
+        # dedupe: make the batch's ids unique first (csrc/kernels/sparse_dedup.cu) — every distinct row is read once
+        # and receives one update, as embedding_lookup_sparse + IndexedSlices do in the reference (lr2.py:390-396).
+        # Pays when ids repeat inside a batch (click logs); with uniform ids the direct kernel is faster.
+        self.dedupe = (os.environ.get("B200PS_SPARSE_DEDUPE", "0") != "0") if dedupe is None else bool(dedupe)
         self._bufs: Dict[int, dict] = {}
+        self._dd: Dict[tuple, dict] = {}
 
     def register(self, store) -> None:
         if hasattr(store, "note_untracked_variable"):
@@ -57,6 +63,37 @@ class SparseLR:
             self._bufs[k] = dict(pred=torch.empty(B, device=device), dz=torch.empty(B, device=device),
                                  loss=torch.zeros(1, device=device))
         return self._bufs[k]
+
+    def _dedup_scratch(self, cap: int, device, key: int) -> dict:
+        """Per (rank, capacity): the id hash table (epoch-tagged keys, never cleared), the unique list and the
+        gathered-weight / gradient buffers of the unique-id step."""
+        k = (int(cap), key)
+        if k not in self._dd:
+            T = ops.sparse_dedup_table_size(cap)
+            z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
+            state = z(4, torch.int32)
+            state[1] = 1                        # epoch 0 is what the zero-filled table holds
+            self._dd[k] = dict(keys=z(T, torch.int64), slot_of=z(T, torch.int32), hpos=z(cap, torch.int32),
+                               uniq=z(cap, torch.int64), wbuf=z(cap, torch.float32), gbuf=z(cap, torch.float32),
+                               state=state, table_size=T)
+        return self._dd[k]
+
+    def last_unique_counts(self, cap: int, key: int = 0):
+        """(distinct ids, non-zeros) of the last finished unique-id step on that scratch (a device read)."""
+        st = self._dd[(int(cap), key)]["state"].tolist()
+        return st[2], st[3]
+
+    def _run(self, store, batch, rank, **kw):
+        """One launch of the step kernel: the direct one, or (dedupe) unique pass + cooperative step."""
+        row_ptr, fid, fval, labels = batch
+        sv = store.sparse_var(self.W)
+        if not (self.dedupe and labels.device.type == "cuda"):
+            kw.pop("unique", None), kw.pop("finish", None)
+            return ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
+                                 rows_per_shard=sv.rows_per_shard, features=self.features, **kw)
+        sc = self._dedup_scratch(fid.numel(), labels.device, 0 if rank is None else rank)
+        return ops.sparse_lr_unique(row_ptr, fid, fval, labels, sv.table, self._bias(store), scratch=sc,
+                                    rows_per_shard=sv.rows_per_shard, features=self.features, **kw)
 
     def _bias(self, store) -> torch.Tensor:
         from ..parallel.symm import tensor_from_ptr
@@ -74,9 +111,8 @@ class SparseLR:
         from ..parallel.symm import tensor_from_ptr
         if not hasattr(self, "_gs0"):
             self._gs0 = tensor_from_ptr(gs, 8, store.device).view(torch.int64)
-        ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], loss_sum=bufs["loss"],
-                      global_step=self._gs0, forward=True, update=True, lr=lr)
+        self._run(store, batch, rank, pred=bufs["pred"], loss_sum=bufs["loss"], global_step=self._gs0, forward=True,
+                  update=True, lr=lr)
         return bufs["loss"]
 
     def step_sync(self, store, batch, lr: float, rank: Optional[int] = None, replicas: Optional[int] = None):
@@ -87,14 +123,12 @@ class SparseLR:
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
         N = replicas or store.world
-        ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], dz_out=bufs["dz"],
-                      loss_sum=bufs["loss"], forward=True, update=False)
+        self._run(store, batch, rank, pred=bufs["pred"], dz_out=bufs["dz"], loss_sum=bufs["loss"], forward=True,
+                  update=False, finish=False)   # (dedupe) the update launch below reuses this batch's unique list
         store.barrier()                       # nobody updates rows somebody is still reading
         gstep = store.global_step_tensor(rank)  # sync: every rank counts one step per aggregate
-        ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, features=self.features, dz_in=bufs["dz"], global_step=gstep,
-                      forward=False, update=True, lr=lr / N)
+        self._run(store, batch, rank, dz_in=bufs["dz"], global_step=gstep, forward=False, update=True, lr=lr / N,
+                  unique=False)
         store.barrier()                       # all updates landed before the next read
         return bufs["loss"]
 
@@ -104,7 +138,5 @@ class SparseLR:
         sv = store.sparse_var(self.W)
         bufs = self._buffers(labels.numel(), labels.device, 0 if rank is None else rank)
         bufs["loss"].zero_()
-        ops.sparse_lr(row_ptr, fid, fval, labels, sv.table, self._bias(store),
-                      rows_per_shard=sv.rows_per_shard, features=self.features, pred=bufs["pred"], loss_sum=bufs["loss"],
-                      forward=True, update=False)
+        self._run(store, batch, rank, pred=bufs["pred"], loss_sum=bufs["loss"], forward=True, update=False)
         return bufs["pred"], bufs["loss"]

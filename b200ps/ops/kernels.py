@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "wd_owner_fold", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_lr_unique", "sparse_dedup_table_size", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "wd_owner_fold", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -333,6 +333,32 @@ def sparse_lr(row_ptr, fid, fval, labels, w_table, bias, *, rows_per_shard, feat
                                          ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in), ptr(loss_sum),
                                          ptr(global_step), B, rows_per_shard, int(features), int(forward),
                                          int(update), lr, gs, ls, stream_ptr(stream)), "sparse_lr")
+
+
+def sparse_dedup_table_size(cap: int) -> int:
+    """Positions of the id hash table for ``cap`` non-zeros (a power of two, at least 2 * cap)."""
+    return int(native.load().b200ps_sparse_dedup_table_size(int(cap)))
+
+
+def sparse_lr_unique(row_ptr, fid, fval, labels, w_table, bias, *, scratch, rows_per_shard, features=None, pred=None,
+                     dz_out=None, dz_in=None, loss_sum=None, global_step=None, forward=True, update=True, lr=0.0,
+                     grad_scale=None, loss_scale=None, unique=True, finish=True, stream=None):
+    """Sparse LR step over the batch's UNIQUE ids (K4u/K5u, csrc/kernels/sparse_dedup.cu): a hash pass makes the ids
+    unique (``unique=False`` reuses the list the previous launch left: the update half of a synchronous step), then one
+    cooperative launch gathers each distinct weight once, walks the examples on local buffers and posts one update
+    per distinct id.  ``finish`` hands the table to the next batch.  ``scratch``: SparseLR._dedup_scratch."""
+    if features is None:
+        features = rows_per_shard * w_table.numel()
+    _cuda(row_ptr, fid, fval, labels, w_table, bias)
+    B = labels.numel()
+    gs = (1.0 / B) if grad_scale is None else grad_scale
+    ls = (1.0 / B) if loss_scale is None else loss_scale
+    sc = scratch
+    check(native.load().b200ps_sparse_lr_unique(
+        ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), ptr(w_table), ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in),
+        ptr(loss_sum), ptr(global_step), B, fid.numel(), rows_per_shard, int(features), int(unique), int(forward),
+        int(update), int(finish), lr, gs, ls, ptr(sc["keys"]), ptr(sc["slot_of"]), sc["table_size"], ptr(sc["hpos"]),
+        ptr(sc["uniq"]), ptr(sc["wbuf"]), ptr(sc["gbuf"]), ptr(sc["state"]), stream_ptr(stream)), "sparse_lr_unique")
 
 
 def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, emb_table, emb_rows_per_shard, dim,

@@ -493,9 +493,10 @@ class SparseLRTrainer(_TrainerBase):
     """lr2.py's trainer over a row-sharded weight: async (default, like the reference) or sync."""
 
     def __init__(self, ctx, features: int, lr: float = 0.001, mode: str = "async",
-                 placement: str = "flat_shard", seed: int = 1, use_graph: bool = True, model=None):
+                 placement: str = "flat_shard", seed: int = 1, use_graph: bool = True, model=None,
+                 dedupe: Optional[bool] = None):
         super().__init__(ctx, mode, lr, None, placement, seed)
-        self.model = model or SparseLR(features)
+        self.model = model or SparseLR(features, dedupe=dedupe)    # dedupe: unique-id step (sparse_dedup.cu)
         self.model.register(self.store)
         self.store.build()
         self.store.initialize()

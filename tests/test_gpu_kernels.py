@@ -281,6 +281,79 @@ def test_sparse_lr_vs_dense_reference(native_lib, world):
     assert (torch.cat(shards2).double() - W_ref).abs().max().item() < 1e-3 and gstep.item() == 2
 
 
+def _skewed_batch(F, seed, B=500, nnz=100, spread=20):
+    """A click-log-like batch: ids drawn as F * u^6 (a few hot ids in most rows), plus two ids outside the range."""
+    rp, fid, fv, y = _sparse_batch(B=B, nnz=nnz, spread=spread, F=F, seed=seed)
+    n = rp[-1].item()
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    u = torch.rand(n, device=DEV, generator=g, dtype=torch.float64)
+    fid[:n] = (u.pow(6) * F).long().clamp_(0, F - 1)
+    return rp, fid, fv, y
+
+
+@pytest.mark.parametrize("world", [1, 4])
+def test_sparse_lr_unique_ids_vs_dense_reference(native_lib, world):
+    """K4u/K5u (sparse_dedup.cu): the unique-id step against a float64 dense reference on batches full of repeated
+    ids — forward, the synchronous split, the fused step (exact here: every weight is read before any is written),
+    the distinct-id count, refused ids, and a second and third batch through the same never-cleared table."""
+    from b200ps import ops
+    from b200ps.models.sparse_lr import SparseLR
+    F = 1 << 20
+    rows = F // world
+    g = torch.Generator(device=DEV).manual_seed(9)
+    W = torch.randn(F, device=DEV, generator=g) * 0.1
+    shards = [W[r * rows:(r + 1) * rows].clone() for r in range(world)]
+    table = ops.device_ptr_table([s.data_ptr() for s in shards], DEV)
+    bias = torch.full((1,), 0.25, device=DEV)
+    gstep = torch.zeros(1, device=DEV, dtype=torch.int64)
+    model = SparseLR(F, dedupe=True)
+    lr = 0.5
+    W_ref, b_ref = W.double().clone(), 0.25
+    ops.sparse_bad_ids(reset=True)
+    for it, mode in enumerate(["split", "fused", "fused"]):
+        rp, fid, fv, y = _skewed_batch(F, seed=11 + it)
+        B = y.numel(); n = rp[-1].item()
+        if it == 1:
+            fid[3] = F + 5; fid[n - 1] = -2                  # refused: contribute nothing, counted
+        ok = (fid[:n] >= 0) & (fid[:n] < F)
+        sc = model._dedup_scratch(fid.numel(), DEV, 0)
+        row_of = torch.repeat_interleave(torch.arange(B, device=DEV), (rp[1:] - rp[:-1]).long())
+        fsafe = fid[:n].clamp(0, F - 1)
+        contrib = torch.where(ok, W_ref[fsafe] * fv[:n].double(), torch.zeros((), device=DEV, dtype=torch.float64))
+        z = torch.zeros(B, device=DEV, dtype=torch.float64).index_add_(0, row_of, contrib) + b_ref
+        p_ref = torch.sigmoid(z)
+        loss_ref = torch.nn.functional.binary_cross_entropy_with_logits(z, y.double())
+        dz_ref = (p_ref - y.double()) / B
+        upd = torch.where(ok, -lr * dz_ref[row_of] * fv[:n].double(), torch.zeros((), device=DEV, dtype=torch.float64))
+        W_ref = W_ref.index_add(0, fsafe, upd)
+        b_ref = b_ref - lr * dz_ref.sum().item()
+        pred = torch.empty(B, device=DEV); loss = torch.zeros(1, device=DEV); dz = torch.empty(B, device=DEV)
+        kw = dict(scratch=sc, rows_per_shard=rows, features=F)
+        if mode == "split":
+            before = torch.cat(shards).clone()
+            ops.sparse_lr_unique(rp, fid, fv, y, table, bias, pred=pred, dz_out=dz, loss_sum=loss, forward=True,
+                                 update=False, finish=False, **kw)
+            torch.cuda.synchronize()
+            assert torch.allclose(pred.double(), p_ref, atol=1e-5) and abs(loss.item() - loss_ref.item()) < 1e-5
+            assert torch.allclose(dz.double(), dz_ref, atol=1e-8) and torch.equal(torch.cat(shards), before)
+            ops.sparse_lr_unique(rp, fid, fv, y, table, bias, dz_in=dz, global_step=gstep, forward=False, update=True,
+                                 lr=lr, unique=False, **kw)
+        else:
+            ops.sparse_lr_unique(rp, fid, fv, y, table, bias, pred=pred, loss_sum=loss, global_step=gstep,
+                                 forward=True, update=True, lr=lr, **kw)
+            torch.cuda.synchronize()
+            assert torch.allclose(pred.double(), p_ref, atol=1e-5) and abs(loss.item() - loss_ref.item()) < 1e-5
+        torch.cuda.synchronize()
+        got = torch.cat(shards).double()
+        assert (got - W_ref).abs().max().item() < 2e-5, (it, (got - W_ref).abs().max().item())
+        assert abs(bias.item() - b_ref) < 1e-5 and gstep.item() == it + 1
+        distinct, nz = model.last_unique_counts(fid.numel(), 0)
+        assert distinct == torch.unique(fid[:n][ok]).numel() and nz == n
+        assert distinct < 0.8 * n                              # the batch really repeats ids
+        W_ref = got                                            # carry the fp32 state forward
+    assert ops.sparse_bad_ids(reset=True) == 2
+
+
 @pytest.mark.parametrize("world,dim,wide", [(1, 128, True), (4, 128, True), (2, 256, False), (2, 512, True)])
 def test_sparse_wide_deep_vs_float64_reference(native_lib, world, dim, wide):
     """K4w/K5w: forward exact on frozen tables; update-only conserves every contribution of all four
