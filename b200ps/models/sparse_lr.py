@@ -70,18 +70,28 @@ class SparseLR:
         k = (int(cap), key)
         if k not in self._dd:
             T = ops.sparse_dedup_table_size(cap)
+            with torch.cuda.device(device):
+                L = ops.sparse_dedup_list_size(cap)
+                sms = torch.cuda.get_device_properties(device).multi_processor_count
             z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
-            state = z(4, torch.int32)
+            state = z(16, torch.int32)
             state[1] = 1                        # epoch 0 is what the zero-filled table holds
             self._dd[k] = dict(keys=z(T, torch.int64), slot_of=z(T, torch.int32), hpos=z(cap, torch.int32),
-                               uniq=z(cap, torch.int64), wbuf=z(cap, torch.float32), gbuf=z(cap, torch.float32),
-                               state=state, table_size=T)
+                               uniq=z(L, torch.int64), wbuf=z(L, torch.float32), gbuf=z(L, torch.float32),
+                               seg_cnt=z(2 * sms, torch.int32), state=state, table_size=T, list_cap=L)
         return self._dd[k]
 
     def last_unique_counts(self, cap: int, key: int = 0):
         """(distinct ids, non-zeros) of the last finished unique-id step on that scratch (a device read)."""
-        st = self._dd[(int(cap), key)]["state"].tolist()
-        return st[2], st[3]
+        sc = self._dd[(int(cap), key)]
+        return int(sc["seg_cnt"].sum().item()), int(sc["state"][3].item())
+
+    def last_phase_times_ns(self, cap: int, key: int = 0):
+        """CTA 0's globaltimer stamps of the last unique-id step as differences: (hash pass, sync, gather + convert,
+        sync, examples, sync, scatter)."""
+        st = [v & 0xffffffff for v in self._dd[(int(cap), key)]["state"].tolist()]
+        t = st[4:12]
+        return [(t[i + 1] - t[i]) & 0xffffffff for i in range(7)]
 
     def _run(self, store, batch, rank, **kw):
         """One launch of the step kernel: the direct one, or (dedupe) unique pass + cooperative step."""

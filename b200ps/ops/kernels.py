@@ -18,7 +18,7 @@ from .native import (ACT_NONE, ACT_SIGMOID, DT_BF16, DT_F32, EPI_ATOMIC_ADD, EPI
 __all__ = [
     "gemm", "mlp_tail", "mlp_fused_step", "mlp_cluster_steps", "mlp_cluster_supported", "softmax_ce", "colsum", "sgd_apply", "adam_apply", "adam_advance",
     "linreg_fwd_bwd", "synth_mnist", "synth_dense_bf16", "synth_sparse", "init_normal",
-    "cast_f32_bf16", "sparse_lr", "sparse_lr_unique", "sparse_dedup_table_size", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "wd_owner_fold", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
+    "cast_f32_bf16", "sparse_lr", "sparse_lr_unique", "sparse_dedup_table_size", "sparse_dedup_list_size", "sparse_bad_ids", "check_sparse_ids", "sparse_wd", "sparse_wd_apply", "wd_owner_request", "wd_owner_serve", "wd_owner_loss", "wd_owner_fold", "auc_hist", "push_sync_sgd", "push_sync_ll", "store_nvls", "push_async", "pull", "barrier",
     "device_ptr_table", "signal_pad_words", "copy_words",
 ]
 
@@ -340,6 +340,11 @@ def sparse_dedup_table_size(cap: int) -> int:
     return int(native.load().b200ps_sparse_dedup_table_size(int(cap)))
 
 
+def sparse_dedup_list_size(cap: int) -> int:
+    """Entries of the unique list / gathered-weight / gradient buffers for ``cap`` non-zeros on the current device."""
+    return int(native.load().b200ps_sparse_dedup_list_size(int(cap)))
+
+
 def sparse_lr_unique(row_ptr, fid, fval, labels, w_table, bias, *, scratch, rows_per_shard, features=None, pred=None,
                      dz_out=None, dz_in=None, loss_sum=None, global_step=None, forward=True, update=True, lr=0.0,
                      grad_scale=None, loss_scale=None, unique=True, finish=True, stream=None):
@@ -358,7 +363,8 @@ def sparse_lr_unique(row_ptr, fid, fval, labels, w_table, bias, *, scratch, rows
         ptr(row_ptr), ptr(fid), ptr(fval), ptr(labels), ptr(w_table), ptr(bias), ptr(pred), ptr(dz_out), ptr(dz_in),
         ptr(loss_sum), ptr(global_step), B, fid.numel(), rows_per_shard, int(features), int(unique), int(forward),
         int(update), int(finish), lr, gs, ls, ptr(sc["keys"]), ptr(sc["slot_of"]), sc["table_size"], ptr(sc["hpos"]),
-        ptr(sc["uniq"]), ptr(sc["wbuf"]), ptr(sc["gbuf"]), ptr(sc["state"]), stream_ptr(stream)), "sparse_lr_unique")
+        ptr(sc["uniq"]), ptr(sc["wbuf"]), ptr(sc["gbuf"]), sc["list_cap"], ptr(sc["seg_cnt"]), ptr(sc["state"]),
+        stream_ptr(stream)), "sparse_lr_unique")
 
 
 def sparse_wd(row_ptr, fid, fval, labels, *, wide_table, wide_rows_per_shard, emb_table, emb_rows_per_shard, dim,

@@ -7,7 +7,7 @@
 // logs are not like that — a few hot features sit in most rows — and then the direct plan reads the same remote
 // word thousands of times and serialises thousands of remote atomics on one address.  This file is the other plan:
 //
-// one cooperative launch, one CTA per SM, four phases separated by grid syncs:
+// one cooperative launch, up to two CTAs per SM, four phases separated by grid syncs:
 //   0. unique   every non-zero inserts its id into an open-addressing hash table in this GPU's memory (64-bit keys
 //               tagged with a step epoch, so the table is never cleared); the winners of an insert take the next
 //               slots of the unique list (one atomic per warp).  Each non-zero remembers its table position.
@@ -29,20 +29,22 @@ namespace cg = cooperative_groups;
 namespace b200ps {
 
 constexpr int kDdThreads = 256;
+constexpr int kDdCtasPerSm = 2;                        // 75 k threads: one round of the hash pass for ~60 k non-zeros
 constexpr int kDdEpochShift = 40;                      // ids < 2^40; the upper 24 bits of a key carry the epoch
 constexpr unsigned long long kDdIdMask = (1ull << kDdEpochShift) - 1ull;
 
-// state[0] = number of distinct ids so far (reset by the step that consumes them), state[1] = epoch,
-// state[2] = distinct ids of the last finished step, state[3] = non-zeros of the last finished step (for the ratio)
+// state[1] = epoch, state[3] = non-zeros of the last finished step, state[4..11] = CTA 0's globaltimer stamps
 struct DedupScratch {
   unsigned long long* keys;   // [T]  (epoch << 40) | id ; anything with another epoch counts as empty
   int* slot_of;               // [T]  table position -> index in uniq
   int* hpos;                  // [cap] non-zero -> table position after the unique pass, -> index in uniq once the
                               //       step kernel has converted it (-1: refused id)
-  long long* uniq;            // [cap] distinct ids in insertion order
-  float* wbuf;                // [cap] gathered weights
-  float* gbuf;                // [cap] accumulated dz*val
-  unsigned* state;            // [4]
+  long long* uniq;            // [grid*seg] distinct ids, CTA c's in [c*seg, c*seg + seg_cnt[c])
+  float* wbuf;                // [grid*seg] gathered weights
+  float* gbuf;                // [grid*seg] accumulated dz*val
+  unsigned* state;            // [16]
+  unsigned* seg_cnt;          // [grid] distinct ids in each CTA's segment of uniq / wbuf / gbuf
+  int seg;                    // segment length: rounds of the hash pass * 256 (a CTA cannot win more than it visits)
   unsigned tmask;             // T - 1
 };
 
@@ -70,13 +72,20 @@ __device__ __forceinline__ float* dd_w_addr(const DedupParams& p, long long id) 
   return p.w_shards[owner] + local;
 }
 
-// ---- unique: insert every id, the winner of an insert appends it to the list ----------------------------------
-__device__ __forceinline__ void dd_unique_pass(const long long* __restrict__ fid, int nnz, long long features,
-                                               const DedupScratch& s, unsigned long long* bad_ids) {
+// ---- unique: insert every id; the winners of an insert append it to their CTA's segment of the list ----------
+// No global list counter: 148 CTAs bumping one word with returning atomics measured 3.4 us per round here (same-
+// address atomics retire one after the other, ~23 ns each), so each CTA fills its own segment [c*seg, c*seg + n_c)
+// from a shared-memory counter and leaves n_c in seg_cnt[c].
+__device__ __forceinline__ int dd_unique_pass(const long long* __restrict__ fid, int nnz, long long features,
+                                              const DedupScratch& s, unsigned long long* bad_ids) {
+  __shared__ unsigned s_cnt;
   const unsigned long long epoch = (unsigned long long)s.state[1] << kDdEpochShift;
   const int lane = threadIdx.x & 31;
+  const unsigned seg0 = blockIdx.x * (unsigned)s.seg;
+  if (threadIdx.x == 0) s_cnt = 0u;
+  __syncthreads();
   int bad = 0;
-  for (int j0 = blockIdx.x * kDdThreads; j0 < nnz; j0 += gridDim.x * kDdThreads) {   // warp-uniform trip count
+  for (int j0 = blockIdx.x * kDdThreads; j0 < nnz; j0 += gridDim.x * kDdThreads) {   // CTA-uniform trip count
     const int j = j0 + threadIdx.x;
     const long long id = j < nnz ? fid[j] : -1;
     const bool valid = (unsigned long long)id < (unsigned long long)features;
@@ -100,15 +109,14 @@ __device__ __forceinline__ void dd_unique_pass(const long long* __restrict__ fid
       }
       if (where < 0) ++bad;
     }
-    // the winners of this warp take consecutive slots of the unique list: one atomic per warp, not one per id
     const unsigned wm = __ballot_sync(0xffffffffu, won);
-    if (wm) {
+    if (wm) {                                          // one shared-memory atomic per warp
       const int leader = __ffs(wm) - 1;
       unsigned base = 0;
-      if (lane == leader) base = atomicAdd(s.state, (unsigned)__popc(wm));
+      if (lane == leader) base = atomicAdd(&s_cnt, (unsigned)__popc(wm));
       base = __shfl_sync(0xffffffffu, base, leader);
       if (won) {
-        const unsigned slot = base + (unsigned)__popc(wm & ((1u << lane) - 1u));
+        const unsigned slot = seg0 + base + (unsigned)__popc(wm & ((1u << lane) - 1u));
         s.uniq[slot] = id;
         s.slot_of[where] = (int)slot;
       }
@@ -116,6 +124,9 @@ __device__ __forceinline__ void dd_unique_pass(const long long* __restrict__ fid
     if (j < nnz) s.hpos[j] = where;
   }
   if (bad && bad_ids) atomicAdd(bad_ids, (unsigned long long)bad);
+  __syncthreads();
+  if (threadIdx.x == 0) s.seg_cnt[blockIdx.x] = s_cnt;
+  return (int)s_cnt;
 }
 
 // ---- the step over the unique list ------------------------------------------------------------------------------
@@ -125,25 +136,24 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const int tid = blockIdx.x * kDdThreads + threadIdx.x, nthreads = gridDim.x * kDdThreads;
   const int nnz = p.row_ptr[p.B];
+  auto stamp = [&](int i) { if (tid == 0) p.s.state[4 + i] = (unsigned)globaltimer_ns(); };
+  stamp(0);
+  int U;                                              // distinct ids in this CTA's segment
   if (p.convert) {                                    // phase 0: this batch's ids -> unique list
-    dd_unique_pass(p.fid, nnz, p.features, p.s, p.bad_ids);
+    U = dd_unique_pass(p.fid, nnz, p.features, p.s, p.bad_ids);
+    stamp(1);
     grid.sync();
+  } else {
+    U = (int)p.s.seg_cnt[blockIdx.x];                 // the launch that ran the hash pass had this very grid
   }
-  const int U = (int)__ldcg(p.s.state);
+  stamp(2);
+  const int seg0 = blockIdx.x * p.s.seg;
 
-  // phase 1: the distinct weights, four loads in flight per thread (the gather is latency: most rows are remote)
-  for (int u0 = tid; u0 < U; u0 += 4 * nthreads) {
-    float w[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int u = u0 + k * nthreads;
-      w[k] = (p.do_forward && u < U) ? __ldcg(dd_w_addr(p, p.s.uniq[u])) : 0.f;
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int u = u0 + k * nthreads;
-      if (u < U) { p.s.wbuf[u] = w[k]; p.s.gbuf[u] = 0.f; }
-    }
+  // phase 1: the distinct weights of this CTA's segment (the gather is latency: most rows are remote) ...
+  for (int u = threadIdx.x; u < U; u += kDdThreads) {
+    const float w = p.do_forward ? __ldcg(dd_w_addr(p, p.s.uniq[seg0 + u])) : 0.f;
+    p.s.wbuf[seg0 + u] = w;
+    p.s.gbuf[seg0 + u] = 0.f;
   }
   // ... and every non-zero's table position becomes its index in the unique list (once per batch: the launch that
   // ran the unique pass), so that phase 2 is one dependent load shorter
@@ -154,7 +164,9 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
     }
   }
   const float b = p.do_forward ? __ldcg(p.bias) : 0.f;
+  stamp(3);
   grid.sync();
+  stamp(4);
 
   // phase 2: warp per example, everything local; 4 non-zeros per lane in flight, kept in registers for the update
   float loss_acc = 0.f, dz_acc = 0.f;
@@ -220,24 +232,23 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
       if (blockIdx.x == 0 && p.global_step) atomicAdd_system(p.global_step, 1ull);
     }
   }
+  stamp(5);
   if (p.do_update) {
     grid.sync();
-    // phase 3: one red per distinct id
-    for (int u = tid; u < U; u += nthreads) {
-      const float g = __ldcg(p.s.gbuf + u);
-      if (g != 0.f) red_add_f32_sys(dd_w_addr(p, p.s.uniq[u]), -p.lr * g);
+    stamp(6);
+    // phase 3: one red per distinct id, every CTA its segment
+    for (int u = threadIdx.x; u < U; u += kDdThreads) {
+      const float g = __ldcg(p.s.gbuf + seg0 + u);
+      if (g != 0.f) red_add_f32_sys(dd_w_addr(p, p.s.uniq[seg0 + u]), -p.lr * g);
     }
   }
-  // hand the table to the next batch: new epoch, empty list.  Every thread read U before the grid sync of phase 1,
-  // and the next unique pass is a later launch on this stream, so no further sync is needed.
-  if (p.finish) {
-    if (tid == 0) {
-      p.s.state[2] = (unsigned)U;
-      p.s.state[3] = (unsigned)nnz;
-      p.s.state[0] = 0u;
-      const unsigned e = (p.s.state[1] + 1u) & 0xffffffu;
-      p.s.state[1] = e ? e : 1u;                    // epoch 0 is what a zero-filled table holds
-    }
+  // hand the table to the next batch: a new epoch.  Every thread read the epoch in phase 0, at least one grid sync
+  // ago, and the next hash pass is a later launch on this stream.
+  if (p.finish && tid == 0) {
+    p.s.state[3] = (unsigned)nnz;
+    p.s.state[11] = (unsigned)globaltimer_ns();
+    const unsigned e = (p.s.state[1] + 1u) & 0xffffffu;
+    p.s.state[1] = e ? e : 1u;                      // epoch 0 is what a zero-filled table holds
   }
 }
 
@@ -247,9 +258,12 @@ using namespace b200ps;
 
 extern "C" int64_t b200ps_sparse_dedup_table_size(int64_t cap) {
   int64_t t = 1024;
-  while (t < 2 * cap) t <<= 1;
+  while (t < 4 * cap) t <<= 1;      // load <= 0.25: probe chains of a warp's 32 lanes stay at 1-2 positions
   return t;
 }
+
+// entries of uniq / wbuf / gbuf (and of seg_cnt: the SM count) for `cap` non-zeros on the current device
+extern "C" int64_t b200ps_sparse_dedup_list_size(int64_t cap) { return cap + (int64_t)kDdCtasPerSm * sm_count() * kDdThreads; }
 
 extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                                        float* const* w_shards, float* bias, float* pred, float* dz_out,
@@ -258,11 +272,11 @@ extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fi
                                        int32_t do_forward, int32_t do_update, int32_t finish, float lr,
                                        float grad_scale, float loss_scale, uint64_t* keys, int32_t* slot_of,
                                        int64_t table_size, int32_t* hpos, int64_t* uniq, float* wbuf, float* gbuf,
-                                       uint32_t* state, b200ps_stream_t stream) {
+                                       int64_t list_cap, uint32_t* seg_cnt, uint32_t* state, b200ps_stream_t stream) {
   B200PS_REQUIRE(B > 0 && cap > 0 && rows_per_shard > 0 && features > 0, "sparse_lr_unique: bad shape");
   B200PS_REQUIRE(features <= (int64_t)1 << kDdEpochShift, "sparse_lr_unique: ids must fit 40 bits");
   B200PS_REQUIRE(do_forward || (do_update && dz_in), "sparse_lr_unique: update-only needs dz_in");
-  B200PS_REQUIRE(keys && slot_of && hpos && uniq && wbuf && gbuf && state, "sparse_lr_unique: null scratch");
+  B200PS_REQUIRE(keys && slot_of && hpos && uniq && wbuf && gbuf && seg_cnt && state, "sparse_lr_unique: null scratch");
   B200PS_REQUIRE(table_size >= 2 * (int64_t)cap && (table_size & (table_size - 1)) == 0 && table_size <= ((int64_t)1 << 31),
                  "sparse_lr_unique: the table needs a power-of-two size of at least twice the non-zero capacity");
   cudaStream_t s = as_stream(stream);
@@ -283,6 +297,7 @@ extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fi
   p.s.keys = reinterpret_cast<unsigned long long*>(keys); p.s.slot_of = slot_of; p.s.hpos = hpos;
   p.s.uniq = reinterpret_cast<long long*>(uniq); p.s.wbuf = wbuf; p.s.gbuf = gbuf; p.s.state = state;
   p.s.tmask = (unsigned)(table_size - 1);
+  p.s.seg_cnt = seg_cnt;
 
   // the grid syncs need the whole grid resident: cooperative launch, sized below what the device can hold
   int dev = 0;
@@ -294,10 +309,14 @@ extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fi
     per_sm[dev & 63] = n > 0 ? n : -1;
   }
   B200PS_REQUIRE(per_sm[dev & 63] > 0, "sparse_lr_unique: the kernel does not fit an SM");
-  // one CTA per SM: the list passes (insert, gather, convert, scatter) are latency chains and want every SM; the
-  // example pass needs B/8 CTAs
+  // the list passes (insert, gather, convert, scatter) are chains of dependent L2 round trips (~0.45 us each under
+  // this load): as many threads as non-zeros, up to two CTAs per SM; the example pass needs B/8 CTAs
   const int want = std::max((B + kDdThreads / 32 - 1) / (kDdThreads / 32), (cap + kDdThreads - 1) / kDdThreads);
-  const int ctas = std::max(1, std::min(want, std::min(sm_count(), per_sm[dev & 63] * sm_count())));
+  const int ctas = std::max(1, std::min(want, std::min(kDdCtasPerSm, per_sm[dev & 63]) * sm_count()));
+  p.s.seg = ((cap + ctas * kDdThreads - 1) / (ctas * kDdThreads)) * kDdThreads;
+  B200PS_REQUIRE(list_cap >= (int64_t)ctas * p.s.seg,
+                 "sparse_lr_unique: uniq / wbuf / gbuf hold %lld entries, %d CTAs x %d are needed (b200ps_sparse_dedup_list_size)",
+                 (long long)list_cap, ctas, p.s.seg);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(kDdThreads); cfg.dynamicSmemBytes = 0; cfg.stream = s;
   cudaLaunchAttribute at[1];

@@ -265,22 +265,25 @@ int b200ps_sparse_lr(const int32_t* row_ptr, const int64_t* fid, const float* fv
                      int32_t do_update, float lr, float grad_scale, float loss_scale, b200ps_stream_t stream);
 int b200ps_sparse_bad_ids(uint64_t* count, int32_t reset);
 /* K4u/K5u: the same step over the batch's UNIQUE ids (lr2.py:390: embedding_lookup_sparse gathers each distinct
- * id once; lr2.py:395-396: one IndexedSlices entry per distinct row goes back).  do_unique runs the hash pass
- * (ids -> unique list `uniq`, every non-zero's table position in `hpos`); the step is one cooperative launch:
- * gather the distinct weights into wbuf, walk the examples on local buffers accumulating dz*val into gbuf, post one
- * red.add per distinct id.  A synchronous step is (do_unique=1, forward, finish=0) ... barrier ...
- * (do_unique=0, update, finish=1); `finish` advances the table's epoch so it never needs clearing.
+ * id once; lr2.py:395-396: one IndexedSlices entry per distinct row goes back).  One cooperative launch, one CTA per
+ * SM: (do_unique) hash pass — every id into an epoch-tagged open-addressing table, distinct ids appended to the
+ * inserting CTA's segment of `uniq`; gather the distinct weights into wbuf; walk the examples on local buffers
+ * accumulating dz*val into gbuf; one red.add per distinct id.  A synchronous step is (do_unique=1, forward, finish=0)
+ * ... barrier ... (do_unique=0, update, finish=1) with the same B and cap; `finish` advances the table's epoch, so
+ * the table never needs clearing.
  * Scratch, caller-owned, zero-filled once with state[1] = 1: keys [table_size] u64, slot_of [table_size] i32,
- * hpos/uniq/wbuf/gbuf [cap], state [4] u32 (state[2], state[3] = distinct ids / non-zeros of the last finished step).
- * table_size = b200ps_sparse_dedup_table_size(cap): a power of two >= 2*cap.  Ids must fit 40 bits. */
+ * hpos [cap] i32, uniq / wbuf / gbuf [list_cap], seg_cnt [2 * #SMs] u32 (distinct ids per CTA segment: their sum is the
+ * batch's distinct-id count), state [16] u32.  table_size = b200ps_sparse_dedup_table_size(cap) (a power of two
+ * >= 4*cap), list_cap = b200ps_sparse_dedup_list_size(cap).  Ids must fit 40 bits. */
+int64_t b200ps_sparse_dedup_list_size(int64_t cap);
 int64_t b200ps_sparse_dedup_table_size(int64_t cap);
 int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                             float* const* w_shards, float* bias, float* pred, float* dz_out, const float* dz_in,
                             float* loss_sum, uint64_t* global_step, int32_t B, int32_t cap, int64_t rows_per_shard,
                             int64_t features, int32_t do_unique, int32_t do_forward, int32_t do_update, int32_t finish,
                             float lr, float grad_scale, float loss_scale, uint64_t* keys, int32_t* slot_of,
-                            int64_t table_size, int32_t* hpos, int64_t* uniq, float* wbuf, float* gbuf, uint32_t* state,
-                            b200ps_stream_t stream);
+                            int64_t table_size, int32_t* hpos, int64_t* uniq, float* wbuf, float* gbuf, int64_t list_cap,
+                            uint32_t* seg_cnt, uint32_t* state, b200ps_stream_t stream);
 /* K4w/K5w: the wide & deep extension sketched at lr2_debug.py:423-428 —
  *   z = sum_j W[fid_j]*val_j + (sum_j val_j*E[fid_j,:]) . w2 + b
  * over row-sharded tables W [F,1] (optional: wide_shards may be NULL), E [F,dim] (dim 128/256/512) and

@@ -55,7 +55,7 @@ if ctx.rank == 0:
     extra = ""
     if m.dedupe:
         d, nz = m.last_unique_counts(cap, 0)
-        extra = f" distinct/nnz {d}/{nz} = {d / max(nz, 1):.3f}"
+        extra = f" distinct/nnz {d}/{nz} = {d / max(nz, 1):.3f} phases(ns: hash,sync,gather,sync,examples,sync,scatter) {m.last_phase_times_ns(cap, 0)}"
     print(f"sparse LR {args.mode} world={ctx.world} skew={args.skew} dedupe={int(m.dedupe)}: {best:.2f} us/step "
           f"({B * ctx.world / best:.1f} M examples/s) loss {loss:.4f}{extra}")
 ctx.shutdown()
