@@ -73,11 +73,12 @@ class SparseLR:
             with torch.cuda.device(device):
                 L = ops.sparse_dedup_list_size(cap)
                 sms = torch.cuda.get_device_properties(device).multi_processor_count
+            R = int(ops.native.load().b200ps_sparse_dedup_grad_copies())
             z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
             state = z(16, torch.int32)
             state[1] = 1                        # epoch 0 is what the zero-filled table holds
             self._dd[k] = dict(keys=z(T, torch.int64), slot_of=z(T, torch.int32), hpos=z(cap, torch.int32),
-                               uniq=z(L, torch.int64), wbuf=z(L, torch.float32), gbuf=z(L, torch.float32),
+                               uniq=z(L, torch.int64), wbuf=z(L, torch.float32), gbuf=z(R * L, torch.float32),
                                seg_cnt=z(2 * sms, torch.int32), state=state, table_size=T, list_cap=L)
         return self._dd[k]
 

@@ -29,6 +29,7 @@ namespace cg = cooperative_groups;
 namespace b200ps {
 
 constexpr int kDdThreads = 256;
+constexpr int kDdGradCopies = 8;                       // privatised gradient lists (a hot id's slot is one address)
 constexpr int kDdCtasPerSm = 2;                        // 75 k threads: one round of the hash pass for ~60 k non-zeros
 constexpr int kDdEpochShift = 40;                      // ids < 2^40; the upper 24 bits of a key carry the epoch
 constexpr unsigned long long kDdIdMask = (1ull << kDdEpochShift) - 1ull;
@@ -41,7 +42,10 @@ struct DedupScratch {
                               //       step kernel has converted it (-1: refused id)
   long long* uniq;            // [grid*seg] distinct ids, CTA c's in [c*seg, c*seg + seg_cnt[c])
   float* wbuf;                // [grid*seg] gathered weights
-  float* gbuf;                // [grid*seg] accumulated dz*val
+  float* gbuf;                // [kDdGradCopies][gstride] accumulated dz*val: CTA c adds into copy c % kDdGradCopies —
+                              //       the red.adds on a hot id's slot retire one after another (20 us of a 54 us step
+                              //       with one copy and an id in half of the non-zeros), the scatter sums the copies
+  long long gstride;          // list_cap
   unsigned* state;            // [16]
   unsigned* seg_cnt;          // [grid] distinct ids in each CTA's segment of uniq / wbuf / gbuf
   int seg;                    // segment length: rounds of the hash pass * 256 (a CTA cannot win more than it visits)
@@ -153,8 +157,10 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
   for (int u = threadIdx.x; u < U; u += kDdThreads) {
     const float w = p.do_forward ? __ldcg(dd_w_addr(p, p.s.uniq[seg0 + u])) : 0.f;
     p.s.wbuf[seg0 + u] = w;
-    p.s.gbuf[seg0 + u] = 0.f;
+#pragma unroll
+    for (int r = 0; r < kDdGradCopies; ++r) p.s.gbuf[r * p.s.gstride + seg0 + u] = 0.f;
   }
+  float* const gmine = p.s.gbuf + (blockIdx.x % kDdGradCopies) * p.s.gstride;
   // ... and every non-zero's table position becomes its index in the unique list (once per batch: the launch that
   // ran the unique pass), so that phase 2 is one dependent load shorter
   if (p.convert) {
@@ -193,7 +199,7 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
       } else if (p.do_update) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (sl[k] >= 0) atomicAdd(p.s.gbuf + sl[k], dz * fv[k]);
+          if (sl[k] >= 0) atomicAdd(gmine + sl[k], dz * fv[k]);
       }
     }
     if (p.do_forward) {
@@ -210,11 +216,11 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
         if (one_batch) {
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            if (sl[k] >= 0) atomicAdd(p.s.gbuf + sl[k], dz * fv[k]);
+            if (sl[k] >= 0) atomicAdd(gmine + sl[k], dz * fv[k]);
         } else {
           for (int j = beg + lane; j < end; j += 32) {
             const int u = __ldcg(p.s.hpos + j);
-            if (u >= 0) atomicAdd(p.s.gbuf + u, dz * p.fval[j]);
+            if (u >= 0) atomicAdd(gmine + u, dz * p.fval[j]);
           }
         }
       }
@@ -238,7 +244,9 @@ __global__ void __launch_bounds__(kDdThreads) sparse_lr_unique_kernel(const Dedu
     stamp(6);
     // phase 3: one red per distinct id, every CTA its segment
     for (int u = threadIdx.x; u < U; u += kDdThreads) {
-      const float g = __ldcg(p.s.gbuf + seg0 + u);
+      float g = 0.f;
+#pragma unroll
+      for (int r = 0; r < kDdGradCopies; ++r) g += __ldcg(p.s.gbuf + r * p.s.gstride + seg0 + u);
       if (g != 0.f) red_add_f32_sys(dd_w_addr(p, p.s.uniq[seg0 + u]), -p.lr * g);
     }
   }
@@ -262,8 +270,10 @@ extern "C" int64_t b200ps_sparse_dedup_table_size(int64_t cap) {
   return t;
 }
 
-// entries of uniq / wbuf / gbuf (and of seg_cnt: the SM count) for `cap` non-zeros on the current device
+// entries of uniq / wbuf (gbuf: b200ps_sparse_dedup_grad_copies() times as many) for `cap` non-zeros on this device
 extern "C" int64_t b200ps_sparse_dedup_list_size(int64_t cap) { return cap + (int64_t)kDdCtasPerSm * sm_count() * kDdThreads; }
+
+extern "C" int32_t b200ps_sparse_dedup_grad_copies(void) { return kDdGradCopies; }
 
 extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                                        float* const* w_shards, float* bias, float* pred, float* dz_out,
@@ -298,6 +308,7 @@ extern "C" int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fi
   p.s.uniq = reinterpret_cast<long long*>(uniq); p.s.wbuf = wbuf; p.s.gbuf = gbuf; p.s.state = state;
   p.s.tmask = (unsigned)(table_size - 1);
   p.s.seg_cnt = seg_cnt;
+  p.s.gstride = list_cap;
 
   // the grid syncs need the whole grid resident: cooperative launch, sized below what the device can hold
   int dev = 0;

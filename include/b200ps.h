@@ -272,10 +272,11 @@ int b200ps_sparse_bad_ids(uint64_t* count, int32_t reset);
  * ... barrier ... (do_unique=0, update, finish=1) with the same B and cap; `finish` advances the table's epoch, so
  * the table never needs clearing.
  * Scratch, caller-owned, zero-filled once with state[1] = 1: keys [table_size] u64, slot_of [table_size] i32,
- * hpos [cap] i32, uniq / wbuf / gbuf [list_cap], seg_cnt [2 * #SMs] u32 (distinct ids per CTA segment: their sum is the
+ * hpos [cap] i32, uniq / wbuf [list_cap], gbuf [b200ps_sparse_dedup_grad_copies() * list_cap], seg_cnt [2 * #SMs] u32 (distinct ids per CTA segment: their sum is the
  * batch's distinct-id count), state [16] u32.  table_size = b200ps_sparse_dedup_table_size(cap) (a power of two
  * >= 4*cap), list_cap = b200ps_sparse_dedup_list_size(cap).  Ids must fit 40 bits. */
 int64_t b200ps_sparse_dedup_list_size(int64_t cap);
+int32_t b200ps_sparse_dedup_grad_copies(void);
 int64_t b200ps_sparse_dedup_table_size(int64_t cap);
 int b200ps_sparse_lr_unique(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels,
                             float* const* w_shards, float* bias, float* pred, float* dz_out, const float* dz_in,

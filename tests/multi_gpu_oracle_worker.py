@@ -100,35 +100,44 @@ def main():
     res["async_global_step"] = st.global_step
     ctx.control_barrier()
 
-    # ---- 4. sparse LR, synchronous: weight VALUES against the float64 dense restatement
+    # ---- 4. sparse LR, synchronous: weight VALUES against the float64 dense restatement — the direct kernel on
+    #         uniform ids, then the unique-id step (sparse_dedup.cu) on ids that repeat inside and across the batches
+    from b200ps.models.sparse_lr import sparse_lr_reference
     F, SB, nnz, spread, ST = 1 << 16, 200, 30, 6, 5
-    ts = SparseLRTrainer(ctx, features=F, lr=0.5, mode="sync", use_graph=False)
-    W0 = ts.store.state_dict()
-    w_name, b_name = ts.model.W, ts.model.Bn
-    sb = []
-    for r in range(world):
-        rp = torch.empty(SB + 1, device=dev, dtype=torch.int32); fid = torch.empty(SB * (nnz + spread), device=dev, dtype=torch.int64)
-        fv = torch.empty(SB * (nnz + spread), device=dev); yy = torch.empty(SB, device=dev)
-        ops.synth_sparse(rp, fid, fv, yy, nnz_mean=nnz, spread=spread, features=F, seed=11, offset=r * SB)
-        sb.append((rp, fid, fv, yy))
-    for _ in range(ST):
-        ts.step(sb[rank])
-    torch.cuda.synchronize(); ctx.control_barrier()
-    got_s = ts.store.state_dict()
-    if rank == 0:
-        from b200ps.models.sparse_lr import sparse_lr_reference
-        W = W0[w_name].double().reshape(-1).clone(); b = W0[b_name].double().reshape(()).clone()
+    for tag, dedupe in (("sparse_sync", False), ("sparse_unique_sync", True)):
+        ts = SparseLRTrainer(ctx, features=F, lr=0.5, mode="sync", use_graph=False, dedupe=dedupe)
+        W0 = ts.store.state_dict()
+        w_name, b_name = ts.model.W, ts.model.Bn
+        sb = []
+        for r in range(world):
+            rp = torch.empty(SB + 1, device=dev, dtype=torch.int32); fid = torch.empty(SB * (nnz + spread), device=dev, dtype=torch.int64)
+            fv = torch.empty(SB * (nnz + spread), device=dev); yy = torch.empty(SB, device=dev)
+            ops.synth_sparse(rp, fid, fv, yy, nnz_mean=nnz, spread=spread, features=F, seed=11, offset=r * SB)
+            if dedupe:                           # F * u^8: a handful of ids carries most non-zeros, on every rank
+                g = torch.Generator(device=dev).manual_seed(40 + r)
+                u = torch.rand(fid.numel(), device=dev, generator=g, dtype=torch.float64)
+                fid.copy_((u.pow(8) * F).long().clamp_(0, F - 1))
+            sb.append((rp, fid, fv, yy))
         for _ in range(ST):
-            dW = torch.zeros_like(W); db = 0.0
-            for r in range(world):
-                rp, fid, fv, yy = (t.cpu() for t in sb[r])
-                _, _, (ids, vals), g_b = sparse_lr_reference(W, b, rp, fid, fv, yy)
-                dW.index_add_(0, ids, vals); db = db + g_b
-            W -= 0.5 / world * dW; b = b - 0.5 / world * db
-        res["sparse_sync_max_abs_err"] = float((got_s[w_name].double().reshape(-1) - W).abs().max())
-        res["sparse_sync_bias_err"] = float((got_s[b_name].double().reshape(()) - b).abs())
-        res["sparse_sync_global_step"] = ts.global_step
-    ctx.control_barrier()
+            ts.step(sb[rank])
+        torch.cuda.synchronize(); ctx.control_barrier()
+        got_s = ts.store.state_dict()
+        if rank == 0:
+            W = W0[w_name].double().reshape(-1).clone(); b = W0[b_name].double().reshape(()).clone()
+            for _ in range(ST):
+                dW = torch.zeros_like(W); db = 0.0
+                for r in range(world):
+                    rp, fid, fv, yy = (t.cpu() for t in sb[r])
+                    _, _, (ids, vals), g_b = sparse_lr_reference(W, b, rp, fid, fv, yy)
+                    dW.index_add_(0, ids, vals); db = db + g_b
+                W -= 0.5 / world * dW; b = b - 0.5 / world * db
+            res[tag + "_max_abs_err"] = float((got_s[w_name].double().reshape(-1) - W).abs().max())
+            res[tag + "_bias_err"] = float((got_s[b_name].double().reshape(()) - b).abs())
+            res[tag + "_global_step"] = ts.global_step
+            if dedupe:
+                d, nz = ts.model.last_unique_counts(sb[rank][1].numel(), 0)
+                res["sparse_unique_distinct_ratio"] = d / max(nz, 1)
+        ctx.control_barrier()
     # ---- 5. large dense groups: the store's NVLS path (multimem.ld_reduce / multimem.st through the switch) against
     #         a torch restatement of the synchronous update, fp32 and bf16 (+ fp32 master), then the collective pull
     import torch.distributed as dist

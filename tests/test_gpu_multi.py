@@ -95,6 +95,9 @@ def test_multi_gpu_results_match_independent_oracles(native_lib, tmp_path):
     assert res["async_conserved"] and res["async_global_step"] == 25 * n, res
     assert res["sparse_sync_max_abs_err"] < 1e-4 and res["sparse_sync_bias_err"] < 1e-5, res
     assert res["sparse_sync_global_step"] == 5, res
+    # the unique-id step on ids that repeat (the reference's gather-once / update-once plan, lr2.py:390-396)
+    assert res["sparse_unique_sync_max_abs_err"] < 1e-4 and res["sparse_unique_sync_bias_err"] < 1e-5, res
+    assert res["sparse_unique_sync_global_step"] == 5 and res["sparse_unique_distinct_ratio"] < 0.8, res
     # large groups: through the switch when the box has NVLS (else the same numbers from the P2P kernels)
     assert res["nvls_f32_master_err"] < 1e-5 and res["nvls_f32_work_err"] < 1e-5 and res["nvls_f32_pull_err"] < 1e-5, res
     assert res["nvls_bf16_master_err"] < 2e-2 and res["nvls_bf16_work_err"] < 2e-2 and res["nvls_bf16_pull_err"] < 2e-2, res
