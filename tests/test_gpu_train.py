@@ -247,9 +247,10 @@ def test_sparse_lr_trainer_learns(native_lib):
     from b200ps.parallel.context import init_from_env
     from b200ps.train import SparseLRTrainer
     F, B, nnz, spread = 1 << 12, 500, 40, 10
-    for mode in ("async", "sync"):
+    # dedupe: the unique-id step (sparse_dedup.cu), a cooperative launch inside the captured step graph
+    for mode, dedupe in (("async", False), ("sync", False), ("async", True), ("sync", True)):
         ctx = init_from_env(virtual_world=1)
-        tr = SparseLRTrainer(ctx, features=F, lr=5.0, mode=mode)
+        tr = SparseLRTrainer(ctx, features=F, lr=5.0, mode=mode, dedupe=dedupe)
         tr.store.sparse_shard(tr.model.W).mul_(0.01)       # start near zero so learning shows quickly
         batches = []
         for i in range(40):
@@ -266,7 +267,10 @@ def test_sparse_lr_trainer_learns(native_lib):
         for b in batches[32:]:
             pred, _ = tr.predict(b)
             auc.update(pred, b[3])
-        assert auc.result() > 0.65, (mode, auc.result())
+        assert auc.result() > 0.65, (mode, dedupe, auc.result())
+        if dedupe:
+            distinct, nz = tr.model.last_unique_counts(batches[0][1].numel(), 0)
+            assert 0 < distinct < nz                           # 2^12 features, ~20 k non-zeros: ids repeat
 
 
 def test_sparse_wide_deep_trainer_learns_and_checkpoints(native_lib, tmp_path):
