@@ -69,6 +69,10 @@ class SparseLR:
         gathered-weight / gradient buffers of the unique-id step."""
         k = (int(cap), key)
         if k not in self._dd:
+            if torch.cuda.is_current_stream_capturing():
+                # the epoch word must be set ONCE: a captured "state[1] = 1" would rewind it on every replay
+                raise RuntimeError("SparseLR(dedupe=True): run one eager step (or predict) on this batch shape before "
+                                   "capturing it into a CUDA graph")
             T = ops.sparse_dedup_table_size(cap)
             with torch.cuda.device(device):
                 L = ops.sparse_dedup_list_size(cap)
