@@ -18,10 +18,8 @@ gather/loss/scatter kernel (K4/K5); ``--backend gloo``: ids go up to the ps, row
 from __future__ import annotations
 
 import os
-import sys
 import tempfile
 
-import numpy as np
 import torch
 
 from .. import flags
@@ -31,7 +29,6 @@ from ..cluster.supervisor import Supervisor
 from ..data.libsvm import Sample, csr_from_sparse_triple
 from ..data.provider import DataProvider
 from ..data.queue import DeadlineExceededError, QueueClosedError
-from ..io import log
 from ..io.log import debug, error, info  # noqa: F401  (the reference's helpers, lr2.py:38-48)
 from ..metrics.auc import StreamingAUC
 from ..models.sparse_lr import SparseLR, sparse_lr_reference

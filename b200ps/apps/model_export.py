@@ -6,7 +6,6 @@ signatures ``inputs: {x}`` / ``outputs: {y}`` (model_export.py:10-11,19-66).
 """
 from __future__ import annotations
 
-import sys
 
 import numpy as np
 import torch

@@ -22,9 +22,8 @@ the reference only sketches in comments (lr2.py:329,337-346).
 from __future__ import annotations
 
 import datetime
-import os
 import struct
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 

@@ -9,7 +9,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import re
-from typing import Iterable, Iterator, List, Sequence, Tuple
+from typing import Iterator, List, Sequence
 
 import numpy as np
 

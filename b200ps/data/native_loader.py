@@ -17,7 +17,6 @@ the caller / ``shard_files``) and reader thread ``t`` takes ``files[t::threads]`
 from __future__ import annotations
 
 import ctypes as C
-import os
 from dataclasses import dataclass
 from typing import Iterator, List, Optional, Sequence
 

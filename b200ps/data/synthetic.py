@@ -7,7 +7,7 @@ materialises text shards so the loaders/parsers can be exercised end to end offl
 from __future__ import annotations
 
 import os
-from typing import List, Tuple
+from typing import List
 
 import numpy as np
 import torch

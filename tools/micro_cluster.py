@@ -1,6 +1,5 @@
 """Phase timing of the resident-cluster MNIST step (K14): CTA-0 SM-clock stamps of the last step of a launch +
 CUDA-event time per step for launches of 1 / 8 / 200 steps, 3xTF32 and plain tf32."""
-import sys
 import torch
 from b200ps import ops
 from b200ps.ops import native
