@@ -31,6 +31,7 @@
 #include <vector>
 
 #include "../common.h"
+#include "fast_parse.h"
 
 using namespace b200ps;
 
@@ -91,38 +92,18 @@ inline uint64_t rng_next(uint64_t& s) {
   return s * 2685821657736338717ull;
 }
 
-// Decimal float: digits[.digits]; anything fancier (exponent, inf, nan, hex) goes through strtof.
+// Decimal float: the exact fast path of fast_parse.h; anything fancier (exponent, inf, nan, hex, long digit strings)
+// goes through strtof.
 inline bool parse_float(const char*& q, const char* le, float* out) {
-  const char* p = q;
-  bool neg = false;
-  if (p < le && (*p == '-' || *p == '+')) { neg = *p == '-'; ++p; }
-  const char* d0 = p;
-  uint64_t ip = 0;
-  int nd = 0;
-  while (p < le && *p >= '0' && *p <= '9' && nd < 18) { ip = ip * 10 + (uint64_t)(*p - '0'); ++p; ++nd; }
-  uint64_t fp = 0;
-  int nf = 0;
-  if (p < le && *p == '.') {
-    ++p;
-    while (p < le && *p >= '0' && *p <= '9' && nf < 18) { fp = fp * 10 + (uint64_t)(*p - '0'); ++p; ++nf; }
-  }
-  const bool simple = (p > d0) && (nd + nf > 0) && (p >= le || *p == ' ' || *p == '\t' || *p == '\r');
-  if (!simple) {
-    // strtof skips leading white space (new lines included) and needs a terminator: refuse an empty value
-    // here, and a result that ran past the line; every line handed to add_line ends in '\n' or NUL
-    if (q >= le || *q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') return false;
-    char* e = nullptr;
-    const float v = strtof(q, &e);
-    if (e == q || e > le) return false;
-    *out = v;
-    q = e;
-    return true;
-  }
-  static const double p10[19] = {1,    1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,
-                                 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18};
-  double v = (double)ip + (nf ? (double)fp / p10[nf] : 0.0);
-  *out = (float)(neg ? -v : v);
-  q = p;
+  if (b200ps_parse::fast_float(q, le, out)) return true;
+  // strtof skips leading white space (new lines included) and needs a terminator: refuse an empty value
+  // here, and a result that ran past the line; every line handed to add_line ends in '\n' or NUL
+  if (q >= le || *q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') return false;
+  char* e = nullptr;
+  const float v = strtof(q, &e);
+  if (e == q || e > le) return false;
+  *out = v;
+  q = e;
   return true;
 }
 

@@ -47,6 +47,60 @@ def test_native_parser_equals_python_parser(rows, tabs):
     assert np.allclose(fv, fv2, rtol=1e-6, atol=1e-30)
 
 
+def _float32_of_decimal(text: str) -> np.float32:
+    """The correctly rounded (nearest, ties to even) float32 of a decimal string, by exact rational arithmetic."""
+    from fractions import Fraction
+    x = Fraction(text)
+    f0 = np.float32(float(text))
+    with np.errstate(over="ignore"):
+        cands = {f0, np.nextafter(f0, np.float32(np.inf)), np.nextafter(f0, np.float32(-np.inf))}
+    best = None
+    for c in cands:
+        if not np.isfinite(c):
+            continue
+        err = abs(Fraction(float(c)) - x)
+        even = (int(np.float32(c).view(np.uint32)) & 1) == 0
+        key = (err, 0 if even else 1)
+        if best is None or key < best[0]:
+            best = (key, c)
+    return np.float32(best[1])
+
+
+def test_native_parser_decimals_are_correctly_rounded():
+    """csrc/data/fast_parse.h converts plain decimals itself (m / 10^k in double, then to float) and must hand
+    anything it cannot convert exactly to strtof: every value is compared BIT FOR BIT with the correctly rounded
+    float32 of the decimal — random short and long digit strings, float rounding boundaries and their neighbours."""
+    rng = np.random.RandomState(7)
+    texts = ["0", "-0", "0.0", "5.", ".5", "000.250", "16777217", "16777217.0000001", "16777216.9999999",
+             "0.1", "0.2", "0.3", "1.00000005960464", "1.0000000596046448", "33554434", "33554435", "8388608.5",
+             "8388609.5", "0.000000000000000000001", "123456789012345", "1234567890123456", "340282346638528859811704183484516925440",
+             "0.00000000000000000000000000000000000001", "3.4028234e38", "1e-40", "1.17549435e-38", "4.5"]
+    for _ in range(6000):
+        nd, nf = rng.randint(0, 9), rng.randint(0, 12)
+        if nd + nf == 0:
+            nd = 1
+        ip = "".join(str(d) for d in rng.randint(0, 10, size=nd))
+        fp = "".join(str(d) for d in rng.randint(0, 10, size=nf))
+        texts.append(("-" if rng.rand() < 0.3 else "") + ip + ("." + fp if nf or rng.rand() < 0.1 else ""))
+    for _ in range(2000):                       # float32 halfway points (exactly, and one decimal digit to either side)
+        f = np.float32(rng.rand() * 10 ** rng.randint(-3, 6))
+        from fractions import Fraction
+        mid = (Fraction(float(f)) + Fraction(float(np.nextafter(f, np.float32(np.inf))))) / 2
+        digits = 12
+        scaled = mid * 10 ** digits
+        base = scaled.numerator // scaled.denominator
+        for delta in (-1, 0, 1):
+            v = base + delta
+            texts.append("%d.%0*d" % (v // 10 ** digits, digits, v % 10 ** digits))
+    texts = [t for t in texts if t not in ("", "-")]
+    buf = "".join("1 %d:%s\n" % (i, t) for i, t in enumerate(texts)).encode()
+    rp, fid, fv, y = libsvm.parse_buffer(buf)
+    assert len(fv) == len(texts) and fid.tolist() == list(range(len(texts)))
+    want = np.asarray([_float32_of_decimal(t) for t in texts], dtype=np.float32)
+    bad = np.nonzero(fv.view(np.uint32) != want.view(np.uint32))[0]
+    assert bad.size == 0, [(texts[i], float(fv[i]), float(want[i])) for i in bad[:5]]
+
+
 def test_native_parser_reports_bad_line():
     with pytest.raises(ValueError, match="line 2"):
         libsvm.parse_buffer(b"1 3:1\n0 oops\n")
