@@ -42,7 +42,8 @@ def test_example_async_one_ps_two_workers(tmp_path):
     # async: global_step counts every worker's update => ends at 2 workers x 2 epochs x 15 batches
     finals = [int(PROGRESS.fullmatch([l for l in lines_of(out, w) if l.startswith("Step:")][-1]).group(2))
               for w in ("worker:0", "worker:1")]
-    assert max(finals) == 60 and min(finals) >= 45
+    # (the first finisher has at least its own 30 in; how many of the other's depends on when that one started)
+    assert max(finals) == 60 and min(finals) >= 30
     ps = lines_of(out, "ps:0")
     assert ps[0] == "ps 0 start ..." and any("Terminating parameter server: 0" in l for l in ps)
     # per-task summary directories with readable event files (example.py:48-51,154,171)
