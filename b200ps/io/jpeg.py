@@ -10,6 +10,7 @@ also the CPU oracle of the GPU kernels.  Baseline sequential JPEG only (what PIL
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence, Tuple
 
 import numpy as np
@@ -30,6 +31,9 @@ class JpegDesc(C.Structure):
                 ("total_coefs", C.c_int64), ("comp", JpegComp * 3)]
 
 
+MAX_PIXELS = int(os.environ.get("B200PS_JPEG_MAX_PIXELS", str(64 << 20)))
+
+
 def jpeg_info(data: bytes) -> Tuple[int, int, int]:
     """(height, width, components) from the frame header."""
     lib = native.load()
@@ -42,6 +46,8 @@ def parse_jpeg(data: bytes):
     """Host stage: (descriptor, int16 coefficient array in natural order)."""
     lib = native.load()
     h, w, n = jpeg_info(data)
+    if h * w > MAX_PIXELS:            # a damaged frame header can claim 65535 x 65535: refuse before allocating for it
+        raise ValueError(f"jpeg: {w} x {h} pixels exceeds the limit of {MAX_PIXELS} (B200PS_JPEG_MAX_PIXELS)")
     cap = ((w + 15) // 16 * 16) * ((h + 15) // 16 * 16) * max(n, 1) + 64
     coef = np.zeros(cap, dtype=np.int16)
     desc = JpegDesc()

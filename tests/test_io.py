@@ -255,6 +255,40 @@ def test_jpeg_decoder_host_path_matches_pil(native_lib):
         jpeg_info(b"not a jpeg at all")
 
 
+def test_jpeg_decoder_survives_damaged_files(native_lib):
+    """Truncated files, flipped bytes and inserted garbage: the entropy decoder either refuses the file with an
+    error or returns an image of the announced shape — it never reads outside its buffers (a crash here would take
+    the test process down) and never allocates for a frame header that claims gigapixels."""
+    from b200ps.io import jpeg
+    from b200ps.ops import native
+    rng = np.random.default_rng(1)
+    cases = [d for d, _ in _jpeg_cases()]
+    decoded = refused = 0
+    for it in range(900):
+        d = bytearray(cases[it % len(cases)])
+        mode = it % 3
+        if mode == 0:
+            d = d[: rng.integers(0, len(d))]
+        elif mode == 1:
+            for _ in range(rng.integers(1, 6)):
+                d[rng.integers(0, len(d))] = rng.integers(0, 256)
+        else:
+            i = int(rng.integers(0, len(d)))
+            d[i:i] = bytes(rng.integers(0, 256, size=rng.integers(1, 40), dtype=np.uint8))
+        try:
+            out = jpeg.decode_jpeg_numpy(bytes(d))
+            assert out.ndim == 3 and out.shape[2] == 3 and out.dtype == np.uint8
+            decoded += 1
+        except (ValueError, native.NativeError):
+            refused += 1
+    assert decoded > 100 and refused > 100
+    big = bytearray(cases[0])
+    sof = big.index(b"\xff\xc0")
+    big[sof + 5:sof + 9] = b"\xff\xff\xff\xff"                # 65535 x 65535
+    with pytest.raises(ValueError, match="exceeds the limit"):
+        jpeg.parse_jpeg(bytes(big))
+
+
 @pytest.mark.gpu
 def test_jpeg_decoder_gpu_matches_pil(native_lib):
     """The CUDA stage (inverse DCT, chroma upsampling, YCbCr->RGB) against PIL, +-1 LSB (decode_jpeg(channels=3),
