@@ -196,6 +196,48 @@ def test_native_bundle_writer_reader_match_python_twin(tmp_path, monkeypatch):
         tf_bundle.read_bundle(p)
 
 
+@pytest.mark.parametrize("use_native", ["1", "0"], ids=["native", "python"])
+def test_bundle_readers_refuse_damaged_files(tmp_path, monkeypatch, use_native):
+    """Truncation, flipped bytes and inserted garbage in either file of a checkpoint: both readers answer with a
+    ValueError (or, when the damage is a no-op, the right tensors) — never a crash, never silently wrong values."""
+    import numpy as np
+    from b200ps.io import tf_bundle
+    from b200ps.ops import native
+    if use_native == "1" and not native.available():
+        pytest.skip("libb200ps.so not built")
+    monkeypatch.setenv("B200PS_NATIVE_BUNDLE", use_native)
+    rng = np.random.default_rng(3)
+    tensors = {"global_step": np.float32(17.0), "w/Variable": rng.standard_normal((20, 7)).astype(np.float32),
+               "ids": rng.integers(-2**40, 2**40, size=37)}
+    for i in range(40):
+        tensors["layer_%03d/weights" % i] = rng.standard_normal((i % 5 + 1, 3)).astype(np.float32)
+    p = str(tmp_path / "model.ckpt-1")
+    tf_bundle.write_bundle(p, tensors)
+    files = {s: open(p + s, "rb").read() for s in (".index", ".data-00000-of-00001")}
+    refused = 0
+    for it in range(240):
+        cur = {k: bytearray(v) for k, v in files.items()}
+        tgt = cur[".index" if it % 2 == 0 else ".data-00000-of-00001"]
+        mode = (it // 2) % 3
+        if mode == 0:
+            del tgt[int(rng.integers(0, len(tgt))):]
+        elif mode == 1:
+            for _ in range(int(rng.integers(1, 4))):
+                tgt[int(rng.integers(0, len(tgt)))] = int(rng.integers(0, 256))
+        else:
+            i = int(rng.integers(0, len(tgt)))
+            tgt[i:i] = bytes(rng.integers(0, 256, size=int(rng.integers(1, 30)), dtype=np.uint8))
+        for k, v in cur.items():
+            open(p + k, "wb").write(bytes(v))
+        try:
+            got = tf_bundle.read_bundle(p)
+        except ValueError:
+            refused += 1
+            continue
+        assert set(got) == set(tensors) and all(np.array_equal(got[k], np.asarray(v)) for k, v in tensors.items())
+    assert refused > 200
+
+
 def test_native_events_writer_matches_python_twin(tmp_path, monkeypatch):
     """csrc/io/events.cpp vs b200ps/io/events.py: byte-identical scalar records for the same inputs."""
     from b200ps.io import events
