@@ -57,17 +57,24 @@ flags.DEFINE_integer("deep_dim", 0, "0 = plain LR (lr2.py); 128/256/512 adds the
                      "deep part sketched at lr2_debug.py:423-428")
 flags.DEFINE_float("init_stddev", 0.0, "stddev of the weight initialiser; 0 = the script's default (1.0 for LR as in "
                    "lr2.py:384, 0.01 with --deep_dim as in lr2_debug.py:288-289)")
-flags.DEFINE_boolean("native_loader", False, "GPU backend: read, sample and batch the train files with the native loader "
-                     "threads (packed pinned batches -> one H2D copy + one graph launch per step) instead of the "
-                     "Python DataProvider")
+flags.DEFINE_boolean("native_loader", False, "read, sample and batch the train files with the native loader threads instead "
+                     "of the Python DataProvider (GPU backend: packed pinned batches -> one H2D copy + one graph launch "
+                     "per step; gloo backend: the CSR arrays go straight to the CPU step)")
 flags.DEFINE_boolean("unique_ids", False, "GPU backend, plain LR: make each batch's ids unique on the device first (one read and "
                      "one update per distinct id, as embedding_lookup_sparse / IndexedSlices do); pays when ids repeat")
 flags.DEFINE_integer("synthetic_rows", 4000, "rows per synthetic file when --train/--test is 'synthetic'")
 
 
+def _csr(samples):
+    """A batch as CPU tensors (row_ptr, fid, fval, labels): a list of Samples is formatted, a CSR tuple (numpy or
+    torch: what the native loader hands out) is taken as it is."""
+    if isinstance(samples, tuple):
+        return tuple(a if isinstance(a, torch.Tensor) else torch.from_numpy(a) for a in samples)
+    return tuple(torch.from_numpy(a) for a in Sample.format_samples_csr(samples))
+
+
 def _to_device_batch(samples, device):
-    row_ptr, fid, fval, labels = Sample.format_samples_csr(samples)
-    return tuple(torch.from_numpy(a).to(device) for a in (row_ptr, fid, fval, labels))
+    return tuple(a.to(device) for a in _csr(samples))
 
 
 class _CpuRunner:
@@ -77,7 +84,7 @@ class _CpuRunner:
         self.store, self.model, self.lr, self.sync, self.replicas = store, model, lr, sync, replicas
 
     def _fwd(self, samples, train):
-        row_ptr, fid, fval, labels = (torch.from_numpy(a) for a in Sample.format_samples_csr(samples))
+        row_ptr, fid, fval, labels = _csr(samples)
         uniq, inv = torch.unique(fid, return_inverse=True)
         rows = self.store.sparse_pull(self.model.W, uniq)
         self.store.pull()
@@ -111,7 +118,7 @@ class _CpuWideDeepRunner:
 
     def _fwd(self, samples, train):
         m = self.model
-        row_ptr, fid, fval, labels = (torch.from_numpy(a) for a in Sample.format_samples_csr(samples))
+        row_ptr, fid, fval, labels = _csr(samples)
         uniq, inv = torch.unique(fid, return_inverse=True)
         W = self.store.sparse_pull(m.W, uniq) if m.wide else None
         E = self.store.sparse_pull(m.E, uniq)
@@ -260,20 +267,30 @@ def main(argv=None) -> int:
         info("Start train ...")
         step_num, iter_num = 0, 0
         info("num_epochs: %d" % num_epochs)
-        if gpu and FLAGS.native_loader:
+        if FLAGS.native_loader:
             # the input side of lr2.py:87-169 in native threads: thread_num readers over this worker's files,
-            # Bernoulli sampling, batches of exactly batch_size rows in pinned buffers
+            # Bernoulli sampling, batches of exactly batch_size rows (pinned buffers on the GPU backend)
             from ..data.native_loader import NativeLibsvmLoader
             files = DataProvider.GetFileList(FLAGS.train, num_workers, FLAGS.task_index)
             while iter_num < num_epochs:
                 loader = NativeLibsvmLoader(files, FLAGS.batch_size, threads=FLAGS.thread_num,
-                                            sampling_rate=FLAGS.train_sampling_rate, epochs=1, seed=FLAGS.seed + iter_num)
+                                            sampling_rate=FLAGS.train_sampling_rate, epochs=1, seed=FLAGS.seed + iter_num,
+                                            pinned=gpu)
                 base = step_num
 
                 def on_loss(i, loss, base=base, epoch=iter_num):
                     if (base + i + 1) % trace_step_interval == 0:
                         Test(runner, store, epoch, base + i + 1, test_samples)
-                step_num += trainer.fit_from_loader(loader, on_loss=on_loss)
+                if gpu:
+                    step_num += trainer.fit_from_loader(loader, on_loss=on_loss)
+                else:
+                    for i, batch in enumerate(loader):
+                        n, z = batch.rows, batch.nnz
+                        rp, fid, fval, y = batch.arrays()
+                        runner.train_step((rp[: n + 1].clone(), fid[:z].clone(), fval[:z].clone(), y[:n].clone()))
+                        batch.release()
+                        step_num += 1
+                        on_loss(i, None)
                 info("native loader: %s" % loader.stats())
                 loader.close()
                 Test(runner, store, iter_num, step_num, test_samples)

@@ -126,6 +126,21 @@ def test_lr2_app_queue_mode_and_log_lines(tmp_path):
     assert re.search(r"\[\d{4}-\d\d-\d\d \d\d:\d\d:\d\d\] \[worker:0\] Start train \.\.\.", out)
 
 
+def test_lr2_native_loader_on_the_gloo_backend(tmp_path):
+    """--native_loader on the CPU backend: the C++ reader threads parse, sample and batch this worker's files and the
+    CSR arrays go straight into the CPU step (no per-line Python, lr2.py:57-84's hot spot)."""
+    rc, out = launch(tmp_path, ["--num_ps", "1", "--num_workers", "2", "lr2", "--", "--backend", "gloo", "--train", "synthetic",
+                                "--test", "synthetic", "--features", "3000", "--num_epochs", "3", "--batch_size", "100",
+                                "--learning_rate", "0.5", "--synthetic_rows", "400", "--native_loader",
+                                "--trace_step_interval", "2"])
+    assert rc == 0, out
+    for w in ("worker:0", "worker:1"):
+        assert any("native loader: " in l and "'malformed': 0" in l and "'batches': 4" in l for l in lines_of(out, w)), out
+    ls = lines_of(out, "worker:0")               # the one synthetic test file is worker 0's share (lr2.py:232-253)
+    assert any(re.search(r"epoch: \d+, local step: \d+, global step: \d+, loss: [\d.]+", l) for l in ls), out
+    assert any(re.search(r"Finish evaluate, auc: \(0\.\d+, 0\.\d+\)", l) for l in ls), out
+
+
 def test_lr2_round_robin_vs_flat_shard_two_ps(tmp_path):
     for placement in ("round_robin_variable", "flat_shard"):
         rc, out = launch(tmp_path / placement, ["--num_ps", "2", "--num_workers", "2", "lr2", "--", "--backend", "gloo",
