@@ -9,8 +9,9 @@
 //   dE[f] = c_f * w2,  dW[f] = c_f,  dw2 = sum_f c_f * E[f]    backward: c_f = -lr * sum dz_i v_ij is a scalar, the
 //                                                              rank-one row update and the w2 gradient are OWNER work
 //
-// so a step becomes three collective phases separated by the cross-GPU barrier kernel, all remote traffic posted
-// writes of 4-8 bytes (no remote read, no row ever crosses a link):
+// so a step becomes collective phases separated by the cross-GPU barrier kernel; the remote traffic is posted writes
+// of 4-8 bytes, no row ever crosses a link, and the only remote READ is the (sharded) w2 vector, once per CTA of the
+// serve and fold kernels (once per warp it was half of the step at 8 GPUs):
 //
 //   request   every rank buckets its batch's non-zeros by owner (warp-aggregated slot allocation) and writes
 //             {local row, non-zero index} into the owner's inbox; the last CTA publishes the per-owner counts
