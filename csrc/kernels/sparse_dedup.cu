@@ -9,12 +9,15 @@
 //
 // one cooperative launch, up to two CTAs per SM, four phases separated by grid syncs:
 //   0. unique   every non-zero inserts its id into an open-addressing hash table in this GPU's memory (64-bit keys
-//               tagged with a step epoch, so the table is never cleared); the winners of an insert take the next
-//               slots of the unique list (one atomic per warp).  Each non-zero remembers its table position.
+//               tagged with a 24-bit step epoch, so the table is never cleared; a slot is rewritten every few steps,
+//               an entry surviving a whole epoch cycle is not a practical event); the winners of an insert take the
+//               next slots of their CTA's OWN segment of the unique list (shared-memory counter: no global one).
+//               Each non-zero remembers its table position.
 //   1. gather   wbuf[u] = W[uniq[u]]  for the U distinct ids (the only remote reads), gbuf[u] = 0; the non-zeros'
 //               table positions become indices into the unique list
-//   2. examples warp per example: z from wbuf (local), loss, dz; dz*val added into gbuf (local atomics)
-//   3. scatter  one red.add of -lr*gbuf[u] per distinct id (the only remote writes)
+//   2. examples warp per example: z from wbuf (local), loss, dz; dz*val added into one of 8 private copies of gbuf
+//               (local atomics; a hot id's slot is a single address)
+//   3. scatter  one red.add of -lr*sum(gbuf copies)[u] per distinct id (the only remote writes)
 //
 // Remote traffic per step: U reads + U reds instead of nnz + nnz.  With nothing repeated it costs three grid syncs
 // and the hash pass more than the direct kernel, so it is a choice (SparseLR(dedupe=True)), not the default.
