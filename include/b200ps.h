@@ -313,14 +313,18 @@ int b200ps_sparse_wd_apply(float* pend_local, float* wide_local, float* emb_loca
  * request: bucket this rank's non-zeros by owner, write {local row, non-zero index} into the owners' inboxes
  * (inbox[o] + rank*cap + slot) and publish the counts (inbox_cnt[o][rank]); `count` = world+1 zeroed device words.
  * serve (after a cross-rank barrier): dot every requested LOCAL row with w2, add the wide weight, write the scalar
- * pair into the requester's resp[owner*cap + slot] (inbox order: coalesced remote writes; resp holds world*cap pairs).  loss (after a barrier): z, loss, dz from the response array; with
- * do_update the coefficients -lr*dz*v go as scalar red.adds into the owners' pending table (then a barrier and
- * b200ps_sparse_wd_apply with pend2_shards fold them in).  Replaces the row gather / row scatter of
- * embedding_lookup_sparse (lr2.py:390, lr2_debug.py:423-428) by ~24 bytes of posted writes per non-zero. */
+ * pair into the requester's resp[owner*cap + slot] (inbox order: a warp's answers are one contiguous remote write;
+ * resp holds world*cap pairs; `slot_tab`, filled by request, tells the requester where each non-zero's answer lands).
+ * loss (after a barrier): z, loss, dz from the response array; with do_update the coefficients -lr*dz*v go as scalar
+ * red.adds into the owners' pending table.  fold (after a barrier): the owner folds the coefficients of the rows its
+ * inbox names (W += c, dw2 += c*E_old[row], E[row] += c*w2); after one more barrier b200ps_sparse_wd_apply phase 2
+ * folds w2 (and the pending bias).  Replaces the row gather / row scatter of embedding_lookup_sparse (lr2.py:390,
+ * lr2_debug.py:423-428) by ~24 bytes of posted writes per non-zero. */
 int b200ps_wd_owner_request(const int32_t* row_ptr, const int64_t* fid, int32_t B, int32_t world, int32_t rank,
                             int32_t cap, int64_t rows_per_shard, int64_t features, void* const* inbox,
-                            uint32_t* const* inbox_cnt, void* const* resp, uint32_t* count, int32_t* slot_tab /* [cap] local:
-                            where each non-zero's answer will land (owner*cap + slot) */, b200ps_stream_t stream);
+                            uint32_t* const* inbox_cnt, void* const* resp, uint32_t* count,
+                            int32_t* slot_tab /* [cap] local: owner*cap + slot of each non-zero's answer */,
+                            b200ps_stream_t stream);
 int b200ps_wd_owner_serve(int32_t world, int32_t rank, int32_t cap, void* const* inbox, uint32_t* const* inbox_cnt,
                           void* const* resp, const float* emb_local, const float* wide_local, int32_t dim,
                           float* const* w2_shards, int64_t w2_rows_per_shard, b200ps_stream_t stream);
@@ -330,8 +334,8 @@ int b200ps_wd_owner_fold(int32_t world, int32_t rank, int32_t cap, void* const* 
 int b200ps_wd_owner_loss(const int32_t* row_ptr, const int64_t* fid, const float* fval, const float* labels, int32_t B,
                          int32_t world, int32_t rank, int32_t cap, int64_t rows_per_shard, int64_t features,
                          void* const* resp, const int32_t* slot_tab, float* const* pend_shards, float* bias,
-                         float* bias_pend /* pending bias
-                         update on the bias owner, folded after the round (NULL: update bias in place) */, float* pred,
+                         float* bias_pend /* pending bias update on the bias owner, folded after the round (NULL:
+                         update the bias in place) */, float* pred,
                          float* dz_out, float* loss_sum, uint64_t* global_step, int32_t do_update, float lr,
                          float grad_scale, float loss_scale, b200ps_stream_t stream);
 int b200ps_auc_hist(const float* pred, const float* labels, int32_t B, const float* thresholds,
