@@ -1,4 +1,5 @@
-// b200ps — number parsing for the libsvm readers (libsvm_parse.cpp, loader.cpp).
+// b200ps — number parsing for the libsvm readers (libsvm_parse.cpp, loader.cpp): the int(...) / float(...) calls of
+// Sample.parse_line_libsvm (lr2.py:57-67), which the reference runs once per feature in CPython.
 //
 // strtol / strtoll / strtof cost 50-150 ns per token, want a NUL terminator and skip leading white space including
 // new lines, so a bounded (pointer, end) reader has to copy every line first.  Almost every token of a libsvm file is
