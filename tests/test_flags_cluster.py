@@ -149,3 +149,26 @@ def test_trace_helpers_step_timer_and_disabled_nvtx():
     time.sleep(0.02); t.tick(4)
     avg = t.report()
     assert x == 1 and 3.0 < avg < 50.0 and t.report() >= 0.0
+
+
+def test_cpu_thread_cap_for_single_host_clusters(monkeypatch):
+    """Tasks started by hand on one host share its cores: every task keeps cores / (2 x tasks) intra-op threads,
+    unless OMP_NUM_THREADS is set or the cluster spans other hosts (then the choice is the user's)."""
+    import os
+    import torch
+    from b200ps.cluster.server import _cap_cpu_threads
+    from b200ps.cluster.spec import ClusterSpec
+    before = torch.get_num_threads()
+    try:
+        torch.set_num_threads(max(before, 2))
+        monkeypatch.setenv("OMP_NUM_THREADS", "7")
+        _cap_cpu_threads(ClusterSpec.local(1, 2))
+        assert torch.get_num_threads() == max(before, 2)                      # the user chose: untouched
+        monkeypatch.delenv("OMP_NUM_THREADS")
+        _cap_cpu_threads(ClusterSpec({"ps": ["10.0.0.1:2222"], "worker": ["localhost:2223"]}))
+        assert torch.get_num_threads() == max(before, 2)                      # other hosts: untouched
+        _cap_cpu_threads(ClusterSpec.local(1, 2))
+        want = max(1, min(max(before, 2), (os.cpu_count() or 1) // 6))
+        assert torch.get_num_threads() == want
+    finally:
+        torch.set_num_threads(before)
