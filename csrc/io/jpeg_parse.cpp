@@ -23,8 +23,11 @@ struct Huff {
   int mincode[17], maxcode[18], valptr[17];   // by code length 1..16
   uint8_t look_len[512];                      // 9-bit fast path: code length (0 = longer than 9 bits)
   uint8_t look_sym[512];
+  // AC tables: when a code AND its value bits fit the 9-bit window, one lookup yields everything —
+  // (value << 8) | (run << 4) | (code length + value bits); 0 = take the general path
+  int16_t fast_ac[512];
 
-  void build(const uint8_t counts[16], const uint8_t* syms, int nsyms) {
+  void build(const uint8_t counts[16], const uint8_t* syms, int nsyms, bool is_ac) {
     present = true;
     memcpy(symbols, syms, nsyms);
     memset(look_len, 0, sizeof(look_len));
@@ -42,19 +45,29 @@ struct Huff {
       code <<= 1;
     }
     maxcode[17] = 0x7fffffff;
+    for (int i = 0; is_ac && i < 512; ++i) {
+      fast_ac[i] = 0;
+      const int len = look_len[i];
+      if (!len) continue;
+      const int rs = look_sym[i], run = rs >> 4, sz = rs & 15;
+      if (sz == 0 || len + sz > 9) continue;
+      int v = ((i << len) & 511) >> (9 - sz);                 // the sz bits behind the code
+      if (v < (1 << (sz - 1))) v += (int)((~0u) << sz) + 1;   // sign extension of the JPEG magnitude code
+      if (v >= -128 && v <= 127) fast_ac[i] = (int16_t)(v * 256 + run * 16 + (len + sz));
+    }
   }
 };
 
 struct BitReader {
   const uint8_t* p;
   const uint8_t* end;
-  uint32_t acc = 0;
+  uint64_t acc = 0;                            // the next bits of the stream, left-aligned
   int nbits = 0;
   bool hit_marker = false;
 
-  void fill() {
-    while (nbits <= 24) {
-      uint32_t byte = 0;
+  void fill() {                                // up to 64 bits ahead; zeros past the data or behind a marker
+    while (nbits <= 56) {
+      uint64_t byte = 0;
       if (!hit_marker && p < end) {
         byte = *p;
         if (byte == 0xFF) {
@@ -64,11 +77,11 @@ struct BitReader {
           ++p;
         }
       }
-      acc |= byte << (24 - nbits);
+      acc |= byte << (56 - nbits);
       nbits += 8;
     }
   }
-  inline uint32_t peek(int n) { if (nbits < n) fill(); return acc >> (32 - n); }
+  inline uint32_t peek(int n) { if (nbits < n) fill(); return (uint32_t)(acc >> (64 - n)); }
   inline void skip(int n) { acc <<= n; nbits -= n; }
   inline int get(int n) { if (n == 0) return 0; const uint32_t v = peek(n); skip(n); return (int)v; }
   void reset() { acc = 0; nbits = 0; hit_marker = false; }
@@ -158,7 +171,7 @@ extern "C" int b200ps_jpeg_parse(const uint8_t* data, uint64_t len, int16_t* coe
         int total = 0;
         for (int i = 0; i < 16; ++i) total += s[o + 1 + i];
         B200PS_REQUIRE(tc < 2 && th < 4 && total <= 256 && o + 17 + total <= n, "jpeg: bad Huffman table");
-        (tc ? ac[th] : dc[th]).build(s + o + 1, s + o + 17, total);
+        (tc ? ac[th] : dc[th]).build(s + o + 1, s + o + 17, total, tc != 0);
         o += 17 + total;
       }
     } else if (m == 0xC0 || m == 0xC1) {                        // SOF0 / SOF1 (Huffman, sequential)
@@ -244,8 +257,18 @@ extern "C" int b200ps_jpeg_parse(const uint8_t* data, uint64_t len, int16_t* coe
               B200PS_REQUIRE(sbits >= 0 && sbits <= 11, "jpeg: corrupt DC code (MCU %d)", mcu);
               if (sbits) pred[c] += extend(br.get(sbits), sbits);
               blk[0] = (int16_t)pred[c];
+              const Huff& hac = ac[ta[c]];
               for (int k = 1; k < 64;) {
-                const int rs = decode_symbol(br, ac[ta[c]]);
+                const int f = hac.fast_ac[br.peek(9)];
+                if (f) {                                        // run, value and length from one lookup
+                  k += (f >> 4) & 15;
+                  B200PS_REQUIRE(k < 64, "jpeg: AC run past the block (MCU %d)", mcu);
+                  blk[kZigzag[k]] = (int16_t)(f >> 8);
+                  br.skip(f & 15);
+                  ++k;
+                  continue;
+                }
+                const int rs = decode_symbol(br, hac);
                 B200PS_REQUIRE(rs >= 0, "jpeg: corrupt AC code (MCU %d)", mcu);
                 const int r = rs >> 4, sz = rs & 15;
                 if (sz == 0) {
