@@ -295,6 +295,13 @@ def test_jpeg_decoder_host_path_matches_pil(native_lib):
         assert torch.equal(decode_jpeg(data, device="cpu"), torch.from_numpy(got))
     with pytest.raises(Exception):
         jpeg_info(b"not a jpeg at all")
+    # a batch: the host stage of the files on a thread pool, same pixels as one by one
+    from b200ps.io.jpeg import decode_jpeg_batch, parse_jpeg_batch
+    same = [d for d, r in _jpeg_cases() if r.shape[:2] == (28, 28)] * 3
+    got = decode_jpeg_batch(same, device="cpu")
+    assert torch.equal(got, torch.stack([torch.from_numpy(decode_jpeg_numpy(d)) for d in same]))
+    for (d1, c1), (d2, c2) in zip(parse_jpeg_batch(same, threads=4), parse_jpeg_batch(same, threads=1)):
+        assert np.array_equal(c1, c2) and d1.total_coefs == d2.total_coefs
 
 
 def test_jpeg_decoder_survives_damaged_files(native_lib):
