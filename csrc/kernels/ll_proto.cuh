@@ -23,7 +23,7 @@ __device__ __forceinline__ void st_packet(uint2* p, float v, uint32_t epoch) {
   {   // a slot is written exactly once per epoch, and epochs only move forward
     uint32_t ov, oe;
     asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(ov), "=r"(oe) : "l"(p) : "memory");
-    B200PS_DEV_CHECK(oe < epoch, "packet slot %p rewritten: holds epoch %u, writing epoch %u\n", (void*)p, oe, epoch);
+    B200PS_DEV_CHECK((int32_t)(oe - epoch) < 0 /* wrap-safe: epochs are 32-bit counters */, "packet slot %p rewritten: holds epoch %u, writing epoch %u\n", (void*)p, oe, epoch);
   }
 #endif
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
@@ -42,7 +42,7 @@ __device__ __forceinline__ float poll_packet(const uint2* p, uint32_t epoch) {
     uint32_t spins = 0;
     do {
       asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(p) : "memory");
-      B200PS_DEV_CHECK(f <= epoch, "packet %p is from the future: epoch %u while waiting for %u\n", (void*)p, f, epoch);
+      B200PS_DEV_CHECK((int32_t)(f - epoch) <= 0, "packet %p is from the future: epoch %u while waiting for %u\n", (void*)p, f, epoch);
       if ((++spins & 0xff) == 0 && globaltimer_ns() - t0 > B200PS_WAIT_TIMEOUT_NS) {
         printf("b200ps: LL packet wait timed out (block %d, want epoch %u, have %u)\n", blockIdx.x, epoch, f);
         __trap();
